@@ -1,0 +1,116 @@
+"""ctypes binding of the C-ABI library (include/b200_retrieval.h).
+
+There is deliberately no fallback: if ``libb200_retrieval.so`` has not been built, or no sm_100
+device is visible, importing the native layer / creating a handle fails loudly.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libb200_retrieval.so")
+
+OK, ERR_INVALID, ERR_DIMENSION, ERR_NOT_FOUND, ERR_CUDA, ERR_UNSUPPORTED, ERR_NOMEM = 0, -1, -2, -3, -4, -5, -6
+MASTER_F32, MASTER_BF16 = 0, 1
+
+
+class EncoderConfigC(ctypes.Structure):
+    _fields_ = [
+        ("vocab_size", ctypes.c_int32), ("hidden", ctypes.c_int32), ("layers", ctypes.c_int32),
+        ("heads", ctypes.c_int32), ("intermediate", ctypes.c_int32), ("max_pos", ctypes.c_int32),
+        ("type_vocab", ctypes.c_int32), ("ln_eps", ctypes.c_float),
+    ]
+
+
+#: every symbol include/b200_retrieval.h declares: name -> (restype, argtypes)
+_vp, _i, _i64, _cp = ctypes.c_void_p, ctypes.c_int, ctypes.c_int64, ctypes.c_char_p
+SYMBOLS = {
+    "b200_last_error": (_cp, []),
+    "b200_version": (_i, []),
+    "b200_device_count": (_i, []),
+    "b200_index_create": (_i, [_i, _i64, _i, _i, ctypes.POINTER(_vp)]),
+    "b200_index_destroy": (_i, [_vp]),
+    "b200_index_clear": (_i, [_vp]),
+    "b200_index_count": (_i64, [_vp]),
+    "b200_index_dim": (_i, [_vp]),
+    "b200_index_reserve": (_i, [_vp, _i64]),
+    "b200_index_add": (_i, [_vp, _vp, _i64, _i, _vp]),
+    "b200_index_remove_rows": (_i, [_vp, _vp, _i64, _vp]),
+    "b200_index_get_rows": (_i, [_vp, _vp, _i64, _vp, _i, _vp]),
+    "b200_index_search": (_i, [_vp, _vp, _i, _i, _i64, _i, _i64, _vp, _vp, _i, _vp]),
+    "b200_merge_topk": (_i, [_vp, _vp, _i64, _i, _i, _i, _vp, _vp, _i, _vp]),
+    "b200_encoder_create": (_i, [ctypes.POINTER(EncoderConfigC), _i, ctypes.POINTER(_vp)]),
+    "b200_encoder_destroy": (_i, [_vp]),
+    "b200_encoder_load_tensor": (_i, [_vp, _cp, _vp, _i64]),
+    "b200_encoder_finalize": (_i, [_vp]),
+    "b200_encoder_hidden": (_i, [_vp]),
+    "b200_encode": (_i, [_vp, _vp, _vp, _i, _i, _i, _vp, _i, _vp]),
+}
+
+_lib = None
+
+
+def lib() -> ctypes.CDLL:
+    """Load the shared library once; raise if it is missing (no CPU path exists)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(
+                f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                "(or `make -C copilot-for-consensus_b200/csrc`). There is no CPU fallback."
+            )
+        L = ctypes.CDLL(LIB_PATH)
+        for name, (res, args) in SYMBOLS.items():
+            fn = getattr(L, name)  # AttributeError here means header and library disagree
+            fn.restype, fn.argtypes = res, args
+        _lib = L
+    return _lib
+
+
+def last_error() -> str:
+    msg = lib().b200_last_error()
+    return msg.decode("utf-8", "replace") if msg else ""
+
+
+def check(rc: int) -> None:
+    """Map a C status to the Python exception the reference's contract uses."""
+    if rc == OK:
+        return
+    msg = last_error() or f"b200 error {rc}"
+    if rc in (ERR_INVALID, ERR_DIMENSION):
+        raise ValueError(msg)
+    if rc == ERR_NOT_FOUND:
+        raise KeyError(msg)
+    if rc == ERR_NOMEM:
+        raise MemoryError(msg)
+    raise RuntimeError(msg)
+
+
+def device_index(device) -> int:
+    """'cuda', 'cuda:3', 3, torch.device -> ordinal.  Anything that is not a CUDA device is refused."""
+    if isinstance(device, int):
+        return device
+    s = str(device)
+    if s == "cuda":
+        try:
+            import torch
+
+            return torch.cuda.current_device() if torch.cuda.is_available() else 0
+        except Exception:
+            return 0
+    if s.startswith("cuda:"):
+        return int(s.split(":", 1)[1])
+    raise ValueError(f"the B200 path needs a CUDA device, got {device!r}")
+
+
+def current_stream_ptr(device_ordinal: int) -> int:
+    """torch's current stream on that device as a cudaStream_t value (0 = legacy default stream)."""
+    try:
+        import torch
+
+        if torch.cuda.is_available():
+            return int(torch.cuda.current_stream(device_ordinal).cuda_stream)
+    except Exception:
+        pass
+    return 0

@@ -1,0 +1,103 @@
+// host_util.h -- host-side plumbing shared by index.cu and encoder.cu: thread-local error
+// reporting for the C ABI, CUDA error checks, device buffers, TMA descriptor encoding.
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <string>
+
+#include "../../include/b200_retrieval.h"
+
+namespace b200 {
+
+void set_error(const char* fmt, ...);
+const char* get_error();
+
+#define B200_FAIL(code, ...)        \
+  do {                              \
+    ::b200::set_error(__VA_ARGS__); \
+    return (code);                  \
+  } while (0)
+
+#define B200_CUDA(expr)                                                                          \
+  do {                                                                                           \
+    cudaError_t _e = (expr);                                                                     \
+    if (_e != cudaSuccess) {                                                                     \
+      ::b200::set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, __LINE__); \
+      return _e == cudaErrorMemoryAllocation ? B200_ERR_NOMEM : B200_ERR_CUDA;                   \
+    }                                                                                            \
+  } while (0)
+
+#define B200_TRY(expr)          \
+  do {                          \
+    int _rc = (expr);           \
+    if (_rc != B200_OK) return _rc; \
+  } while (0)
+
+// Makes `device` current for the scope of a call and restores the caller's device afterwards.
+struct DeviceGuard {
+  int prev = -1;
+  bool ok = false;
+  explicit DeviceGuard(int device) {
+    if (cudaGetDevice(&prev) != cudaSuccess) prev = -1;
+    ok = cudaSetDevice(device) == cudaSuccess;
+  }
+  ~DeviceGuard() {
+    if (prev >= 0) cudaSetDevice(prev);
+  }
+};
+
+// Owning device allocation that can grow (contents preserved up to `keep` bytes).
+struct DevBuf {
+  void* p = nullptr;
+  size_t bytes = 0;
+  int alloc(size_t n) {
+    release();
+    if (n == 0) return B200_OK;
+    B200_CUDA(cudaMalloc(&p, n));
+    bytes = n;
+    return B200_OK;
+  }
+  int grow(size_t n, size_t keep, cudaStream_t st) {
+    if (n <= bytes) return B200_OK;
+    void* np = nullptr;
+    B200_CUDA(cudaMalloc(&np, n));
+    if (p && keep) {
+      cudaError_t e = cudaMemcpyAsync(np, p, keep, cudaMemcpyDeviceToDevice, st);
+      if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+      if (e != cudaSuccess) {
+        cudaFree(np);
+        B200_FAIL(B200_ERR_CUDA, "device buffer growth copy failed: %s", cudaGetErrorString(e));
+      }
+    }
+    if (p) cudaFree(p);
+    p = np;
+    bytes = n;
+    return B200_OK;
+  }
+  void release() {
+    if (p) cudaFree(p);
+    p = nullptr;
+    bytes = 0;
+  }
+  ~DevBuf() { release(); }
+  DevBuf() = default;
+  DevBuf(const DevBuf&) = delete;
+  DevBuf& operator=(const DevBuf&) = delete;
+  template <typename T>
+  T* as() const { return reinterpret_cast<T*>(p); }
+};
+
+// 2-D bf16 row-major tensor [rows, cols] -> TMA descriptor with a {box_cols, box_rows} box and
+// 128-byte swizzle (box_cols must be 64 bf16 = 128 bytes).  Out-of-bounds elements read as zero.
+int make_tma_2d_bf16(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint32_t box_rows,
+                     uint32_t box_cols);
+
+int check_device_is_sm100(int device);
+
+}  // namespace b200

@@ -1,0 +1,444 @@
+// index.cu -- host side of the vector index behind the C ABI (include/b200_retrieval.h):
+// storage, ingest, search orchestration, compaction.  Device code is in search_kernels.cuh.
+//
+// Replaces the storage + arithmetic of InMemoryVectorStore
+// (adapters/copilot_vectorstore/copilot_vectorstore/inmemory.py:14-178); ids, metadata and the
+// Python exception contract live in the wrapper (vectorstore/store.py).
+//
+// Data layout in HBM (one index = one GPU's shard):
+//   search  bf16 [capacity, dpad]  unit-normalised rows, dpad = dim rounded up to 64; the operand
+//                                  the tcgen05 tiles stream through TMA (768 B/row at dim 384)
+//   master  fp32|bf16 [capacity, dim]  the caller's rows, untouched: SearchResult.vector and the
+//                                  exact fp32 rescoring of the KP survivors per query
+//   cand_*  [nq, nsplit, KP]       per-split candidate lists (scratch between K8 and K9)
+#include <algorithm>
+#include <vector>
+
+#include "host_util.h"
+#include "search_kernels.cuh"
+
+namespace b200 {
+
+// ------------------------------------------------------------------------------------------
+// error + driver plumbing (shared with encoder.cu through host_util.h)
+// ------------------------------------------------------------------------------------------
+static thread_local char g_err[1024] = "";
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+const char* get_error() { return g_err; }
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn encode_tiled_fn() {
+  static EncodeTiledFn fn = []() -> EncodeTiledFn {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) != cudaSuccess ||
+        qres != cudaDriverEntryPointSuccess)
+      return nullptr;
+    return reinterpret_cast<EncodeTiledFn>(p);
+  }();
+  return fn;
+}
+
+int make_tma_2d_bf16(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint32_t box_rows,
+                     uint32_t box_cols) {
+  EncodeTiledFn fn = encode_tiled_fn();
+  if (!fn) B200_FAIL(B200_ERR_CUDA, "cuTensorMapEncodeTiled is not available from the CUDA driver");
+  if (box_cols * 2 != 128 || box_rows > 256) B200_FAIL(B200_ERR_INVALID, "bad TMA box %u x %u", box_rows, box_cols);
+  cuuint64_t gdim[2] = {cols, rows};
+  cuuint64_t gstride[1] = {cols * 2};
+  cuuint32_t box[2] = {box_cols, box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), gdim, gstride, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS)
+    B200_FAIL(B200_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d (rows %llu cols %llu)", (int)r,
+              (unsigned long long)rows, (unsigned long long)cols);
+  return B200_OK;
+}
+
+int check_device_is_sm100(int device) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess || n == 0) {
+    cudaGetLastError();
+    B200_FAIL(B200_ERR_CUDA, "no CUDA device is visible; this library has no CPU fallback");
+  }
+  if (device < 0 || device >= n) B200_FAIL(B200_ERR_INVALID, "device %d out of range (0..%d)", device, n - 1);
+  int major = 0;
+  B200_CUDA(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, device));
+  if (major != 10)
+    B200_FAIL(B200_ERR_UNSUPPORTED, "device %d has compute capability %d.x; the kernels are sm_100a only", device,
+              major);
+  return B200_OK;
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+struct b200_index {
+  int dim = 0, dpad = 0, device = 0, master_dtype = 0, num_sms = 148;
+  int64_t count = 0, capacity = 0;
+  DevBuf search, master, stage, q_bf16, q_f32, cand_s, cand_i, out_ids, out_scores, tmp;
+  std::mutex mu;
+  size_t master_elt() const { return master_dtype == B200_INDEX_MASTER_BF16 ? 2 : 4; }
+};
+
+static constexpr int64_t kMaxRows = (int64_t)1 << 31;  // row ids are uint32 on the device, 2^32-1 is "no row"
+static constexpr int kMaxQueryChunk = 8192;
+static constexpr int kMaxCandPerQuery = 8192;
+
+static int index_reserve_locked(b200_index* ix, int64_t cap, cudaStream_t st) {
+  if (cap <= ix->capacity) return B200_OK;
+  if (cap > kMaxRows) B200_FAIL(B200_ERR_UNSUPPORTED, "index capacity %lld exceeds %lld rows per GPU", (long long)cap, (long long)kMaxRows);
+  int64_t want = std::max<int64_t>(cap, std::min<int64_t>(kMaxRows, ix->capacity + ix->capacity / 2));
+  want = (want + 255) / 256 * 256;
+  B200_TRY(ix->search.grow((size_t)want * ix->dpad * 2, (size_t)ix->count * ix->dpad * 2, st));
+  B200_TRY(ix->master.grow((size_t)want * ix->dim * ix->master_elt(), (size_t)ix->count * ix->dim * ix->master_elt(), st));
+  ix->capacity = want;
+  return B200_OK;
+}
+
+template <int BLOCK_N, int KP>
+static int launch_sim(b200_index* ix, int nq, int nqt, const CUtensorMap& map_q, cudaStream_t st, int* nsplit_out) {
+  const int kc = ix->dpad / SIM_BLOCK_K;
+  const size_t a_bytes = (size_t)kc * SIM_A_CHUNK_BYTES;
+  const size_t list_bytes = (size_t)SIM_BLOCK_M * (KP + 1) * 8;
+  const size_t stage_bytes = (size_t)BLOCK_N * SIM_BLOCK_K * 2;
+  const size_t fixed = 1024 + a_bytes + list_bytes + 256;
+  const size_t max_smem = 232448;  // 227 KB opt-in limit per CTA
+  if (fixed + 2 * stage_bytes > max_smem)
+    B200_FAIL(B200_ERR_UNSUPPORTED, "dimension %d needs %zu bytes of shared memory for the query tile", ix->dim, fixed);
+  int nstage = (int)std::min<size_t>(8, (max_smem - fixed) / stage_bytes);
+  const size_t smem = fixed + (size_t)nstage * stage_bytes;
+
+  const uint32_t n_rows = (uint32_t)ix->count;
+  const uint32_t total_tiles = (n_rows + BLOCK_N - 1) / BLOCK_N;
+  // Split the corpus so that (query tiles x splits) fills whole waves of SMs.  Cost model: every
+  // CTA walks tiles_per_split tiles plus a fixed prologue worth ~2 tiles (query-tile load, TMEM
+  // allocation, list write-out); waves run back to back.
+  const int max_split = std::max(1, std::min<int>((int)std::min<uint32_t>(total_tiles, 65535u), kMaxCandPerQuery / KP));
+  int best = 1;
+  double best_cost = 1e300;
+  for (int w = 1; w <= 12; ++w) {
+    int ns = std::min(max_split, std::max(1, (ix->num_sms * w) / nqt));
+    const uint32_t t = (total_tiles + ns - 1) / ns;
+    ns = (int)((total_tiles + t - 1) / t);
+    if (w > 1 && t < 8) break;
+    const long items = (long)ns * nqt;
+    const long waves = (items + ix->num_sms - 1) / ix->num_sms;
+    const double cost = (double)waves * ((double)t + 2.0);
+    if (cost < best_cost * 0.995) { best_cost = cost; best = ns; }
+  }
+  const int nsplit = best;
+  const uint32_t tps = (total_tiles + nsplit - 1) / nsplit;
+
+  const size_t cand_n = (size_t)nqt * SIM_BLOCK_M * nsplit * KP;
+  B200_TRY(ix->cand_s.grow(cand_n * 4, 0, st));
+  B200_TRY(ix->cand_i.grow(cand_n * 4, 0, st));
+
+  CUtensorMap map_c;
+  B200_TRY(make_tma_2d_bf16(&map_c, ix->search.p, (uint64_t)ix->count, (uint64_t)ix->dpad, BLOCK_N, SIM_BLOCK_K));
+
+  SimParams p;
+  p.nq = nq; p.kc = kc; p.nstage = nstage; p.n_rows = n_rows; p.tiles_per_split = tps; p.nsplit = nsplit;
+  p.cand_s = ix->cand_s.as<float>(); p.cand_i = ix->cand_i.as<uint32_t>();
+  auto kern = sim_topk_kernel<BLOCK_N, KP>;
+  B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  kern<<<dim3(nqt, nsplit), SIM_THREADS, smem, st>>>(map_q, map_c, p);
+  B200_CUDA(cudaGetLastError());
+  *nsplit_out = nsplit;
+  return B200_OK;
+}
+
+static int search_chunk(b200_index* ix, const void* q_dev, int q_dtype, int nq, int k, int kp, int64_t id_base,
+                        int64_t* ids_dev, float* sc_dev, cudaStream_t st) {
+  const int nqt = (nq + SIM_BLOCK_M - 1) / SIM_BLOCK_M;
+  const int nq_pad = nqt * SIM_BLOCK_M;
+  B200_TRY(ix->q_bf16.grow((size_t)nq_pad * ix->dpad * 2, 0, st));
+  B200_TRY(ix->q_f32.grow((size_t)nq * ix->dim * 4, 0, st));
+  const int wpb = 8;
+  if (q_dtype == 0)
+    prep_queries_kernel<float><<<(nq_pad + wpb - 1) / wpb, wpb * 32, 0, st>>>(
+        (const float*)q_dev, nq, nq_pad, ix->dim, ix->dpad, ix->q_bf16.as<__nv_bfloat16>(), ix->q_f32.as<float>());
+  else
+    prep_queries_kernel<__nv_bfloat16><<<(nq_pad + wpb - 1) / wpb, wpb * 32, 0, st>>>(
+        (const __nv_bfloat16*)q_dev, nq, nq_pad, ix->dim, ix->dpad, ix->q_bf16.as<__nv_bfloat16>(), ix->q_f32.as<float>());
+  B200_CUDA(cudaGetLastError());
+
+  CUtensorMap map_q;
+  B200_TRY(make_tma_2d_bf16(&map_q, ix->q_bf16.p, (uint64_t)nq_pad, (uint64_t)ix->dpad, SIM_BLOCK_M, SIM_BLOCK_K));
+  int nsplit = 0;
+  if (kp == 16) B200_TRY((launch_sim<256, 16>(ix, nq, nqt, map_q, st, &nsplit)));
+  else if (kp == 32) B200_TRY((launch_sim<128, 32>(ix, nq, nqt, map_q, st, &nsplit)));
+  else B200_TRY((launch_sim<128, 64>(ix, nq, nqt, map_q, st, &nsplit)));
+
+  MergeParams m;
+  m.nq = nq; m.nsplit = nsplit; m.kp = kp; m.k = k; m.d = ix->dim;
+  int pow2 = 64;
+  while (pow2 < nsplit * kp) pow2 <<= 1;
+  m.ncand_pow2 = pow2;
+  m.n_rows = (uint32_t)ix->count; m.id_base = id_base;
+  m.cand_s = ix->cand_s.as<float>(); m.cand_i = ix->cand_i.as<uint32_t>();
+  m.q_f32 = ix->q_f32.as<float>(); m.master = ix->master.p;
+  m.master_is_bf16 = ix->master_dtype == B200_INDEX_MASTER_BF16;
+  m.out_ids = ids_dev; m.out_scores = sc_dev; m.out_margin = nullptr;
+  const size_t msmem = (size_t)pow2 * 8 + (size_t)((ix->dim + 1) & ~1) * 4 + 64 * 8;
+  B200_CUDA(cudaFuncSetAttribute(merge_rescore_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)msmem));
+  merge_rescore_kernel<<<nq, 256, msmem, st>>>(m);
+  B200_CUDA(cudaGetLastError());
+  return B200_OK;
+}
+
+// move nrows rows of row_bytes each from src_row to dst_row (dst_row < src_row) inside one buffer
+static int move_rows_down(uint8_t* base, size_t row_bytes, int64_t dst_row, int64_t src_row, int64_t nrows,
+                          DevBuf& tmp, cudaStream_t st) {
+  if (nrows <= 0 || dst_row == src_row) return B200_OK;
+  const int64_t shift = src_row - dst_row;
+  if (shift >= nrows) {
+    B200_CUDA(cudaMemcpyAsync(base + dst_row * row_bytes, base + src_row * row_bytes, (size_t)nrows * row_bytes,
+                              cudaMemcpyDeviceToDevice, st));
+    return B200_OK;
+  }
+  const int64_t piece = std::max<int64_t>(shift, std::min<int64_t>(nrows, (int64_t)((64u << 20) / row_bytes)));
+  if (piece > shift) B200_TRY(tmp.grow((size_t)piece * row_bytes, 0, st));
+  for (int64_t o = 0; o < nrows; o += piece) {
+    const int64_t m = std::min(piece, nrows - o);
+    uint8_t* s = base + (src_row + o) * row_bytes;
+    uint8_t* d = base + (dst_row + o) * row_bytes;
+    if (m <= shift) {
+      B200_CUDA(cudaMemcpyAsync(d, s, (size_t)m * row_bytes, cudaMemcpyDeviceToDevice, st));
+    } else {
+      B200_CUDA(cudaMemcpyAsync(tmp.p, s, (size_t)m * row_bytes, cudaMemcpyDeviceToDevice, st));
+      B200_CUDA(cudaMemcpyAsync(d, tmp.p, (size_t)m * row_bytes, cudaMemcpyDeviceToDevice, st));
+    }
+  }
+  return B200_OK;
+}
+
+extern "C" {
+
+const char* b200_last_error(void) { return b200::get_error(); }
+int b200_version(void) { return 100; }
+
+int b200_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) {
+    cudaGetLastError();
+    return 0;
+  }
+  int ok = 0;
+  for (int d = 0; d < n; ++d) {
+    int major = 0;
+    if (cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, d) == cudaSuccess && major == 10) ++ok;
+  }
+  return ok;
+}
+
+int b200_index_create(int dim, int64_t capacity, int device, int master_dtype, b200_index_t** out) {
+  if (!out) B200_FAIL(B200_ERR_INVALID, "out is NULL");
+  *out = nullptr;
+  if (dim <= 0) B200_FAIL(B200_ERR_INVALID, "dim must be positive, got %d", dim);
+  if (dim > 384) B200_FAIL(B200_ERR_UNSUPPORTED, "dim %d > 384: the resident-query-tile kernel covers dimensions up to 384", dim);
+  if (master_dtype != B200_INDEX_MASTER_F32 && master_dtype != B200_INDEX_MASTER_BF16)
+    B200_FAIL(B200_ERR_INVALID, "unknown master_dtype %d", master_dtype);
+  B200_TRY(check_device_is_sm100(device));
+  DeviceGuard g(device);
+  if (!g.ok) B200_FAIL(B200_ERR_CUDA, "cudaSetDevice(%d) failed", device);
+  b200_index* ix = new b200_index();
+  ix->dim = dim;
+  ix->dpad = (dim + 63) / 64 * 64;
+  ix->device = device;
+  ix->master_dtype = master_dtype;
+  cudaDeviceGetAttribute(&ix->num_sms, cudaDevAttrMultiProcessorCount, device);
+  int rc = index_reserve_locked(ix, std::max<int64_t>(capacity, 1024), 0);
+  if (rc != B200_OK) {
+    delete ix;
+    return rc;
+  }
+  *out = ix;
+  return B200_OK;
+}
+
+int b200_index_destroy(b200_index_t* ix) {
+  if (!ix) return B200_OK;
+  {
+    DeviceGuard g(ix->device);
+    cudaDeviceSynchronize();
+    delete ix;
+  }
+  return B200_OK;
+}
+
+int b200_index_clear(b200_index_t* ix) {
+  if (!ix) B200_FAIL(B200_ERR_INVALID, "index is NULL");
+  std::lock_guard<std::mutex> lk(ix->mu);
+  ix->count = 0;
+  return B200_OK;
+}
+
+int64_t b200_index_count(const b200_index_t* ix) { return ix ? ix->count : 0; }
+int b200_index_dim(const b200_index_t* ix) { return ix ? ix->dim : 0; }
+
+int b200_index_reserve(b200_index_t* ix, int64_t capacity) {
+  if (!ix) B200_FAIL(B200_ERR_INVALID, "index is NULL");
+  std::lock_guard<std::mutex> lk(ix->mu);
+  DeviceGuard g(ix->device);
+  return index_reserve_locked(ix, capacity, 0);
+}
+
+int b200_index_add(b200_index_t* ix, const void* rows, int64_t n, int rows_on_device, void* stream) {
+  if (!ix) B200_FAIL(B200_ERR_INVALID, "index is NULL");
+  if (n < 0 || (n > 0 && !rows)) B200_FAIL(B200_ERR_INVALID, "bad rows pointer / count");
+  if (n == 0) return B200_OK;
+  std::lock_guard<std::mutex> lk(ix->mu);
+  DeviceGuard g(ix->device);
+  cudaStream_t st = (cudaStream_t)stream;
+  B200_TRY(index_reserve_locked(ix, ix->count + n, st));
+  const size_t elt = ix->master_elt();
+  const void* src = rows;
+  if (!rows_on_device) {
+    B200_TRY(ix->stage.grow((size_t)n * ix->dim * elt, 0, st));
+    B200_CUDA(cudaMemcpyAsync(ix->stage.p, rows, (size_t)n * ix->dim * elt, cudaMemcpyHostToDevice, st));
+    src = ix->stage.p;
+  }
+  const int wpb = 8;
+  const unsigned grid = (unsigned)((n + wpb - 1) / wpb);
+  if (ix->master_dtype == B200_INDEX_MASTER_F32) {
+    if (ix->dim == ix->dpad && (ix->dim % 8) == 0 && ((uintptr_t)src % 16) == 0)
+      ingest_rows_f32_vec_kernel<<<grid, wpb * 32, 0, st>>>((const float*)src, n, ix->dim,
+                                                           ix->search.as<__nv_bfloat16>(), ix->count, ix->master.as<float>());
+    else
+      ingest_rows_kernel<float><<<grid, wpb * 32, 0, st>>>((const float*)src, n, ix->dim, ix->dpad,
+                                                           ix->search.as<__nv_bfloat16>(), ix->count, ix->master.as<float>());
+  } else {
+    ingest_rows_kernel<__nv_bfloat16><<<grid, wpb * 32, 0, st>>>((const __nv_bfloat16*)src, n, ix->dim, ix->dpad,
+                                                                  ix->search.as<__nv_bfloat16>(), ix->count,
+                                                                  ix->master.as<__nv_bfloat16>());
+  }
+  B200_CUDA(cudaGetLastError());
+  if (!rows_on_device) B200_CUDA(cudaStreamSynchronize(st));  // the staging buffer and the caller's rows are reusable
+  ix->count += n;
+  return B200_OK;
+}
+
+int b200_index_remove_rows(b200_index_t* ix, const int64_t* rows, int64_t n, void* stream) {
+  if (!ix) B200_FAIL(B200_ERR_INVALID, "index is NULL");
+  if (n < 0 || (n > 0 && !rows)) B200_FAIL(B200_ERR_INVALID, "bad rows pointer / count");
+  if (n == 0) return B200_OK;
+  std::lock_guard<std::mutex> lk(ix->mu);
+  for (int64_t i = 0; i < n; ++i) {
+    if (rows[i] < 0 || rows[i] >= ix->count) B200_FAIL(B200_ERR_NOT_FOUND, "row %lld not found (count %lld)", (long long)rows[i], (long long)ix->count);
+    if (i > 0 && rows[i] <= rows[i - 1]) B200_FAIL(B200_ERR_INVALID, "rows to remove must be ascending and unique");
+  }
+  DeviceGuard g(ix->device);
+  cudaStream_t st = (cudaStream_t)stream;
+  const size_t sb = (size_t)ix->dpad * 2, mb = (size_t)ix->dim * ix->master_elt();
+  int64_t dst = rows[0];
+  for (int64_t i = 0; i < n; ++i) {
+    const int64_t seg0 = rows[i] + 1;
+    const int64_t seg1 = (i + 1 < n) ? rows[i + 1] : ix->count;
+    B200_TRY(move_rows_down(ix->search.as<uint8_t>(), sb, dst, seg0, seg1 - seg0, ix->tmp, st));
+    B200_TRY(move_rows_down(ix->master.as<uint8_t>(), mb, dst, seg0, seg1 - seg0, ix->tmp, st));
+    dst += seg1 - seg0;
+  }
+  ix->count -= n;
+  return B200_OK;
+}
+
+int b200_index_get_rows(b200_index_t* ix, const int64_t* rows, int64_t n, float* out, int out_on_device, void* stream) {
+  if (!ix) B200_FAIL(B200_ERR_INVALID, "index is NULL");
+  if (n < 0 || (n > 0 && (!rows || !out))) B200_FAIL(B200_ERR_INVALID, "bad pointer / count");
+  if (n == 0) return B200_OK;
+  std::lock_guard<std::mutex> lk(ix->mu);
+  for (int64_t i = 0; i < n; ++i)
+    if (rows[i] < 0 || rows[i] >= ix->count) B200_FAIL(B200_ERR_NOT_FOUND, "row %lld not found (count %lld)", (long long)rows[i], (long long)ix->count);
+  DeviceGuard g(ix->device);
+  cudaStream_t st = (cudaStream_t)stream;
+  const size_t idx_bytes = ((size_t)n * 8 + 255) / 256 * 256;
+  const size_t out_bytes = (size_t)n * ix->dim * 4;
+  B200_TRY(ix->stage.grow(idx_bytes + (out_on_device ? 0 : out_bytes), 0, st));
+  int64_t* d_rows = ix->stage.as<int64_t>();
+  float* d_out = out_on_device ? out : reinterpret_cast<float*>(ix->stage.as<uint8_t>() + idx_bytes);
+  B200_CUDA(cudaMemcpyAsync(d_rows, rows, (size_t)n * 8, cudaMemcpyHostToDevice, st));
+  if (ix->master_dtype == B200_INDEX_MASTER_F32)
+    gather_rows_kernel<float, float><<<(unsigned)n, 128, 0, st>>>(ix->master.as<float>(), d_rows, n, ix->dim, d_out);
+  else
+    gather_rows_kernel<__nv_bfloat16, float><<<(unsigned)n, 128, 0, st>>>(ix->master.as<__nv_bfloat16>(), d_rows, n, ix->dim, d_out);
+  B200_CUDA(cudaGetLastError());
+  if (!out_on_device) B200_CUDA(cudaMemcpyAsync(out, d_out, out_bytes, cudaMemcpyDeviceToHost, st));
+  B200_CUDA(cudaStreamSynchronize(st));
+  return B200_OK;
+}
+
+int b200_index_search(b200_index_t* ix, const void* queries, int q_dtype, int queries_on_device, int64_t nq, int k,
+                      int64_t id_base, int64_t* ids, float* scores, int out_on_device, void* stream) {
+  if (!ix) B200_FAIL(B200_ERR_INVALID, "index is NULL");
+  if (nq < 0 || k < 0) B200_FAIL(B200_ERR_INVALID, "negative nq / k");
+  if (nq == 0 || k == 0) return B200_OK;
+  if (!queries || !ids || !scores) B200_FAIL(B200_ERR_INVALID, "NULL buffer");
+  if (q_dtype != 0 && q_dtype != 1) B200_FAIL(B200_ERR_INVALID, "q_dtype must be 0 (fp32) or 1 (bf16)");
+  if (k > 48) B200_FAIL(B200_ERR_UNSUPPORTED, "k=%d: the fused select keeps at most 64 candidates per query (k <= 48)", k);
+  const int kp = k <= 10 ? 16 : (k <= 24 ? 32 : 64);
+  std::lock_guard<std::mutex> lk(ix->mu);
+  DeviceGuard g(ix->device);
+  cudaStream_t st = (cudaStream_t)stream;
+  const size_t qelt = q_dtype == 0 ? 4 : 2;
+
+  int64_t* d_ids = ids;
+  float* d_sc = scores;
+  if (!out_on_device) {
+    B200_TRY(ix->out_ids.grow((size_t)nq * k * 8, 0, st));
+    B200_TRY(ix->out_scores.grow((size_t)nq * k * 4, 0, st));
+    d_ids = ix->out_ids.as<int64_t>();
+    d_sc = ix->out_scores.as<float>();
+  }
+  if (ix->count == 0) {  // inmemory.py:93-94: empty store -> no results
+    B200_CUDA(cudaMemsetAsync(d_ids, 0xFF, (size_t)nq * k * 8, st));
+    B200_CUDA(cudaMemsetAsync(d_sc, 0, (size_t)nq * k * 4, st));
+  } else {
+    const uint8_t* q_dev = (const uint8_t*)queries;
+    if (!queries_on_device) {
+      B200_TRY(ix->stage.grow((size_t)nq * ix->dim * qelt, 0, st));
+      B200_CUDA(cudaMemcpyAsync(ix->stage.p, queries, (size_t)nq * ix->dim * qelt, cudaMemcpyHostToDevice, st));
+      q_dev = ix->stage.as<uint8_t>();
+    }
+    for (int64_t q0 = 0; q0 < nq; q0 += kMaxQueryChunk) {
+      const int n = (int)std::min<int64_t>(kMaxQueryChunk, nq - q0);
+      B200_TRY(search_chunk(ix, q_dev + (size_t)q0 * ix->dim * qelt, q_dtype, n, k, kp, id_base, d_ids + q0 * k,
+                            d_sc + q0 * k, st));
+    }
+  }
+  if (!out_on_device) {
+    B200_CUDA(cudaMemcpyAsync(ids, d_ids, (size_t)nq * k * 8, cudaMemcpyDeviceToHost, st));
+    B200_CUDA(cudaMemcpyAsync(scores, d_sc, (size_t)nq * k * 4, cudaMemcpyDeviceToHost, st));
+    B200_CUDA(cudaStreamSynchronize(st));
+  }
+  return B200_OK;
+}
+
+int b200_merge_topk(const int64_t* ids_in, const float* scores_in, int64_t nq, int nlists, int k_in, int k_out,
+                    int64_t* ids_out, float* scores_out, int device, void* stream) {
+  if (nq < 0 || nlists <= 0 || k_in <= 0 || k_out <= 0) B200_FAIL(B200_ERR_INVALID, "bad merge shape");
+  if (nq == 0) return B200_OK;
+  if (!ids_in || !scores_in || !ids_out || !scores_out) B200_FAIL(B200_ERR_INVALID, "NULL buffer");
+  if ((int64_t)nlists * k_in > 4096) B200_FAIL(B200_ERR_UNSUPPORTED, "nlists*k_in = %lld > 4096", (long long)nlists * k_in);
+  DeviceGuard g(device);
+  if (!g.ok) B200_FAIL(B200_ERR_CUDA, "cudaSetDevice(%d) failed", device);
+  const int wpb = 4;
+  merge_lists_kernel<<<(unsigned)((nq + wpb - 1) / wpb), wpb * 32, 0, (cudaStream_t)stream>>>(
+      ids_in, scores_in, (int)nq, nlists, k_in, k_out, ids_out, scores_out);
+  B200_CUDA(cudaGetLastError());
+  return B200_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,500 @@
+// search_kernels.cuh -- device code for the cosine top-k path.
+//
+//   ingest_rows_kernel   K11  raw rows -> unit-normalised bf16 search copy (+ master copy)
+//   prep_queries_kernel        raw queries -> zero-padded bf16 tile operand + fp32 copy
+//   sim_topk_kernel      K8   Q x C^T on tcgen05 (TMA-fed, TMEM accumulators) with the top-KP
+//                             select fused into the TMEM drain: scores never reach HBM
+//   merge_rescore_kernel K9   per query: merge the per-split candidate lists, rescore the KP
+//                             survivors with the reference's fp32 arithmetic in the canonical
+//                             summation order (oracle/search_oracle.c), emit top-k
+//
+// Reference semantics being reproduced: InMemoryVectorStore.query,
+// adapters/copilot_vectorstore/copilot_vectorstore/inmemory.py:96-119.
+#pragma once
+#include "common.cuh"
+
+namespace b200 {
+
+constexpr int SIM_BLOCK_M = 128;   // queries per CTA = TMEM lanes
+constexpr int SIM_BLOCK_K = 64;    // bf16 elements per 128-byte swizzle row
+constexpr int SIM_THREADS = 256;   // warp 0 TMA, 1 MMA, 2 TMEM alloc, 3 idle, 4..7 drain/select
+constexpr int SIM_A_CHUNK_BYTES = SIM_BLOCK_M * SIM_BLOCK_K * 2;
+constexpr uint32_t kNoRow = 0xFFFFFFFFu;
+
+// ---------------------------------------------------------------------------------------------
+// K11: one warp per row.  search[r] = bf16( x / (||x|| + 1e-8) ), zero-padded to dpad columns.
+// The search copy only has to rank candidates; exact scores come from the master copy later, so
+// the norm here is an ordinary warp-shuffle reduction.
+// ---------------------------------------------------------------------------------------------
+template <typename TIn>
+__global__ void __launch_bounds__(256) ingest_rows_kernel(const TIn* __restrict__ in, int64_t n, int d, int dpad,
+                                                          __nv_bfloat16* __restrict__ search, int64_t row0,
+                                                          TIn* __restrict__ master) {
+  const int64_t r = (int64_t)blockIdx.x * (blockDim.x / kWarp) + (threadIdx.x / kWarp);
+  if (r >= n) return;
+  const int lane = threadIdx.x & 31;
+  const TIn* src = in + r * (int64_t)d;
+  float ss = 0.f;
+  for (int i = lane; i < d; i += kWarp) {
+    float x = static_cast<float>(src[i]);
+    ss = fmaf(x, x, ss);
+  }
+  ss = warp_sum(ss);
+  const float inv = 1.0f / (sqrtf(ss) + 1e-8f);
+  __nv_bfloat16* dst = search + (row0 + r) * (int64_t)dpad;
+  TIn* mdst = master ? master + (row0 + r) * (int64_t)d : nullptr;
+  for (int i = lane; i < dpad; i += kWarp) {
+    float x = (i < d) ? static_cast<float>(src[i]) : 0.f;
+    dst[i] = __float2bfloat16_rn(x * inv);
+    if (mdst && i < d) mdst[i] = src[i];
+  }
+}
+
+// Vectorised K11 for d % 8 == 0 and d == dpad (the 384/768-d production shapes): 16-byte loads
+// and stores, one warp per row, rows of 384 fp32 = 3 x float4 per lane.
+__global__ void __launch_bounds__(256) ingest_rows_f32_vec_kernel(const float* __restrict__ in, int64_t n, int d,
+                                                                  __nv_bfloat16* __restrict__ search, int64_t row0,
+                                                                  float* __restrict__ master) {
+  const int64_t r = (int64_t)blockIdx.x * (blockDim.x / kWarp) + (threadIdx.x / kWarp);
+  if (r >= n) return;
+  const int lane = threadIdx.x & 31;
+  const float4* src = reinterpret_cast<const float4*>(in + r * (int64_t)d);
+  const int nv = d >> 2;
+  float ss = 0.f;
+  for (int i = lane; i < nv; i += kWarp) {
+    float4 x = __ldg(src + i);
+    ss = fmaf(x.x, x.x, ss); ss = fmaf(x.y, x.y, ss); ss = fmaf(x.z, x.z, ss); ss = fmaf(x.w, x.w, ss);
+  }
+  ss = warp_sum(ss);
+  const float inv = 1.0f / (sqrtf(ss) + 1e-8f);
+  uint2* dst = reinterpret_cast<uint2*>(search + (row0 + r) * (int64_t)d);
+  float4* mdst = master ? reinterpret_cast<float4*>(master + (row0 + r) * (int64_t)d) : nullptr;
+  for (int i = lane; i < nv; i += kWarp) {
+    float4 x = __ldg(src + i);
+    __nv_bfloat162 lo = __floats2bfloat162_rn(x.x * inv, x.y * inv);
+    __nv_bfloat162 hi = __floats2bfloat162_rn(x.z * inv, x.w * inv);
+    uint2 o;
+    o.x = *reinterpret_cast<uint32_t*>(&lo);
+    o.y = *reinterpret_cast<uint32_t*>(&hi);
+    dst[i] = o;
+    if (mdst) mdst[i] = x;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// queries: raw (fp32 or bf16) -> bf16 [nq_pad, dpad] tile operand (zero padded) and fp32 [nq, d]
+// for the rescoring pass.  Queries are NOT normalised for the tensor-core pass: a positive
+// per-query scale does not change that query's ranking.  They are scaled by 1/max|q| only to keep
+// bf16 conversion away from denormals for tiny-magnitude inputs.
+// ---------------------------------------------------------------------------------------------
+template <typename TIn>
+__global__ void __launch_bounds__(256) prep_queries_kernel(const TIn* __restrict__ in, int nq, int nq_pad, int d,
+                                                           int dpad, __nv_bfloat16* __restrict__ q_bf16,
+                                                           float* __restrict__ q_f32) {
+  const int r = blockIdx.x * (blockDim.x / kWarp) + (threadIdx.x / kWarp);
+  if (r >= nq_pad) return;
+  const int lane = threadIdx.x & 31;
+  __nv_bfloat16* dst = q_bf16 + (int64_t)r * dpad;
+  if (r >= nq) {
+    for (int i = lane; i < dpad; i += kWarp) dst[i] = __float2bfloat16_rn(0.f);
+    return;
+  }
+  const TIn* src = in + (int64_t)r * d;
+  float amax = 0.f;
+  for (int i = lane; i < d; i += kWarp) amax = fmaxf(amax, fabsf(static_cast<float>(src[i])));
+  amax = warp_max(amax);
+  const float sc = (amax > 0.f && amax < 1e-3f) ? (1.0f / amax) : 1.0f;
+  for (int i = lane; i < dpad; i += kWarp) {
+    float x = (i < d) ? static_cast<float>(src[i]) : 0.f;
+    dst[i] = __float2bfloat16_rn(x * sc);
+    if (i < d) q_f32[(int64_t)r * d + i] = x;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// K8: similarity tiles with fused top-KP selection.
+// ---------------------------------------------------------------------------------------------
+struct SimParams {
+  int nq;                 // valid queries
+  int kc;                 // 64-wide K chunks per row (dpad / 64), 1..6 with the query tile resident
+  int nstage;             // corpus-tile pipeline stages
+  uint32_t n_rows;        // valid corpus rows
+  uint32_t tiles_per_split;
+  int nsplit;
+  float* cand_s;          // [nq_tiles*128][nsplit][KP]
+  uint32_t* cand_i;
+};
+
+// Sorted-descending insertion into one query's candidate list (shared memory, thread-private
+// row).  Equal scores keep the earlier (lower) row first: rows are scanned in ascending order,
+// so a strict '<' on the shift is the reference's stable-sort tie rule (inmemory.py:118).
+template <int KP>
+__device__ __noinline__ float topk_insert(float* cs, uint32_t* ci, float s, uint32_t id) {
+  int j = KP - 1;
+  while (j > 0 && cs[j - 1] < s) {
+    cs[j] = cs[j - 1];
+    ci[j] = ci[j - 1];
+    --j;
+  }
+  cs[j] = s;
+  ci[j] = id;
+  return cs[KP - 1];
+}
+
+template <int BLOCK_N, int KP>
+__global__ void __launch_bounds__(SIM_THREADS, 1)
+sim_topk_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_c,
+                const SimParams p) {
+  constexpr uint32_t B_STAGE_BYTES = BLOCK_N * SIM_BLOCK_K * 2;
+  constexpr uint32_t IDESC = umma_idesc_bf16_f32(SIM_BLOCK_M, BLOCK_N);
+  constexpr uint32_t TMEM_COLS = 2 * BLOCK_N;  // two accumulator stages
+  static_assert(TMEM_COLS == 256 || TMEM_COLS == 512, "TMEM allocation must be a power of two");
+
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sA = smem;
+  uint8_t* sB = sA + (size_t)p.kc * SIM_A_CHUNK_BYTES;
+  float* cs = reinterpret_cast<float*>(sB + (size_t)p.nstage * B_STAGE_BYTES);
+  uint32_t* ci = reinterpret_cast<uint32_t*>(cs + SIM_BLOCK_M * (KP + 1));
+  uint64_t* bars = reinterpret_cast<uint64_t*>(ci + SIM_BLOCK_M * (KP + 1));
+  uint64_t* full = bars;                       // [nstage]  TMA -> MMA
+  uint64_t* empty = bars + p.nstage;           // [nstage]  MMA -> TMA
+  uint64_t* acc_full = bars + 2 * p.nstage;    // [2]       MMA -> drain
+  uint64_t* acc_empty = acc_full + 2;          // [2]       drain -> MMA
+  uint64_t* a_full = acc_empty + 2;            // [1]       query tile landed
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(a_full + 1);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int qtile = blockIdx.x;
+  const int split = blockIdx.y;
+
+  const uint32_t total_tiles = (p.n_rows + BLOCK_N - 1) / BLOCK_N;
+  const uint32_t tile0 = (uint32_t)split * p.tiles_per_split;
+  const uint32_t ntiles = tile0 < total_tiles ? min(p.tiles_per_split, total_tiles - tile0) : 0u;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&map_q);
+    tma_prefetch_desc(&map_c);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < p.nstage; ++i) {
+      mbar_init(&full[i], 1);
+      mbar_init(&empty[i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&acc_full[i], 1);
+      mbar_init(&acc_empty[i], 4);  // one arrival per drain warp
+    }
+    mbar_init(a_full, 1);
+    fence_mbar_init();
+  }
+  if (warp == 2) tmem_alloc(tmem_slot, TMEM_COLS);
+  // candidate lists start empty: -inf scores, no-row ids
+  for (int i = threadIdx.x; i < SIM_BLOCK_M * (KP + 1); i += SIM_THREADS) {
+    cs[i] = -INFINITY;
+    ci[i] = kNoRow;
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===== TMA producer =====
+    if (lane == 0 && ntiles > 0) {
+      mbar_arrive_expect_tx(a_full, (uint32_t)p.kc * SIM_A_CHUNK_BYTES);
+      for (int c = 0; c < p.kc; ++c)
+        tma_load_2d(sA + (size_t)c * SIM_A_CHUNK_BYTES, &map_q, a_full, c * SIM_BLOCK_K, qtile * SIM_BLOCK_M);
+      int s = 0;
+      uint32_t ph = 0;
+      for (uint32_t t = 0; t < ntiles; ++t) {
+        const int32_t row = (int32_t)((tile0 + t) * BLOCK_N);
+        for (int c = 0; c < p.kc; ++c) {
+          mbar_wait(&empty[s], ph ^ 1);
+          mbar_arrive_expect_tx(&full[s], B_STAGE_BYTES);
+          tma_load_2d(sB + (size_t)s * B_STAGE_BYTES, &map_c, &full[s], c * SIM_BLOCK_K, row);
+          if (++s == p.nstage) { s = 0; ph ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer (one thread) =====
+    if (lane == 0 && ntiles > 0) {
+      mbar_wait(a_full, 0);
+      tc_fence_after();
+      const uint32_t a_addr = smem_u32(sA);
+      const uint32_t b_addr = smem_u32(sB);
+      int s = 0;
+      uint32_t ph = 0;
+      for (uint32_t t = 0; t < ntiles; ++t) {
+        const uint32_t as = t & 1, aph = (t >> 1) & 1;
+        mbar_wait(&acc_empty[as], aph ^ 1);
+        tc_fence_after();
+        const uint32_t tacc = tmem_base + as * BLOCK_N;
+        for (int c = 0; c < p.kc; ++c) {
+          mbar_wait(&full[s], ph);
+          tc_fence_after();
+          const uint64_t da = umma_smem_desc_sw128(a_addr + (uint32_t)c * SIM_A_CHUNK_BYTES);
+          const uint64_t db = umma_smem_desc_sw128(b_addr + (uint32_t)s * B_STAGE_BYTES);
+#pragma unroll
+          for (int k = 0; k < SIM_BLOCK_K / 16; ++k) {
+            // +32 bytes per K=16 step inside the 128-byte swizzle row: +2 in the >>4 address field
+            umma_bf16(tacc, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), IDESC, (uint32_t)((c | k) != 0));
+          }
+          umma_commit(&empty[s]);  // stage reusable once these MMAs have read it
+          if (++s == p.nstage) { s = 0; ph ^= 1; }
+        }
+        umma_commit(&acc_full[as]);  // accumulator tile complete
+      }
+    }
+  } else if (warp >= 4) {
+    // ===== drain + select: thread owns one query (one TMEM lane) =====
+    const int wq = warp - 4;                   // TMEM lane group this warp may read
+    const int row = wq * 32 + lane;
+    const int qg = qtile * SIM_BLOCK_M + row;
+    float* my_s = cs + row * (KP + 1);
+    uint32_t* my_i = ci + row * (KP + 1);
+    float thr = (qg < p.nq) ? -INFINITY : INFINITY;  // padded query rows never insert
+    for (uint32_t t = 0; t < ntiles; ++t) {
+      const uint32_t as = t & 1, aph = (t >> 1) & 1;
+      mbar_wait(&acc_full[as], aph);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + ((uint32_t)(wq * 32) << 16) + as * BLOCK_N;
+      const uint32_t col0 = (tile0 + t) * BLOCK_N;
+#pragma unroll 1
+      for (int c = 0; c < BLOCK_N / 32; ++c) {
+        uint32_t v[32];
+        tmem_ld32(taddr + c * 32, v);
+        tmem_ld_wait();
+        float m = __uint_as_float(v[0]);
+#pragma unroll
+        for (int j = 1; j < 32; ++j) m = fmaxf(m, __uint_as_float(v[j]));
+        if (m > thr) {
+          const uint32_t base = col0 + c * 32;
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            const float s = __uint_as_float(v[j]);
+            if (s > thr && base + j < p.n_rows) thr = topk_insert<KP>(my_s, my_i, s, base + j);
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&acc_empty[as]);
+    }
+    // this split's candidates for this query
+    if (qg < p.nq) {
+      const size_t o = ((size_t)qg * p.nsplit + split) * KP;
+#pragma unroll 4
+      for (int j = 0; j < KP; ++j) {
+        p.cand_s[o + j] = my_s[j];
+        p.cand_i[o + j] = my_i[j];
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, TMEM_COLS);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// canonical fp32 arithmetic shared with oracle/search_oracle.c (bit-for-bit):
+//   element i accumulates into partial (i & 31) by fused multiply-add, ascending i; partials are
+//   folded 16, 8, 4, 2, 1.  One warp; every lane returns the same value.
+// ---------------------------------------------------------------------------------------------
+template <typename TA>
+B200_DEVINL float canon_dot_self(const TA* __restrict__ x, int d, int lane) {
+  float p = 0.f;
+  for (int i = lane; i < d; i += kWarp) {
+    const float v = static_cast<float>(x[i]);
+    p = __fmaf_rn(v, v, p);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) p = __fadd_rn(p, __shfl_xor_sync(0xffffffffu, p, o));
+  return p;
+}
+
+// score of raw row v against the already-normalised query qh (shared memory, fp32)
+template <typename TV>
+B200_DEVINL float canon_score(const float* __restrict__ qh, const TV* __restrict__ v, int d, int lane) {
+  const float den = __fadd_rn(__fsqrt_rn(canon_dot_self(v, d, lane)), 1e-8f);
+  float p = 0.f;
+  for (int i = lane; i < d; i += kWarp) {
+    const float vh = __fdiv_rn(static_cast<float>(v[i]), den);
+    p = __fmaf_rn(qh[i], vh, p);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) p = __fadd_rn(p, __shfl_xor_sync(0xffffffffu, p, o));
+  return p;
+}
+
+B200_DEVINL uint64_t pack_key(float s, uint32_t id) {
+  return ((uint64_t)f32_orderable(s) << 32) | (uint64_t)(~id);
+}
+
+// descending bitonic sort of n (power of two) 64-bit keys in shared memory, whole CTA
+B200_DEVINL void bitonic_sort_desc(uint64_t* keys, int n) {
+  for (int k = 2; k <= n; k <<= 1) {
+    for (int j = k >> 1; j > 0; j >>= 1) {
+      for (int i = threadIdx.x; i < n; i += blockDim.x) {
+        const int ixj = i ^ j;
+        if (ixj > i) {
+          const uint64_t a = keys[i], b = keys[ixj];
+          const bool desc = (i & k) == 0;
+          if (desc ? (a < b) : (a > b)) {
+            keys[i] = b;
+            keys[ixj] = a;
+          }
+        }
+      }
+      __syncthreads();
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// K9: one CTA per query.
+//   1. gather nsplit*KP (approx score, row) candidates as 64-bit keys (score desc, row asc),
+//      bitonic-sort, keep the best KP
+//   2. rescore those KP rows from the master copy with the reference arithmetic (canonical order)
+//   3. order by (exact score desc, row asc) and emit k results: ids are id_base + row, -1 padded
+// ---------------------------------------------------------------------------------------------
+struct MergeParams {
+  int nq, nsplit, kp, k, d;
+  int ncand_pow2;
+  uint32_t n_rows;
+  int64_t id_base;
+  const float* cand_s;
+  const uint32_t* cand_i;
+  const float* q_f32;       // [nq, d] raw queries
+  const void* master;       // [n_rows, d] raw rows, fp32 or bf16
+  int master_is_bf16;
+  int64_t* out_ids;         // [nq, k]
+  float* out_scores;        // [nq, k]
+  float* out_margin;        // [nq] optional: approx score of the last kept candidate (diagnostics)
+};
+
+__global__ void __launch_bounds__(256) merge_rescore_kernel(const MergeParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint64_t* keys = reinterpret_cast<uint64_t*>(smem_raw);
+  float* qh = reinterpret_cast<float*>(keys + p.ncand_pow2);  // [d]
+  uint64_t* fin = reinterpret_cast<uint64_t*>(qh + ((p.d + 1) & ~1));  // [64]
+  __shared__ float s_den;
+
+  const int q = blockIdx.x;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
+  const int ncand = p.nsplit * p.kp;
+  const size_t o = (size_t)q * ncand;
+  for (int i = threadIdx.x; i < p.ncand_pow2; i += blockDim.x) {
+    uint64_t key = 0;
+    if (i < ncand) {
+      const uint32_t id = p.cand_i[o + i];
+      if (id != kNoRow) key = pack_key(p.cand_s[o + i], id);
+    }
+    keys[i] = key;
+  }
+  // q_hat = q / (||q|| + 1e-8)   (inmemory.py:108)
+  const float* qraw = p.q_f32 + (size_t)q * p.d;
+  if (warp == 0) {
+    const float den = __fadd_rn(__fsqrt_rn(canon_dot_self(qraw, p.d, lane)), 1e-8f);
+    if (lane == 0) s_den = den;
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < p.d; i += blockDim.x) qh[i] = __fdiv_rn(qraw[i], s_den);
+  for (int i = threadIdx.x; i < 64; i += blockDim.x) fin[i] = 0;
+  bitonic_sort_desc(keys, p.ncand_pow2);  // ends with __syncthreads
+
+  for (int c = warp; c < p.kp; c += nwarp) {
+    const uint64_t key = keys[c];
+    if (key == 0) continue;
+    const uint32_t id = ~(uint32_t)(key & 0xFFFFFFFFu);
+    float s;
+    if (p.master_is_bf16)
+      s = canon_score(qh, reinterpret_cast<const __nv_bfloat16*>(p.master) + (size_t)id * p.d, p.d, lane);
+    else
+      s = canon_score(qh, reinterpret_cast<const float*>(p.master) + (size_t)id * p.d, p.d, lane);
+    if (lane == 0) fin[c] = pack_key(s, id);
+  }
+  __syncthreads();
+  if (p.out_margin && threadIdx.x == 0) {
+    const uint64_t last = keys[p.kp - 1];
+    p.out_margin[q] = last ? orderable_f32((uint32_t)(last >> 32)) : -INFINITY;
+  }
+  bitonic_sort_desc(fin, 64);
+  for (int j = threadIdx.x; j < p.k; j += blockDim.x) {
+    const uint64_t key = (j < 64) ? fin[j] : 0;
+    if (key) {
+      p.out_ids[(size_t)q * p.k + j] = p.id_base + (int64_t)(~(uint32_t)(key & 0xFFFFFFFFu));
+      p.out_scores[(size_t)q * p.k + j] = orderable_f32((uint32_t)(key >> 32));
+    } else {
+      p.out_ids[(size_t)q * p.k + j] = -1;
+      p.out_scores[(size_t)q * p.k + j] = 0.f;
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// K10: merge nlists sorted (score, id) lists of k_in per query into the best k_out, global ids,
+// (score desc, id asc).  Used after the all-gather of per-GPU results: lists arrive as
+// [nlists][nq][k_in].  One warp per query; nlists*k_in <= 1024.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128) merge_lists_kernel(const int64_t* __restrict__ ids_in,
+                                                          const float* __restrict__ sc_in, int nq, int nlists,
+                                                          int k_in, int k_out, int64_t* __restrict__ ids_out,
+                                                          float* __restrict__ sc_out) {
+  const int q = blockIdx.x * (blockDim.x / kWarp) + (threadIdx.x / kWarp);
+  if (q >= nq) return;
+  const int lane = threadIdx.x & 31;
+  const int total = nlists * k_in;
+  // selection by repeated warp arg-max over (score desc, id asc); total is small (<= 1024)
+  float prev_s = INFINITY;
+  int64_t prev_id = -1;
+  for (int j = 0; j < k_out; ++j) {
+    float best_s = -INFINITY;
+    int64_t best_id = INT64_MAX;
+    for (int i = lane; i < total; i += kWarp) {
+      const int l = i / k_in, e = i - l * k_in;
+      const size_t at = ((size_t)l * nq + q) * k_in + e;
+      const int64_t id = ids_in[at];
+      if (id < 0) continue;
+      const float s = sc_in[at];
+      // strictly after the previously emitted (prev_s, prev_id) in the total order
+      const bool after = (s < prev_s) || (s == prev_s && id > prev_id);
+      if (!after) continue;
+      if (s > best_s || (s == best_s && id < best_id)) { best_s = s; best_id = id; }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const float os = __shfl_xor_sync(0xffffffffu, best_s, o);
+      const int64_t oi = __shfl_xor_sync(0xffffffffu, best_id, o);
+      if (os > best_s || (os == best_s && oi < best_id)) { best_s = os; best_id = oi; }
+    }
+    if (best_id == INT64_MAX) {
+      if (lane == 0) { ids_out[(size_t)q * k_out + j] = -1; sc_out[(size_t)q * k_out + j] = 0.f; }
+      prev_s = -INFINITY; prev_id = INT64_MAX;
+    } else {
+      if (lane == 0) { ids_out[(size_t)q * k_out + j] = best_id; sc_out[(size_t)q * k_out + j] = best_s; }
+      prev_s = best_s; prev_id = best_id;
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// row gather (for SearchResult.vector / get()) and stable compaction (delete)
+// ---------------------------------------------------------------------------------------------
+template <typename TIn, typename TOut>
+__global__ void gather_rows_kernel(const TIn* __restrict__ src, const int64_t* __restrict__ rows, int64_t n, int d,
+                                   TOut* __restrict__ dst) {
+  const int64_t r = blockIdx.x;
+  if (r >= n) return;
+  const TIn* s = src + rows[r] * (int64_t)d;
+  TOut* o = dst + r * (int64_t)d;
+  for (int i = threadIdx.x; i < d; i += blockDim.x) o[i] = static_cast<TOut>(static_cast<float>(s[i]));
+}
+
+}  // namespace b200

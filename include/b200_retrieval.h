@@ -1,0 +1,129 @@
+/*
+ * b200_retrieval.h -- C ABI of the B200-native retrieval hot path.
+ *
+ * This is the boundary a maintainer of Copilot-for-Consensus binds (ctypes) to
+ * replace the arithmetic behind two adapter drivers, citations relative to the reference tree:
+ *
+ *   adapters/copilot_embedding/copilot_embedding/sentence_transformer_provider.py:76-94
+ *       SentenceTransformerEmbeddingProvider.embed -> self.model.encode(...)
+ *   adapters/copilot_vectorstore/copilot_vectorstore/inmemory.py:35-178
+ *       InMemoryVectorStore.add_embedding(s) / query / delete / clear / count / get
+ *
+ * Conventions
+ *   - plain C types only; no exceptions cross the boundary.  Every function returns 0 on success
+ *     or a negative b200_status; b200_last_error() gives the calling thread's last message.
+ *   - handles are opaque and own their device memory; buffers passed in are borrowed for the call.
+ *   - `*_on_device` flags say whether a pointer is a device pointer on the handle's GPU (1) or a
+ *     host pointer (0; pinned memory makes the copies asynchronous).
+ *   - `stream` is a cudaStream_t passed as void* (NULL = the legacy default stream).  Calls are
+ *     asynchronous with respect to the host when every buffer is on the device; calls with host
+ *     output buffers synchronise the stream before returning.
+ *   - a handle may be used from several threads; calls on one handle are serialised internally.
+ *   - there is no CPU fallback: without a usable sm_100 device every call fails with
+ *     B200_ERR_CUDA / B200_ERR_UNSUPPORTED.
+ */
+#ifndef B200_RETRIEVAL_H
+#define B200_RETRIEVAL_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum b200_status {
+  B200_OK = 0,
+  B200_ERR_INVALID = -1,     /* bad argument (maps to ValueError) */
+  B200_ERR_DIMENSION = -2,   /* vector dimension mismatch (ValueError "dimension", inmemory.py:100-104) */
+  B200_ERR_NOT_FOUND = -3,   /* row out of range (KeyError "not found", inmemory.py:139,170) */
+  B200_ERR_CUDA = -4,        /* CUDA runtime / driver failure (RuntimeError) */
+  B200_ERR_UNSUPPORTED = -5, /* shape outside what the kernels implement (RuntimeError) */
+  B200_ERR_NOMEM = -6        /* device allocation failed (MemoryError) */
+} b200_status;
+
+typedef struct b200_index b200_index_t;
+typedef struct b200_encoder b200_encoder_t;
+
+/* ---- library ------------------------------------------------------------------------------ */
+const char* b200_last_error(void);
+int b200_version(void);
+/* number of visible sm_100 devices; 0 when there is none (then nothing else will work) */
+int b200_device_count(void);
+
+/* ---- vector index: replaces InMemoryVectorStore's storage + query arithmetic ---------------
+ * Rows are identified by their position in insertion order (row 0 = first inserted), which is
+ * exactly the reference's tie-break order (stable sort at inmemory.py:118).  The id <-> row map
+ * and the metadata dicts stay in the Python wrapper. */
+
+enum {
+  B200_INDEX_MASTER_F32 = 0,  /* keep the caller's fp32 rows (drop-in mode; SearchResult.vector, inmemory.py:124) */
+  B200_INDEX_MASTER_BF16 = 1  /* rows are given as bf16 and kept as bf16 (BASELINE.json "bf16 corpus") */
+};
+
+/* dim: vector dimension (1..384 in this round); capacity: initial row capacity, grows on demand. */
+int b200_index_create(int dim, int64_t capacity, int device, int master_dtype, b200_index_t** out);
+int b200_index_destroy(b200_index_t* idx);
+/* inmemory.py:145-148 clear() */
+int b200_index_clear(b200_index_t* idx);
+/* inmemory.py:150-156 count() */
+int64_t b200_index_count(const b200_index_t* idx);
+int b200_index_dim(const b200_index_t* idx);
+int b200_index_reserve(b200_index_t* idx, int64_t capacity);
+
+/* inmemory.py:35-76 add_embedding(s): append n rows [n, dim] (fp32 for MASTER_F32 indexes, bf16 bit
+ * patterns for MASTER_BF16).  Builds the unit-normalised bf16 search copy (kernel K11). */
+int b200_index_add(b200_index_t* idx, const void* rows, int64_t n, int rows_on_device, void* stream);
+
+/* inmemory.py:130-143 delete(): remove rows (ascending, unique) and close the gaps so that the
+ * remaining rows keep their relative (insertion) order. */
+int b200_index_remove_rows(b200_index_t* idx, const int64_t* rows_host, int64_t n, void* stream);
+
+/* inmemory.py:124,174 SearchResult.vector / get(): copy n stored rows (as fp32) to out[n, dim]. */
+int b200_index_get_rows(b200_index_t* idx, const int64_t* rows_host, int64_t n, float* out, int out_on_device,
+                        void* stream);
+
+/* inmemory.py:78-128 query(), batched: for each of nq raw query vectors return the k best rows by
+ * cosine similarity, scores computed as the reference does (fp32, eps 1e-8), ordered by
+ * (score descending, row ascending).  ids[nq*k] = id_base + row, -1 where fewer than k rows exist;
+ * scores[nq*k].  q_dtype: 0 = fp32, 1 = bf16.  k <= 48 in this round. */
+int b200_index_search(b200_index_t* idx, const void* queries, int q_dtype, int queries_on_device, int64_t nq,
+                      int k, int64_t id_base, int64_t* ids, float* scores, int out_on_device, void* stream);
+
+/* Multi-GPU candidate merge (no reference counterpart: the reference is single-process).  After an
+ * all-gather of per-shard results laid out [nlists][nq][k_in], keep the best k_out per query under
+ * the same (score desc, id asc) order.  All pointers are device pointers. */
+int b200_merge_topk(const int64_t* ids_in, const float* scores_in, int64_t nq, int nlists, int k_in, int k_out,
+                    int64_t* ids_out, float* scores_out, int device, void* stream);
+
+/* ---- encoder: replaces SentenceTransformer.encode for BERT-class models ---------------------
+ * sentence_transformer_provider.py:93 -> tokenise (host, not here) -> BertModel -> masked mean
+ * pool -> L2 normalise.  Weights are handed over by HuggingFace state_dict key. */
+
+typedef struct b200_encoder_config {
+  int32_t vocab_size;
+  int32_t hidden;       /* 384 (MiniLM-L6) or 768 (mpnet-base class) */
+  int32_t layers;
+  int32_t heads;
+  int32_t intermediate;
+  int32_t max_pos;
+  int32_t type_vocab;
+  float ln_eps;
+} b200_encoder_config_t;
+
+int b200_encoder_create(const b200_encoder_config_t* cfg, int device, b200_encoder_t** out);
+int b200_encoder_destroy(b200_encoder_t* enc);
+/* name: HF BertModel state_dict key (e.g. "encoder.layer.0.attention.self.query.weight");
+ * data: fp32 host buffer of numel elements. */
+int b200_encoder_load_tensor(b200_encoder_t* enc, const char* name, const float* data, int64_t numel);
+/* checks that every tensor arrived, packs Q/K/V, converts GEMM operands to bf16 */
+int b200_encoder_finalize(b200_encoder_t* enc);
+int b200_encoder_hidden(const b200_encoder_t* enc);
+/* input_ids[B*S] int32 (0-padded), lengths[B] int32 valid tokens per row (attention mask = first
+ * lengths[b] tokens); out[B*hidden] fp32 L2-normalised embeddings. */
+int b200_encode(b200_encoder_t* enc, const int32_t* input_ids, const int32_t* lengths, int batch, int seq,
+                int inputs_on_device, float* out, int out_on_device, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200_RETRIEVAL_H */
