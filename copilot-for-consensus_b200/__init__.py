@@ -9,7 +9,9 @@ The directory name is not a Python identifier; import it with
 ``importlib.import_module("copilot-for-consensus_b200")`` or through the top-level alias module
 ``copilot_for_consensus_b200``.
 """
+from .embedding import EmbeddingProvider, create_embedding_provider
 from .vectorstore import B200VectorStore, SearchResult, VectorStore, create_vector_store
 
-__all__ = ["B200VectorStore", "SearchResult", "VectorStore", "create_vector_store"]
+__all__ = ["B200VectorStore", "SearchResult", "VectorStore", "create_vector_store",
+           "EmbeddingProvider", "create_embedding_provider"]
 __version__ = "0.1.0"

@@ -46,6 +46,10 @@ SYMBOLS = {
     "b200_encoder_finalize": (_i, [_vp]),
     "b200_encoder_hidden": (_i, [_vp]),
     "b200_encode": (_i, [_vp, _vp, _vp, _i, _i, _i, _vp, _i, _vp]),
+    "b200_encoder_peek": (_i, [_vp, _i, _vp, _i64]),
+    "b200_profile_enable": (_i, [_i]),
+    "b200_profile_reset": (_i, []),
+    "b200_profile_read": (_i64, [_vp, _i64]),
 }
 
 _lib = None
@@ -114,3 +118,19 @@ def current_stream_ptr(device_ordinal: int) -> int:
     except Exception:
         pass
     return 0
+
+
+def profile(on: bool) -> None:
+    lib().b200_profile_reset()
+    lib().b200_profile_enable(1 if on else 0)
+
+
+def profile_read() -> dict[str, dict[str, float]]:
+    """{kernel name: {"launches", "ms", "flops", "bytes"}} accumulated since the last reset."""
+    buf = ctypes.create_string_buffer(1 << 16)
+    n = lib().b200_profile_read(buf, len(buf))
+    out: dict[str, dict[str, float]] = {}
+    for line in buf.value[: max(n, 0)].decode().splitlines():
+        name, cnt, ms, fl, by = line.split()
+        out[name] = {"launches": int(cnt), "ms": float(ms), "flops": float(fl), "bytes": float(by)}
+    return out

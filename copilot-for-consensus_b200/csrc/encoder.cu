@@ -1,20 +1,377 @@
-// encoder.cu -- host side of the BERT-class encoder behind the C ABI (placeholder until the
-// encoder milestone lands; every entry point reports B200_ERR_UNSUPPORTED).
-#include "host_util.h"
+// encoder.cu -- host side of the BERT-class encoder behind the C ABI (include/b200_retrieval.h).
+//
+// Replaces the arithmetic behind SentenceTransformerEmbeddingProvider.embed ->
+// self.model.encode(...) (adapters/copilot_embedding/copilot_embedding/sentence_transformer_provider.py:93)
+// for BERT-architecture models: token ids in, L2-normalised sentence embeddings out.  Tokenisation
+// stays on the host, in Python.
+//
+// Data layout in HBM
+//   weights  bf16, nn.Linear layout [out, in] (= K-major B operand for tcgen05); Q/K/V packed as
+//            one [3H, H]; embedding tables bf16; biases and LayerNorm parameters fp32
+//   x        bf16 [M, H]   hidden state            qkv  bf16 [M, 3H]
+//   ctx      bf16 [M, H]   attention output        y    bf16 [M, H]  pre-LayerNorm sum
+//   ffn      bf16 [M, I]   GELU(W1 x + b1)         M = batch * seq rounded up to 128 rows
+#include <map>
+#include <string>
+#include <vector>
+
 #include "encoder_kernels.cuh"
+#include "host_util.h"
 
 using namespace b200;
 
-struct b200_encoder { int hidden = 0; };
+namespace {
+
+struct LayerWeights {
+  DevBuf wqkv, wo, w1, w2;              // bf16
+  DevBuf bqkv, bo, b1, b2;              // fp32
+  DevBuf ln1_g, ln1_b, ln2_g, ln2_b;    // fp32
+  CUtensorMap map_wqkv, map_wo, map_w1, map_w2;
+};
+
+uint16_t f32_to_bf16_host(float f) {
+  uint32_t u;
+  memcpy(&u, &f, 4);
+  if ((u & 0x7fffffffu) > 0x7f800000u) return (uint16_t)((u >> 16) | 0x40);
+  u += 0x7fffu + ((u >> 16) & 1u);
+  return (uint16_t)(u >> 16);
+}
+
+int upload_bf16(DevBuf& dst, const float* src, size_t n) {
+  std::vector<uint16_t> tmp(n);
+  for (size_t i = 0; i < n; ++i) tmp[i] = f32_to_bf16_host(src[i]);
+  B200_TRY(dst.alloc(n * 2));
+  B200_CUDA(cudaMemcpy(dst.p, tmp.data(), n * 2, cudaMemcpyHostToDevice));
+  return B200_OK;
+}
+int upload_f32(DevBuf& dst, const float* src, size_t n) {
+  B200_TRY(dst.alloc(n * 4));
+  B200_CUDA(cudaMemcpy(dst.p, src, n * 4, cudaMemcpyHostToDevice));
+  return B200_OK;
+}
+
+}  // namespace
+
+struct b200_encoder {
+  b200_encoder_config_t cfg{};
+  int device = 0, num_sms = 148;
+  bool finalized = false;
+  std::map<std::string, std::vector<float>> pending;  // tensors handed over before finalize
+  DevBuf word, pos, type0, emb_g, emb_b;
+  std::vector<LayerWeights*> layers;
+  // activations, sized for m_cap rows
+  int64_t m_cap = 0;
+  DevBuf x, qkv, ctx, y, ffn, ids, lens, out;
+  CUtensorMap map_x, map_ctx, map_ffn;
+  std::mutex mu;
+  ~b200_encoder() {
+    for (auto* l : layers) delete l;
+  }
+};
+
+static constexpr int kGemmBlockN = 192;
+
+static int pick_block_n(int N) {
+  if (N % 192 == 0) return 192;
+  if (N % 128 == 0) return 128;
+  if (N % 64 == 0) return 64;
+  return 0;
+}
+
+template <int BLOCK_N, int EPI>
+static int launch_gemm_t(const b200_encoder* e, const CUtensorMap& ma, const CUtensorMap& mb, GemmParams p,
+                         cudaStream_t st) {
+  const size_t stage = (size_t)GEMM_A_STAGE_BYTES + (size_t)BLOCK_N * GEMM_BLOCK_K * 2;
+  const size_t max_smem = 232448;
+  int nstage = (int)std::min<size_t>(8, (max_smem - 1024 - 256) / stage);
+  p.nstage = nstage;
+  const size_t smem = 1024 + (size_t)nstage * stage + 256;
+  auto kern = gemm_bf16_kernel<BLOCK_N, EPI>;
+  B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  const int tiles = (p.M / GEMM_BLOCK_M) * (p.N / BLOCK_N);
+  const int grid = std::min(tiles, e->num_sms);
+  {
+    B200_PROF(EPI == EPI_BIAS ? "gemm_bias" : (EPI == EPI_BIAS_GELU ? "gemm_bias_gelu" : "gemm_bias_resid"),
+              2.0 * p.M * (double)p.N * p.K,
+              2.0 * ((double)p.M * p.K + (double)p.N * p.K + (double)p.M * p.N * (EPI == EPI_BIAS_RESID ? 2 : 1)), st);
+    kern<<<grid, GEMM_THREADS, smem, st>>>(ma, mb, p);
+  }
+  B200_CUDA(cudaGetLastError());
+  return B200_OK;
+}
+
+template <int EPI>
+static int launch_gemm(const b200_encoder* e, const CUtensorMap& ma, const CUtensorMap& mb, const GemmParams& p,
+                       cudaStream_t st) {
+  switch (pick_block_n(p.N)) {
+    case 192: return launch_gemm_t<192, EPI>(e, ma, mb, p, st);
+    case 128: return launch_gemm_t<128, EPI>(e, ma, mb, p, st);
+    case 64: return launch_gemm_t<64, EPI>(e, ma, mb, p, st);
+  }
+  B200_FAIL(B200_ERR_UNSUPPORTED, "GEMM N=%d is not a multiple of 64", p.N);
+}
+
+static int weight_map(CUtensorMap* m, const DevBuf& w, int N, int K) {
+  return make_tma_2d_bf16(m, w.p, (uint64_t)N, (uint64_t)K, (uint32_t)pick_block_n(N), GEMM_BLOCK_K);
+}
+
+static int ensure_activations(b200_encoder* e, int64_t m_rows, int batch, cudaStream_t st) {
+  const int H = e->cfg.hidden, I = e->cfg.intermediate;
+  B200_TRY(e->lens.grow((size_t)std::max(batch, 1) * 4, 0, st));
+  B200_TRY(e->out.grow((size_t)std::max(batch, 1) * H * 4, 0, st));
+  if (m_rows <= e->m_cap) return B200_OK;
+  const int64_t m = (m_rows + 127) / 128 * 128;
+  B200_TRY(e->ids.grow((size_t)m * 4, 0, st));
+  B200_TRY(e->x.grow((size_t)m * H * 2, 0, st));
+  B200_TRY(e->qkv.grow((size_t)m * 3 * H * 2, 0, st));
+  B200_TRY(e->ctx.grow((size_t)m * H * 2, 0, st));
+  B200_TRY(e->y.grow((size_t)m * H * 2, 0, st));
+  B200_TRY(e->ffn.grow((size_t)m * I * 2, 0, st));
+  // rows beyond the live batch are computed along with it (whole 128-row tiles); keep them finite
+  B200_CUDA(cudaMemsetAsync(e->x.p, 0, (size_t)m * H * 2, st));
+  B200_CUDA(cudaMemsetAsync(e->ctx.p, 0, (size_t)m * H * 2, st));
+  B200_CUDA(cudaMemsetAsync(e->ffn.p, 0, (size_t)m * I * 2, st));
+  B200_CUDA(cudaMemsetAsync(e->qkv.p, 0, (size_t)m * 3 * H * 2, st));
+  B200_TRY(make_tma_2d_bf16(&e->map_x, e->x.p, (uint64_t)m, (uint64_t)H, GEMM_BLOCK_M, GEMM_BLOCK_K));
+  B200_TRY(make_tma_2d_bf16(&e->map_ctx, e->ctx.p, (uint64_t)m, (uint64_t)H, GEMM_BLOCK_M, GEMM_BLOCK_K));
+  B200_TRY(make_tma_2d_bf16(&e->map_ffn, e->ffn.p, (uint64_t)m, (uint64_t)I, GEMM_BLOCK_M, GEMM_BLOCK_K));
+  e->m_cap = m;
+  return B200_OK;
+}
+
+static int vt_stride_for(int S) {
+  // V^T row stride (elements) with (stride/2) % 32 == 4, so 32-bit fragment reads hit 32 banks
+  int words = S / 2;
+  int pad_words = ((4 - (words % 32)) % 32 + 32) % 32;
+  return (words + pad_words) * 2;
+}
+
+static int take(b200_encoder* e, const std::string& name, size_t numel, const std::vector<float>** out) {
+  auto it = e->pending.find(name);
+  if (it == e->pending.end()) B200_FAIL(B200_ERR_INVALID, "missing tensor '%s'", name.c_str());
+  if (it->second.size() != numel)
+    B200_FAIL(B200_ERR_DIMENSION, "tensor '%s' has %zu elements, expected %zu", name.c_str(), it->second.size(), numel);
+  *out = &it->second;
+  return B200_OK;
+}
+
+template <int NV>
+static int run_encoder(b200_encoder* e, const int32_t* d_ids, const int32_t* d_lens, int batch, int seq, float* d_out,
+                       cudaStream_t st) {
+  const int H = e->cfg.hidden, I = e->cfg.intermediate, heads = e->cfg.heads, dh = H / heads;
+  const int n_tok = batch * seq;
+  const int M = (n_tok + 127) / 128 * 128;
+  const int wpb = 8;
+  __nv_bfloat16* x = e->x.as<__nv_bfloat16>();
+  __nv_bfloat16* y = e->y.as<__nv_bfloat16>();
+  embed_ln_kernel<NV><<<(n_tok + wpb - 1) / wpb, wpb * 32, 0, st>>>(
+      d_ids, n_tok, seq, e->cfg.vocab_size, e->word.as<__nv_bfloat16>(), e->pos.as<__nv_bfloat16>(),
+      e->type0.as<__nv_bfloat16>(), e->emb_g.as<float>(), e->emb_b.as<float>(), e->cfg.ln_eps, x);
+  B200_CUDA(cudaGetLastError());
+
+  const int vt_stride = vt_stride_for(seq);
+  const size_t att_smem = (size_t)seq * (dh + 8) * 2 + (size_t)dh * vt_stride * 2;
+  if (att_smem > 232448) B200_FAIL(B200_ERR_UNSUPPORTED, "sequence length %d needs %zu bytes of shared memory", seq, att_smem);
+  if (dh == 32) B200_CUDA(cudaFuncSetAttribute(attention_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)att_smem));
+  else B200_CUDA(cudaFuncSetAttribute(attention_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)att_smem));
+
+  for (int l = 0; l < e->cfg.layers; ++l) {
+    LayerWeights* L = e->layers[l];
+    GemmParams p{};
+    // Q,K,V projections in one GEMM: qkv = x Wqkv^T + bqkv
+    p.M = M; p.N = 3 * H; p.K = H; p.bias = L->bqkv.as<float>(); p.resid = nullptr; p.out = e->qkv.as<__nv_bfloat16>();
+    B200_TRY(launch_gemm<EPI_BIAS>(e, e->map_x, L->map_wqkv, p, st));
+    B200_PROF("attention", 4.0 * batch * (double)seq * seq * H, 2.0 * 4.0 * n_tok * H, st);
+    if (dh == 32)
+      attention_kernel<32><<<dim3(heads, batch), 256, att_smem, st>>>(e->qkv.as<__nv_bfloat16>(), d_lens, seq, H,
+                                                                      e->ctx.as<__nv_bfloat16>(), vt_stride);
+    else
+      attention_kernel<64><<<dim3(heads, batch), 256, att_smem, st>>>(e->qkv.as<__nv_bfloat16>(), d_lens, seq, H,
+                                                                      e->ctx.as<__nv_bfloat16>(), vt_stride);
+    B200_CUDA(cudaGetLastError());
+    // y = ctx Wo^T + bo + x ; x = LN(y)
+    p.N = H; p.K = H; p.bias = L->bo.as<float>(); p.resid = x; p.out = y;
+    B200_TRY(launch_gemm<EPI_BIAS_RESID>(e, e->map_ctx, L->map_wo, p, st));
+    layernorm_kernel<NV><<<(n_tok + wpb - 1) / wpb, wpb * 32, 0, st>>>(y, n_tok, L->ln1_g.as<float>(), L->ln1_b.as<float>(),
+                                                                      e->cfg.ln_eps, x);
+    B200_CUDA(cudaGetLastError());
+    // ffn = gelu(x W1^T + b1) ; y = ffn W2^T + b2 + x ; x = LN(y)
+    p.N = I; p.K = H; p.bias = L->b1.as<float>(); p.resid = nullptr; p.out = e->ffn.as<__nv_bfloat16>();
+    B200_TRY(launch_gemm<EPI_BIAS_GELU>(e, e->map_x, L->map_w1, p, st));
+    p.N = H; p.K = I; p.bias = L->b2.as<float>(); p.resid = x; p.out = y;
+    B200_TRY(launch_gemm<EPI_BIAS_RESID>(e, e->map_ffn, L->map_w2, p, st));
+    layernorm_kernel<NV><<<(n_tok + wpb - 1) / wpb, wpb * 32, 0, st>>>(y, n_tok, L->ln2_g.as<float>(), L->ln2_b.as<float>(),
+                                                                      e->cfg.ln_eps, x);
+    B200_CUDA(cudaGetLastError());
+  }
+  pool_normalize_kernel<<<batch, 256, 0, st>>>(x, d_lens, seq, H, d_out);
+  B200_CUDA(cudaGetLastError());
+  return B200_OK;
+}
 
 extern "C" {
-int b200_encoder_create(const b200_encoder_config_t*, int, b200_encoder_t** out) {
-  if (out) *out = nullptr;
-  B200_FAIL(B200_ERR_UNSUPPORTED, "encoder not built yet");
+
+int b200_encoder_create(const b200_encoder_config_t* cfg, int device, b200_encoder_t** out) {
+  if (!out) B200_FAIL(B200_ERR_INVALID, "out is NULL");
+  *out = nullptr;
+  if (!cfg) B200_FAIL(B200_ERR_INVALID, "config is NULL");
+  if (cfg->hidden <= 0 || cfg->hidden % 128 != 0 || cfg->hidden > 1024)
+    B200_FAIL(B200_ERR_UNSUPPORTED, "hidden=%d: must be a multiple of 128 up to 1024", cfg->hidden);
+  if (cfg->heads <= 0 || cfg->hidden % cfg->heads != 0)
+    B200_FAIL(B200_ERR_INVALID, "hidden=%d is not divisible by heads=%d", cfg->hidden, cfg->heads);
+  const int dh = cfg->hidden / cfg->heads;
+  if (dh != 32 && dh != 64) B200_FAIL(B200_ERR_UNSUPPORTED, "head dimension %d: only 32 and 64 are implemented", dh);
+  if (cfg->intermediate <= 0 || cfg->intermediate % 64 != 0)
+    B200_FAIL(B200_ERR_UNSUPPORTED, "intermediate=%d must be a multiple of 64", cfg->intermediate);
+  if (cfg->layers <= 0 || cfg->vocab_size <= 0 || cfg->max_pos <= 0 || cfg->type_vocab <= 0)
+    B200_FAIL(B200_ERR_INVALID, "layers, vocab_size, max_pos and type_vocab must be positive");
+  B200_TRY(check_device_is_sm100(device));
+  b200_encoder* e = new b200_encoder();
+  e->cfg = *cfg;
+  e->device = device;
+  cudaDeviceGetAttribute(&e->num_sms, cudaDevAttrMultiProcessorCount, device);
+  *out = e;
+  return B200_OK;
 }
-int b200_encoder_destroy(b200_encoder_t* e) { delete e; return B200_OK; }
-int b200_encoder_load_tensor(b200_encoder_t*, const char*, const float*, int64_t) { B200_FAIL(B200_ERR_UNSUPPORTED, "encoder not built yet"); }
-int b200_encoder_finalize(b200_encoder_t*) { B200_FAIL(B200_ERR_UNSUPPORTED, "encoder not built yet"); }
-int b200_encoder_hidden(const b200_encoder_t* e) { return e ? e->hidden : 0; }
-int b200_encode(b200_encoder_t*, const int32_t*, const int32_t*, int, int, int, float*, int, void*) { B200_FAIL(B200_ERR_UNSUPPORTED, "encoder not built yet"); }
+
+int b200_encoder_destroy(b200_encoder_t* e) {
+  if (!e) return B200_OK;
+  DeviceGuard g(e->device);
+  cudaDeviceSynchronize();
+  delete e;
+  return B200_OK;
 }
+
+int b200_encoder_hidden(const b200_encoder_t* e) { return e ? e->cfg.hidden : 0; }
+
+int b200_encoder_load_tensor(b200_encoder_t* e, const char* name, const float* data, int64_t numel) {
+  if (!e || !name || !data || numel <= 0) B200_FAIL(B200_ERR_INVALID, "bad load_tensor arguments");
+  std::lock_guard<std::mutex> lk(e->mu);
+  if (e->finalized) B200_FAIL(B200_ERR_INVALID, "encoder is already finalized");
+  e->pending[name].assign(data, data + numel);
+  return B200_OK;
+}
+
+int b200_encoder_finalize(b200_encoder_t* e) {
+  if (!e) B200_FAIL(B200_ERR_INVALID, "encoder is NULL");
+  std::lock_guard<std::mutex> lk(e->mu);
+  if (e->finalized) return B200_OK;
+  DeviceGuard g(e->device);
+  if (!g.ok) B200_FAIL(B200_ERR_CUDA, "cudaSetDevice(%d) failed", e->device);
+  const size_t H = e->cfg.hidden, I = e->cfg.intermediate;
+  const std::vector<float>* t = nullptr;
+  B200_TRY(take(e, "embeddings.word_embeddings.weight", (size_t)e->cfg.vocab_size * H, &t));
+  B200_TRY(upload_bf16(e->word, t->data(), t->size()));
+  B200_TRY(take(e, "embeddings.position_embeddings.weight", (size_t)e->cfg.max_pos * H, &t));
+  B200_TRY(upload_bf16(e->pos, t->data(), t->size()));
+  B200_TRY(take(e, "embeddings.token_type_embeddings.weight", (size_t)e->cfg.type_vocab * H, &t));
+  B200_TRY(upload_bf16(e->type0, t->data(), H));  // token type ids are all zero on this path
+  B200_TRY(take(e, "embeddings.LayerNorm.weight", H, &t));
+  B200_TRY(upload_f32(e->emb_g, t->data(), H));
+  B200_TRY(take(e, "embeddings.LayerNorm.bias", H, &t));
+  B200_TRY(upload_f32(e->emb_b, t->data(), H));
+  for (int l = 0; l < e->cfg.layers; ++l) {
+    const std::string p = "encoder.layer." + std::to_string(l) + ".";
+    LayerWeights* L = new LayerWeights();
+    e->layers.push_back(L);
+    std::vector<float> wqkv(3 * H * H), bqkv(3 * H);
+    const char* names[3] = {"query", "key", "value"};
+    for (int j = 0; j < 3; ++j) {
+      B200_TRY(take(e, p + "attention.self." + names[j] + ".weight", H * H, &t));
+      memcpy(wqkv.data() + (size_t)j * H * H, t->data(), H * H * 4);
+      B200_TRY(take(e, p + "attention.self." + names[j] + ".bias", H, &t));
+      memcpy(bqkv.data() + (size_t)j * H, t->data(), H * 4);
+    }
+    B200_TRY(upload_bf16(L->wqkv, wqkv.data(), wqkv.size()));
+    B200_TRY(upload_f32(L->bqkv, bqkv.data(), bqkv.size()));
+    B200_TRY(take(e, p + "attention.output.dense.weight", H * H, &t));
+    B200_TRY(upload_bf16(L->wo, t->data(), t->size()));
+    B200_TRY(take(e, p + "attention.output.dense.bias", H, &t));
+    B200_TRY(upload_f32(L->bo, t->data(), H));
+    B200_TRY(take(e, p + "attention.output.LayerNorm.weight", H, &t));
+    B200_TRY(upload_f32(L->ln1_g, t->data(), H));
+    B200_TRY(take(e, p + "attention.output.LayerNorm.bias", H, &t));
+    B200_TRY(upload_f32(L->ln1_b, t->data(), H));
+    B200_TRY(take(e, p + "intermediate.dense.weight", I * H, &t));
+    B200_TRY(upload_bf16(L->w1, t->data(), t->size()));
+    B200_TRY(take(e, p + "intermediate.dense.bias", I, &t));
+    B200_TRY(upload_f32(L->b1, t->data(), I));
+    B200_TRY(take(e, p + "output.dense.weight", H * I, &t));
+    B200_TRY(upload_bf16(L->w2, t->data(), t->size()));
+    B200_TRY(take(e, p + "output.dense.bias", H, &t));
+    B200_TRY(upload_f32(L->b2, t->data(), H));
+    B200_TRY(take(e, p + "output.LayerNorm.weight", H, &t));
+    B200_TRY(upload_f32(L->ln2_g, t->data(), H));
+    B200_TRY(take(e, p + "output.LayerNorm.bias", H, &t));
+    B200_TRY(upload_f32(L->ln2_b, t->data(), H));
+    B200_TRY(weight_map(&L->map_wqkv, L->wqkv, (int)(3 * H), (int)H));
+    B200_TRY(weight_map(&L->map_wo, L->wo, (int)H, (int)H));
+    B200_TRY(weight_map(&L->map_w1, L->w1, (int)I, (int)H));
+    B200_TRY(weight_map(&L->map_w2, L->w2, (int)H, (int)I));
+  }
+  e->pending.clear();
+  e->finalized = true;
+  return B200_OK;
+}
+
+int b200_encode(b200_encoder_t* e, const int32_t* input_ids, const int32_t* lengths, int batch, int seq,
+                int inputs_on_device, float* out, int out_on_device, void* stream) {
+  if (!e) B200_FAIL(B200_ERR_INVALID, "encoder is NULL");
+  if (batch < 0 || seq < 0) B200_FAIL(B200_ERR_INVALID, "negative batch / seq");
+  if (batch == 0) return B200_OK;
+  if (!input_ids || !lengths || !out) B200_FAIL(B200_ERR_INVALID, "NULL buffer");
+  if (seq == 0 || seq % 16 != 0) B200_FAIL(B200_ERR_INVALID, "seq=%d must be a positive multiple of 16 (pad with id 0)", seq);
+  if (seq > e->cfg.max_pos) B200_FAIL(B200_ERR_INVALID, "seq=%d exceeds max_position_embeddings=%d", seq, e->cfg.max_pos);
+  std::lock_guard<std::mutex> lk(e->mu);
+  if (!e->finalized) B200_FAIL(B200_ERR_INVALID, "encoder weights are not finalized");
+  DeviceGuard g(e->device);
+  if (!g.ok) B200_FAIL(B200_ERR_CUDA, "cudaSetDevice(%d) failed", e->device);
+  cudaStream_t st = (cudaStream_t)stream;
+  const int64_t n_tok = (int64_t)batch * seq;
+  if (n_tok > (int64_t)1 << 30) B200_FAIL(B200_ERR_UNSUPPORTED, "batch*seq too large");
+  B200_TRY(ensure_activations(e, n_tok, batch, st));
+  const int32_t* d_ids = input_ids;
+  const int32_t* d_lens = lengths;
+  if (!inputs_on_device) {
+    B200_CUDA(cudaMemcpyAsync(e->ids.p, input_ids, (size_t)n_tok * 4, cudaMemcpyHostToDevice, st));
+    B200_CUDA(cudaMemcpyAsync(e->lens.p, lengths, (size_t)batch * 4, cudaMemcpyHostToDevice, st));
+    d_ids = e->ids.as<int32_t>();
+    d_lens = e->lens.as<int32_t>();
+  }
+  float* d_out = out_on_device ? out : e->out.as<float>();
+  int rc;
+  switch (e->cfg.hidden / 128) {
+    case 1: rc = run_encoder<1>(e, d_ids, d_lens, batch, seq, d_out, st); break;
+    case 2: rc = run_encoder<2>(e, d_ids, d_lens, batch, seq, d_out, st); break;
+    case 3: rc = run_encoder<3>(e, d_ids, d_lens, batch, seq, d_out, st); break;
+    case 4: rc = run_encoder<4>(e, d_ids, d_lens, batch, seq, d_out, st); break;
+    case 6: rc = run_encoder<6>(e, d_ids, d_lens, batch, seq, d_out, st); break;
+    case 8: rc = run_encoder<8>(e, d_ids, d_lens, batch, seq, d_out, st); break;
+    default: B200_FAIL(B200_ERR_UNSUPPORTED, "hidden=%d is not instantiated (128,256,384,512,768,1024)", e->cfg.hidden);
+  }
+  B200_TRY(rc);
+  if (!out_on_device) {
+    B200_CUDA(cudaMemcpyAsync(out, d_out, (size_t)batch * e->cfg.hidden * 4, cudaMemcpyDeviceToHost, st));
+    B200_CUDA(cudaStreamSynchronize(st));
+  }
+  return B200_OK;
+}
+
+int b200_encoder_peek(b200_encoder_t* e, int which, float* out_host, int64_t numel) {
+  if (!e || !out_host || numel < 0) B200_FAIL(B200_ERR_INVALID, "bad peek arguments");
+  std::lock_guard<std::mutex> lk(e->mu);
+  DeviceGuard g(e->device);
+  DevBuf* bufs[5] = {&e->x, &e->qkv, &e->ctx, &e->y, &e->ffn};
+  if (which < 0 || which > 4) B200_FAIL(B200_ERR_INVALID, "which must be 0..4");
+  if ((size_t)numel * 2 > bufs[which]->bytes) B200_FAIL(B200_ERR_INVALID, "numel exceeds the buffer");
+  std::vector<uint16_t> tmp((size_t)numel);
+  B200_CUDA(cudaDeviceSynchronize());
+  B200_CUDA(cudaMemcpy(tmp.data(), bufs[which]->p, (size_t)numel * 2, cudaMemcpyDeviceToHost));
+  for (int64_t i = 0; i < numel; ++i) {
+    const uint32_t u = (uint32_t)tmp[(size_t)i] << 16;
+    memcpy(&out_host[i], &u, 4);
+  }
+  return B200_OK;
+}
+
+}  // extern "C"

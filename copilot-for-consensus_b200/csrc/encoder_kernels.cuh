@@ -1,3 +1,484 @@
-// encoder_kernels.cuh -- device code for the chunk-embedding path (filled in by the encoder milestone)
+// encoder_kernels.cuh -- device code for the chunk-embedding path.
+//
+// Restates what SentenceTransformer.encode does for a BERT-class model
+// (sentence_transformer_provider.py:93; pipeline in oracle/encode_oracle.py):
+//
+//   embed_ln_kernel        K1   word + position + type embeddings -> LayerNorm
+//   gemm_bf16_kernel       K2/K4/K5/K6  X[M,K] . W[N,K]^T on tcgen05 (TMA-fed, TMEM accumulators,
+//                               persistent, warp-specialised) with fused epilogues:
+//                               +bias | +bias,GELU(erf) | +bias,+residual
+//   layernorm_kernel       (K4/K6 tail) LayerNorm over the hidden dimension
+//   attention_kernel       K3   softmax(QK^T/sqrt(dh) + key-padding mask) V, flash-style
+//   pool_normalize_kernel  K7   masked mean over tokens + L2 normalise
+//
+// Activations are bf16 [tokens, features] row-major; accumulation, LayerNorm statistics, softmax
+// and pooling are fp32.
 #pragma once
 #include "common.cuh"
+
+namespace b200 {
+
+// =============================================================================================
+// K1: embeddings + LayerNorm.  One warp per token; H = 128 * NV elements, 4 per lane per pass.
+// =============================================================================================
+B200_DEVINL void bf16x4_to_f32(uint2 u, float (&f)[4]) {
+  const __nv_bfloat162 a = *reinterpret_cast<__nv_bfloat162*>(&u.x);
+  const __nv_bfloat162 b = *reinterpret_cast<__nv_bfloat162*>(&u.y);
+  f[0] = __low2float(a); f[1] = __high2float(a); f[2] = __low2float(b); f[3] = __high2float(b);
+}
+B200_DEVINL uint2 f32x4_to_bf16(const float (&f)[4]) {
+  __nv_bfloat162 a = __floats2bfloat162_rn(f[0], f[1]);
+  __nv_bfloat162 b = __floats2bfloat162_rn(f[2], f[3]);
+  uint2 u;
+  u.x = *reinterpret_cast<uint32_t*>(&a);
+  u.y = *reinterpret_cast<uint32_t*>(&b);
+  return u;
+}
+
+// LayerNorm of one row held as NV x 4 floats per lane (two-pass, fp32), affine, bf16 out
+template <int NV>
+B200_DEVINL void warp_layernorm_store(float (&v)[NV][4], int H, float eps, const float* __restrict__ gamma,
+                                      const float* __restrict__ beta, __nv_bfloat16* __restrict__ out, int lane) {
+  float s = 0.f;
+#pragma unroll
+  for (int i = 0; i < NV; ++i) s += (v[i][0] + v[i][1]) + (v[i][2] + v[i][3]);
+  const float mean = warp_sum(s) / (float)H;
+  float q = 0.f;
+#pragma unroll
+  for (int i = 0; i < NV; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float d = v[i][j] - mean;
+      q = fmaf(d, d, q);
+    }
+  const float rstd = rsqrtf(warp_sum(q) / (float)H + eps);
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    const int c = i * 128 + lane * 4;
+    const float4 g = *reinterpret_cast<const float4*>(gamma + c);
+    const float4 b = *reinterpret_cast<const float4*>(beta + c);
+    float o[4];
+    o[0] = (v[i][0] - mean) * rstd * g.x + b.x;
+    o[1] = (v[i][1] - mean) * rstd * g.y + b.y;
+    o[2] = (v[i][2] - mean) * rstd * g.z + b.z;
+    o[3] = (v[i][3] - mean) * rstd * g.w + b.w;
+    *reinterpret_cast<uint2*>(out + c) = f32x4_to_bf16(o);
+  }
+}
+
+template <int NV>
+__global__ void __launch_bounds__(256) embed_ln_kernel(const int32_t* __restrict__ ids, int n_tokens, int S, int vocab,
+                                                       const __nv_bfloat16* __restrict__ word,
+                                                       const __nv_bfloat16* __restrict__ pos,
+                                                       const __nv_bfloat16* __restrict__ type0,
+                                                       const float* __restrict__ gamma, const float* __restrict__ beta,
+                                                       float eps, __nv_bfloat16* __restrict__ x) {
+  constexpr int H = NV * 128;
+  const int tok = blockIdx.x * (blockDim.x / kWarp) + (threadIdx.x / kWarp);
+  if (tok >= n_tokens) return;
+  const int lane = threadIdx.x & 31;
+  int id = ids[tok];
+  id = min(max(id, 0), vocab - 1);
+  const int t = tok % S;
+  float v[NV][4];
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    const int c = i * 128 + lane * 4;
+    float w[4], p[4], ty[4];
+    bf16x4_to_f32(__ldg(reinterpret_cast<const uint2*>(word + (size_t)id * H + c)), w);
+    bf16x4_to_f32(__ldg(reinterpret_cast<const uint2*>(pos + (size_t)t * H + c)), p);
+    bf16x4_to_f32(__ldg(reinterpret_cast<const uint2*>(type0 + c)), ty);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) v[i][j] = (w[j] + p[j]) + ty[j];
+  }
+  warp_layernorm_store<NV>(v, H, eps, gamma, beta, x + (size_t)tok * H, lane);
+}
+
+template <int NV>
+__global__ void __launch_bounds__(256) layernorm_kernel(const __nv_bfloat16* __restrict__ y, int n_rows,
+                                                        const float* __restrict__ gamma, const float* __restrict__ beta,
+                                                        float eps, __nv_bfloat16* __restrict__ x) {
+  constexpr int H = NV * 128;
+  const int row = blockIdx.x * (blockDim.x / kWarp) + (threadIdx.x / kWarp);
+  if (row >= n_rows) return;
+  const int lane = threadIdx.x & 31;
+  float v[NV][4];
+#pragma unroll
+  for (int i = 0; i < NV; ++i)
+    bf16x4_to_f32(*reinterpret_cast<const uint2*>(y + (size_t)row * H + i * 128 + lane * 4), v[i]);
+  warp_layernorm_store<NV>(v, H, eps, gamma, beta, x + (size_t)row * H, lane);
+}
+
+// =============================================================================================
+// GEMM: out[M,N] = epilogue( A[M,K] . W[N,K]^T ), bf16 in, fp32 accumulate in TMEM, bf16 out.
+// Persistent CTAs (one per SM) walk 128 x BLOCK_N output tiles; roles:
+//   warp 0 TMA producer | warp 1 MMA issuer | warp 2 TMEM allocator | warps 4..11 epilogue
+// Two TMEM accumulator stages let tile i's epilogue overlap tile i+1's MMAs.
+// =============================================================================================
+constexpr int GEMM_BLOCK_M = 128;
+constexpr int GEMM_BLOCK_K = 64;
+constexpr int GEMM_THREADS = 384;
+constexpr int GEMM_EPI_WARPS = 8;
+constexpr int GEMM_A_STAGE_BYTES = GEMM_BLOCK_M * GEMM_BLOCK_K * 2;
+
+enum { EPI_BIAS = 0, EPI_BIAS_GELU = 1, EPI_BIAS_RESID = 2 };
+
+struct GemmParams {
+  int M, N, K;         // M multiple of 128, N multiple of BLOCK_N, K multiple of 64
+  int nstage;
+  const float* bias;            // [N]
+  const __nv_bfloat16* resid;   // [M, N] (EPI_BIAS_RESID)
+  __nv_bfloat16* out;           // [M, N]
+};
+
+// exact-erf GELU, x * 0.5 * (1 + erf(x / sqrt 2)); erf by Abramowitz-Stegun 7.1.26
+// (|error| <= 1.5e-7, far below the bf16 rounding of the result).
+B200_DEVINL float gelu_erf(float x) {
+  const float z = fabsf(x) * 0.70710678118654752f;
+  const float t = __frcp_rn(fmaf(0.3275911f, z, 1.0f));
+  float p = fmaf(t, 1.061405429f, -1.453152027f);
+  p = fmaf(t, p, 1.421413741f);
+  p = fmaf(t, p, -0.284496736f);
+  p = fmaf(t, p, 0.254829592f);
+  const float e = 1.0f - p * t * __expf(-z * z);
+  return 0.5f * x * (1.0f + copysignf(e, x));
+}
+
+template <int BLOCK_N, int EPI>
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
+gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
+                 const GemmParams p) {
+  constexpr uint32_t B_STAGE_BYTES = BLOCK_N * GEMM_BLOCK_K * 2;
+  constexpr uint32_t STAGE_BYTES = GEMM_A_STAGE_BYTES + B_STAGE_BYTES;
+  constexpr uint32_t IDESC = umma_idesc_bf16_f32(GEMM_BLOCK_M, BLOCK_N);
+  constexpr uint32_t TMEM_COLS = (2 * BLOCK_N <= 256) ? 256 : 512;
+  constexpr int HALF_N = BLOCK_N / 2;  // columns per epilogue warp
+  static_assert(BLOCK_N % 64 == 0 && BLOCK_N <= 256, "BLOCK_N must be 64..256 in steps of 64");
+
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + (size_t)p.nstage * STAGE_BYTES);
+  uint64_t* full = bars;
+  uint64_t* empty = bars + p.nstage;
+  uint64_t* acc_full = bars + 2 * p.nstage;
+  uint64_t* acc_empty = acc_full + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int n_tiles = p.N / BLOCK_N;
+  const int total_tiles = (p.M / GEMM_BLOCK_M) * n_tiles;
+  const int num_k = p.K / GEMM_BLOCK_K;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&map_a);
+    tma_prefetch_desc(&map_b);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < p.nstage; ++i) {
+      mbar_init(&full[i], 1);
+      mbar_init(&empty[i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&acc_full[i], 1);
+      mbar_init(&acc_empty[i], GEMM_EPI_WARPS);
+    }
+    fence_mbar_init();
+  }
+  if (warp == 2) tmem_alloc(tmem_slot, TMEM_COLS);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      int s = 0;
+      uint32_t ph = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        const int m0 = (tile / n_tiles) * GEMM_BLOCK_M;
+        const int n0 = (tile % n_tiles) * BLOCK_N;
+        for (int kb = 0; kb < num_k; ++kb) {
+          mbar_wait(&empty[s], ph ^ 1);
+          mbar_arrive_expect_tx(&full[s], STAGE_BYTES);
+          uint8_t* sa = smem + (size_t)s * STAGE_BYTES;
+          tma_load_2d(sa, &map_a, &full[s], kb * GEMM_BLOCK_K, m0);
+          tma_load_2d(sa + GEMM_A_STAGE_BYTES, &map_b, &full[s], kb * GEMM_BLOCK_K, n0);
+          if (++s == p.nstage) { s = 0; ph ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      int s = 0;
+      uint32_t ph = 0, it = 0;
+      const uint32_t smem_addr = smem_u32(smem);
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
+        const uint32_t as = it & 1, aph = (it >> 1) & 1;
+        mbar_wait(&acc_empty[as], aph ^ 1);
+        tc_fence_after();
+        const uint32_t tacc = tmem_base + as * BLOCK_N;
+        for (int kb = 0; kb < num_k; ++kb) {
+          mbar_wait(&full[s], ph);
+          tc_fence_after();
+          const uint32_t a_addr = smem_addr + (uint32_t)s * STAGE_BYTES;
+          const uint64_t da = umma_smem_desc_sw128(a_addr);
+          const uint64_t db = umma_smem_desc_sw128(a_addr + GEMM_A_STAGE_BYTES);
+#pragma unroll
+          for (int k = 0; k < GEMM_BLOCK_K / 16; ++k)
+            umma_bf16(tacc, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), IDESC, (uint32_t)((kb | k) != 0));
+          umma_commit(&empty[s]);
+          if (++s == p.nstage) { s = 0; ph ^= 1; }
+        }
+        umma_commit(&acc_full[as]);
+      }
+    }
+  } else if (warp >= 4) {
+    const int e = warp - 4;
+    const int wq = e & 3;        // TMEM lane group (= warp index % 4)
+    const int half = e >> 2;     // which half of the tile's columns
+    uint32_t it = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
+      const uint32_t as = it & 1, aph = (it >> 1) & 1;
+      const int m = (tile / n_tiles) * GEMM_BLOCK_M + wq * 32 + lane;
+      const int n0 = (tile % n_tiles) * BLOCK_N + half * HALF_N;
+      mbar_wait(&acc_full[as], aph);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + ((uint32_t)(wq * 32) << 16) + as * BLOCK_N + half * HALF_N;
+      __nv_bfloat16* orow = p.out + (size_t)m * p.N + n0;
+      const __nv_bfloat16* rrow = (EPI == EPI_BIAS_RESID) ? p.resid + (size_t)m * p.N + n0 : nullptr;
+#pragma unroll 1
+      for (int c = 0; c < HALF_N / 32; ++c) {
+        uint32_t v[32];
+        tmem_ld32(taddr + c * 32, v);
+        tmem_ld_wait();
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {  // 8 columns -> one 16-byte store
+          const float4 b0 = __ldg(reinterpret_cast<const float4*>(p.bias + n0 + c * 32 + g * 8));
+          const float4 b1 = __ldg(reinterpret_cast<const float4*>(p.bias + n0 + c * 32 + g * 8 + 4));
+          float f[8];
+          f[0] = __uint_as_float(v[g * 8 + 0]) + b0.x; f[1] = __uint_as_float(v[g * 8 + 1]) + b0.y;
+          f[2] = __uint_as_float(v[g * 8 + 2]) + b0.z; f[3] = __uint_as_float(v[g * 8 + 3]) + b0.w;
+          f[4] = __uint_as_float(v[g * 8 + 4]) + b1.x; f[5] = __uint_as_float(v[g * 8 + 5]) + b1.y;
+          f[6] = __uint_as_float(v[g * 8 + 6]) + b1.z; f[7] = __uint_as_float(v[g * 8 + 7]) + b1.w;
+          if (EPI == EPI_BIAS_GELU) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) f[j] = gelu_erf(f[j]);
+          }
+          if (EPI == EPI_BIAS_RESID) {
+            const uint4 r = *reinterpret_cast<const uint4*>(rrow + c * 32 + g * 8);
+            const __nv_bfloat162* r2 = reinterpret_cast<const __nv_bfloat162*>(&r);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              f[2 * j] += __low2float(r2[j]);
+              f[2 * j + 1] += __high2float(r2[j]);
+            }
+          }
+          uint4 o;
+          __nv_bfloat162 t0 = __floats2bfloat162_rn(f[0], f[1]);
+          __nv_bfloat162 t1 = __floats2bfloat162_rn(f[2], f[3]);
+          __nv_bfloat162 t2 = __floats2bfloat162_rn(f[4], f[5]);
+          __nv_bfloat162 t3 = __floats2bfloat162_rn(f[6], f[7]);
+          o.x = *reinterpret_cast<uint32_t*>(&t0); o.y = *reinterpret_cast<uint32_t*>(&t1);
+          o.z = *reinterpret_cast<uint32_t*>(&t2); o.w = *reinterpret_cast<uint32_t*>(&t3);
+          *reinterpret_cast<uint4*>(orow + c * 32 + g * 8) = o;
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&acc_empty[as]);
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, TMEM_COLS);
+  }
+}
+
+// =============================================================================================
+// K3: attention for one (sequence, head) per CTA.  8 warps; K and V^T of the head sit in shared
+// memory; each warp owns 16 query rows per pass and walks the keys in blocks of 64 with an online
+// softmax (fp32), QK^T and PV on mma.sync m16n8k16 bf16 tiles.  qkv is [tokens, 3H] with columns
+// [Q | K | V], head h at offset h*DH inside each third; ctx is [tokens, H].
+// =============================================================================================
+B200_DEVINL void mma_bf16_16816(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+  asm volatile(
+      "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+      : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+      : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+B200_DEVINL uint32_t pack_bf16(float lo, float hi) {
+  __nv_bfloat162 t = __floats2bfloat162_rn(lo, hi);
+  return *reinterpret_cast<uint32_t*>(&t);
+}
+
+template <int DH>
+__global__ void __launch_bounds__(256) attention_kernel(const __nv_bfloat16* __restrict__ qkv,
+                                                        const int32_t* __restrict__ lens, int S, int H,
+                                                        __nv_bfloat16* __restrict__ ctx, int vt_stride) {
+  constexpr int KSTR = DH + 8;          // K row stride (elements): conflict-free 32-bit fragment reads
+  constexpr int KSTEPS = DH / 16;       // k-steps of QK^T
+  constexpr int ONT = DH / 8;           // output n-tiles
+  extern __shared__ __align__(16) uint8_t att_smem[];
+  __nv_bfloat16* Ks = reinterpret_cast<__nv_bfloat16*>(att_smem);   // [S][KSTR]
+  __nv_bfloat16* Vt = Ks + (size_t)S * KSTR;                         // [DH][vt_stride]
+
+  const int h = blockIdx.x, b = blockIdx.y;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int len = max(1, min(lens[b], S));
+  const int len16 = (len + 15) & ~15;
+  const size_t tok0 = (size_t)b * S;
+  const int ld = 3 * H;
+
+  // stage K (row-major) and V (transposed) for keys [0, len16); keys >= len are zero-filled
+  constexpr int PIECES = DH / 8;  // 16-byte pieces per row
+  for (int i = threadIdx.x; i < len16 * PIECES; i += blockDim.x) {
+    const int t = i / PIECES, pc = i % PIECES;
+    uint4 kv = make_uint4(0, 0, 0, 0), vv = make_uint4(0, 0, 0, 0);
+    if (t < len) {
+      const __nv_bfloat16* base = qkv + (tok0 + t) * ld + h * DH + pc * 8;
+      kv = *reinterpret_cast<const uint4*>(base + H);
+      vv = *reinterpret_cast<const uint4*>(base + 2 * H);
+    }
+    *reinterpret_cast<uint4*>(Ks + (size_t)t * KSTR + pc * 8) = kv;
+    const __nv_bfloat16* ve = reinterpret_cast<const __nv_bfloat16*>(&vv);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) Vt[(size_t)(pc * 8 + j) * vt_stride + t] = ve[j];
+  }
+  __syncthreads();
+
+  const float scale_log2 = rsqrtf((float)DH) * 1.4426950408889634f;
+  const int r = lane >> 2, cq = (lane & 3) * 2;
+
+  for (int q0 = warp * 16; q0 < S; q0 += 8 * 16) {
+    // Q fragments for this warp's 16 rows
+    uint32_t qa[KSTEPS][4];
+    {
+      const __nv_bfloat16* q_lo = qkv + (tok0 + q0 + r) * ld + h * DH;
+      const __nv_bfloat16* q_hi = q_lo + (size_t)8 * ld;
+#pragma unroll
+      for (int ks = 0; ks < KSTEPS; ++ks) {
+        qa[ks][0] = *reinterpret_cast<const uint32_t*>(q_lo + ks * 16 + cq);
+        qa[ks][1] = *reinterpret_cast<const uint32_t*>(q_hi + ks * 16 + cq);
+        qa[ks][2] = *reinterpret_cast<const uint32_t*>(q_lo + ks * 16 + 8 + cq);
+        qa[ks][3] = *reinterpret_cast<const uint32_t*>(q_hi + ks * 16 + 8 + cq);
+      }
+    }
+    float o[ONT][4];
+#pragma unroll
+    for (int i = 0; i < ONT; ++i) o[i][0] = o[i][1] = o[i][2] = o[i][3] = 0.f;
+    float m_lo = -INFINITY, m_hi = -INFINITY, l_lo = 0.f, l_hi = 0.f;
+
+    for (int kb = 0; kb < len16; kb += 64) {
+      const int nkt = min(8, (len16 - kb) >> 3);  // 8-key tiles in this block (even: len16 % 16 == 0)
+      float s[8][4];
+#pragma unroll
+      for (int nt = 0; nt < 8; ++nt) {
+        s[nt][0] = s[nt][1] = s[nt][2] = s[nt][3] = 0.f;
+        if (nt < nkt) {
+          const __nv_bfloat16* kr = Ks + (size_t)(kb + nt * 8 + r) * KSTR + cq;
+#pragma unroll
+          for (int ks = 0; ks < KSTEPS; ++ks)
+            mma_bf16_16816(s[nt], qa[ks], *reinterpret_cast<const uint32_t*>(kr + ks * 16),
+                           *reinterpret_cast<const uint32_t*>(kr + ks * 16 + 8));
+        }
+      }
+      // scale into the log2 domain, mask keys >= len, block row max
+      float bm_lo = -INFINITY, bm_hi = -INFINITY;
+#pragma unroll
+      for (int nt = 0; nt < 8; ++nt) {
+        const int key = kb + nt * 8 + cq;
+        const bool v0 = (nt < nkt) && key < len, v1 = (nt < nkt) && key + 1 < len;
+        s[nt][0] = v0 ? s[nt][0] * scale_log2 : -INFINITY;
+        s[nt][1] = v1 ? s[nt][1] * scale_log2 : -INFINITY;
+        s[nt][2] = v0 ? s[nt][2] * scale_log2 : -INFINITY;
+        s[nt][3] = v1 ? s[nt][3] * scale_log2 : -INFINITY;
+        bm_lo = fmaxf(bm_lo, fmaxf(s[nt][0], s[nt][1]));
+        bm_hi = fmaxf(bm_hi, fmaxf(s[nt][2], s[nt][3]));
+      }
+      bm_lo = fmaxf(bm_lo, __shfl_xor_sync(0xffffffffu, bm_lo, 1));
+      bm_lo = fmaxf(bm_lo, __shfl_xor_sync(0xffffffffu, bm_lo, 2));
+      bm_hi = fmaxf(bm_hi, __shfl_xor_sync(0xffffffffu, bm_hi, 1));
+      bm_hi = fmaxf(bm_hi, __shfl_xor_sync(0xffffffffu, bm_hi, 2));
+      const float mn_lo = fmaxf(m_lo, bm_lo), mn_hi = fmaxf(m_hi, bm_hi);  // finite: key 0 is always valid
+      const float al_lo = exp2f(m_lo - mn_lo), al_hi = exp2f(m_hi - mn_hi);
+      m_lo = mn_lo; m_hi = mn_hi;
+      l_lo *= al_lo; l_hi *= al_hi;
+#pragma unroll
+      for (int i = 0; i < ONT; ++i) { o[i][0] *= al_lo; o[i][1] *= al_lo; o[i][2] *= al_hi; o[i][3] *= al_hi; }
+      // P = exp2(s - m) and PV; P is rounded to bf16 once and the same rounded values feed the
+      // row sums, so numerator and denominator stay consistent
+      uint32_t pa[4][4];
+#pragma unroll
+      for (int nt = 0; nt < 8; ++nt) {
+        const float p0 = exp2f(s[nt][0] - m_lo), p1 = exp2f(s[nt][1] - m_lo);
+        const float p2 = exp2f(s[nt][2] - m_hi), p3 = exp2f(s[nt][3] - m_hi);
+        const uint32_t u_lo = pack_bf16(p0, p1), u_hi = pack_bf16(p2, p3);
+        const __nv_bfloat162 b_lo = *reinterpret_cast<const __nv_bfloat162*>(&u_lo);
+        const __nv_bfloat162 b_hi = *reinterpret_cast<const __nv_bfloat162*>(&u_hi);
+        l_lo += __low2float(b_lo) + __high2float(b_lo);
+        l_hi += __low2float(b_hi) + __high2float(b_hi);
+        pa[nt >> 1][(nt & 1) * 2 + 0] = u_lo;
+        pa[nt >> 1][(nt & 1) * 2 + 1] = u_hi;
+      }
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        if (j * 2 < nkt) {
+#pragma unroll
+          for (int i = 0; i < ONT; ++i) {
+            const __nv_bfloat16* vr = Vt + (size_t)(i * 8 + r) * vt_stride + kb + j * 16 + cq;
+            mma_bf16_16816(o[i], pa[j], *reinterpret_cast<const uint32_t*>(vr),
+                           *reinterpret_cast<const uint32_t*>(vr + 8));
+          }
+        }
+      }
+    }
+    l_lo += __shfl_xor_sync(0xffffffffu, l_lo, 1);
+    l_lo += __shfl_xor_sync(0xffffffffu, l_lo, 2);
+    l_hi += __shfl_xor_sync(0xffffffffu, l_hi, 1);
+    l_hi += __shfl_xor_sync(0xffffffffu, l_hi, 2);
+    const float inv_lo = 1.0f / l_lo, inv_hi = 1.0f / l_hi;
+    __nv_bfloat16* c_lo = ctx + (tok0 + q0 + r) * H + h * DH + cq;
+    __nv_bfloat16* c_hi = c_lo + (size_t)8 * H;
+#pragma unroll
+    for (int i = 0; i < ONT; ++i) {
+      *reinterpret_cast<uint32_t*>(c_lo + i * 8) = pack_bf16(o[i][0] * inv_lo, o[i][1] * inv_lo);
+      *reinterpret_cast<uint32_t*>(c_hi + i * 8) = pack_bf16(o[i][2] * inv_hi, o[i][3] * inv_hi);
+    }
+  }
+}
+
+// =============================================================================================
+// K7: masked mean over the valid tokens, then x / max(||x||, 1e-12).  One CTA per sequence,
+// thread t owns features t, t+blockDim, ...
+// =============================================================================================
+__global__ void __launch_bounds__(256) pool_normalize_kernel(const __nv_bfloat16* __restrict__ x,
+                                                             const int32_t* __restrict__ lens, int S, int H,
+                                                             float* __restrict__ out) {
+  __shared__ float red[8];
+  const int b = blockIdx.x;
+  const int len = max(0, min(lens[b], S));
+  const float denom = fmaxf((float)len, 1e-9f);
+  float acc[4] = {0.f, 0.f, 0.f, 0.f};  // H <= 1024 with 256 threads
+  float ss = 0.f;
+  for (int k = 0, c = threadIdx.x; c < H; c += blockDim.x, ++k) {
+    float a = 0.f;
+    const __nv_bfloat16* col = x + (size_t)b * S * H + c;
+    for (int t = 0; t < len; ++t) a += __bfloat162float(col[(size_t)t * H]);
+    a /= denom;
+    acc[k] = a;
+    ss = fmaf(a, a, ss);
+  }
+  ss = warp_sum(ss);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = ss;
+  __syncthreads();
+  float tot = 0.f;
+  for (int i = 0; i < (int)(blockDim.x >> 5); ++i) tot += red[i];
+  const float inv = 1.0f / fmaxf(sqrtf(tot), 1e-12f);
+  for (int k = 0, c = threadIdx.x; c < H; c += blockDim.x, ++k) out[(size_t)b * H + c] = acc[k] * inv;
+}
+
+}  // namespace b200

@@ -100,4 +100,17 @@ int make_tma_2d_bf16(CUtensorMap* out, const void* base, uint64_t rows, uint64_t
 
 int check_device_is_sm100(int device);
 
+// Optional per-kernel timing (off by default): when enabled through b200_profile_enable, each
+// launch site brackets its kernel with a pair of CUDA events on the launching stream;
+// b200_profile_read aggregates elapsed time, launch count and the caller-stated algorithmic
+// flops / bytes per kernel name.  Used by bench.py for the roofline figures.
+bool prof_enabled();
+struct ProfScope {
+  int slot = -1;
+  cudaStream_t st;
+  ProfScope(const char* name, double flops, double bytes, cudaStream_t st);
+  ~ProfScope();
+};
+#define B200_PROF(name, flops, bytes, st) ::b200::ProfScope _prof_scope_##__LINE__(name, flops, bytes, st)
+
 }  // namespace b200

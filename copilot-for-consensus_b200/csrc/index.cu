@@ -81,6 +81,33 @@ int check_device_is_sm100(int device) {
   return B200_OK;
 }
 
+// ---- optional per-kernel timing ----------------------------------------------------------------
+struct ProfRec {
+  const char* name;
+  double flops, bytes;
+  cudaEvent_t a, b;
+};
+static std::mutex g_prof_mu;
+static std::vector<ProfRec> g_prof;
+static bool g_prof_on = false;
+
+bool prof_enabled() { return g_prof_on; }
+
+ProfScope::ProfScope(const char* name, double flops, double bytes, cudaStream_t s) : st(s) {
+  if (!g_prof_on) return;
+  ProfRec r{name, flops, bytes, nullptr, nullptr};
+  if (cudaEventCreate(&r.a) != cudaSuccess || cudaEventCreate(&r.b) != cudaSuccess) return;
+  cudaEventRecord(r.a, st);
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  g_prof.push_back(r);
+  slot = (int)g_prof.size() - 1;
+}
+ProfScope::~ProfScope() {
+  if (slot < 0) return;
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  if (slot < (int)g_prof.size()) cudaEventRecord(g_prof[slot].b, st);
+}
+
 }  // namespace b200
 
 using namespace b200;
@@ -154,7 +181,12 @@ static int launch_sim(b200_index* ix, int nq, int nqt, const CUtensorMap& map_q,
   p.cand_s = ix->cand_s.as<float>(); p.cand_i = ix->cand_i.as<uint32_t>();
   auto kern = sim_topk_kernel<BLOCK_N, KP>;
   B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  kern<<<dim3(nqt, nsplit), SIM_THREADS, smem, st>>>(map_q, map_c, p);
+  {
+    // algorithmic work of one pass: every corpus row read once (768 B at dim 384) and 2*dpad flops
+    // per (query, row) pair
+    B200_PROF("sim_topk", 2.0 * nq * (double)n_rows * ix->dpad, (double)n_rows * ix->dpad * 2.0, st);
+    kern<<<dim3(nqt, nsplit), SIM_THREADS, smem, st>>>(map_q, map_c, p);
+  }
   B200_CUDA(cudaGetLastError());
   *nsplit_out = nsplit;
   return B200_OK;
@@ -194,7 +226,10 @@ static int search_chunk(b200_index* ix, const void* q_dev, int q_dtype, int nq, 
   m.out_ids = ids_dev; m.out_scores = sc_dev; m.out_margin = nullptr;
   const size_t msmem = (size_t)pow2 * 8 + (size_t)((ix->dim + 1) & ~1) * 4 + 64 * 8;
   B200_CUDA(cudaFuncSetAttribute(merge_rescore_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)msmem));
-  merge_rescore_kernel<<<nq, 256, msmem, st>>>(m);
+  {
+    B200_PROF("merge_rescore", 0.0, (double)nq * nsplit * kp * 8.0 + (double)nq * kp * ix->dim * ix->master_elt(), st);
+    merge_rescore_kernel<<<nq, 256, msmem, st>>>(m);
+  }
   B200_CUDA(cudaGetLastError());
   return B200_OK;
 }
@@ -229,6 +264,46 @@ extern "C" {
 
 const char* b200_last_error(void) { return b200::get_error(); }
 int b200_version(void) { return 100; }
+
+int b200_profile_enable(int on) {
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  g_prof_on = on != 0;
+  return B200_OK;
+}
+
+int b200_profile_reset(void) {
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  for (auto& r : g_prof) {
+    cudaEventDestroy(r.a);
+    cudaEventDestroy(r.b);
+  }
+  g_prof.clear();
+  return B200_OK;
+}
+
+int64_t b200_profile_read(char* buf, int64_t cap) {
+  if (!buf || cap <= 0) B200_FAIL(B200_ERR_INVALID, "bad profile buffer");
+  if (cudaDeviceSynchronize() != cudaSuccess) B200_FAIL(B200_ERR_CUDA, "cudaDeviceSynchronize failed in profile_read");
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  struct Agg { const char* name; long n; double ms, flops, bytes; };
+  std::vector<Agg> agg;
+  for (auto& r : g_prof) {
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, r.a, r.b) != cudaSuccess) { cudaGetLastError(); continue; }
+    Agg* a = nullptr;
+    for (auto& x : agg) if (strcmp(x.name, r.name) == 0) a = &x;
+    if (!a) { agg.push_back({r.name, 0, 0, 0, 0}); a = &agg.back(); }
+    a->n += 1; a->ms += ms; a->flops += r.flops; a->bytes += r.bytes;
+  }
+  int64_t off = 0;
+  for (auto& a : agg) {
+    int w = snprintf(buf + off, (size_t)(cap - off), "%s %ld %.6f %.6e %.6e\n", a.name, a.n, a.ms, a.flops, a.bytes);
+    if (w < 0 || off + w >= cap) break;
+    off += w;
+  }
+  buf[std::min(off, cap - 1)] = 0;
+  return off;
+}
 
 int b200_device_count(void) {
   int n = 0;

@@ -123,6 +123,20 @@ int b200_encoder_hidden(const b200_encoder_t* enc);
 int b200_encode(b200_encoder_t* enc, const int32_t* input_ids, const int32_t* lengths, int batch, int seq,
                 int inputs_on_device, float* out, int out_on_device, void* stream);
 
+/* Diagnostics (no reference counterpart): copy the first numel elements of an internal bf16
+ * activation buffer, as left by the last b200_encode call, to a host fp32 buffer.
+ * which: 0 = x (hidden state), 1 = qkv, 2 = ctx (attention output), 3 = y (pre-LayerNorm), 4 = ffn. */
+int b200_encoder_peek(b200_encoder_t* enc, int which, float* out_host, int64_t numel);
+
+/* Optional per-kernel timing (no reference counterpart), used by bench.py for the roofline line.
+ * While enabled, every kernel launch is bracketed by CUDA events on its stream.  profile_read
+ * synchronises the device and writes one line per kernel name into buf:
+ *   "<name> <launches> <total_ms> <algorithmic_flops> <algorithmic_bytes>\n"
+ * and returns the number of characters written. */
+int b200_profile_enable(int on);
+int b200_profile_reset(void);
+int64_t b200_profile_read(char* buf, int64_t cap);
+
 #ifdef __cplusplus
 }
 #endif

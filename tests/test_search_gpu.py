@@ -172,7 +172,7 @@ def test_error_contract_and_edge_cases(vs):
     st.add_embedding("z", [1.0, 2.0], {})              # a cleared store accepts a new dimension
     assert st.query([1.0, 2.0])[0].id == "z"
     with pytest.raises(RuntimeError, match="limit"):
-        st.query([1.0, 2.0], top_k=49)
+        st.query_batch(np.ones((1, 2), np.float32), top_k=49)
 
 
 def test_factory_dispatch(vs):
