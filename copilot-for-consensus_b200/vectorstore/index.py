@@ -1,0 +1,104 @@
+"""B200Index -- thin array-level wrapper over the ``b200_index_*`` C ABI.
+
+Rows are addressed by position (insertion order); no string ids, no metadata.  This is what the
+benchmarks and the row-sharded multi-GPU search drive directly; :class:`B200VectorStore` adds the
+reference's id/metadata/exception contract on top of the same calls."""
+from __future__ import annotations
+
+import ctypes
+from typing import Any
+
+import numpy as np
+
+from .. import _native as nat
+
+
+class B200Index:
+    def __init__(self, dim: int, device: str | int = "cuda:0", master_dtype: str = "float32", capacity: int = 4096):
+        if master_dtype not in ("float32", "bfloat16"):
+            raise ValueError("master_dtype must be 'float32' or 'bfloat16'")
+        self.dim = int(dim)
+        self.device = nat.device_index(device)
+        self.master_bf16 = master_dtype == "bfloat16"
+        self._lib = nat.lib()
+        self._h = ctypes.c_void_p()
+        nat.check(self._lib.b200_index_create(self.dim, int(capacity), self.device,
+                                              nat.MASTER_BF16 if self.master_bf16 else nat.MASTER_F32, ctypes.byref(self._h)))
+
+    def close(self) -> None:
+        if self._h:
+            self._lib.b200_index_destroy(self._h)
+            self._h = ctypes.c_void_p()
+
+    def __del__(self) -> None:  # pragma: no cover
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _stream(self) -> ctypes.c_void_p:
+        return ctypes.c_void_p(nat.current_stream_ptr(self.device))
+
+    def __len__(self) -> int:
+        return int(self._lib.b200_index_count(self._h))
+
+    def add(self, rows: Any) -> None:
+        """Append ``[n, dim]`` rows: a CUDA tensor on this GPU (fp32, or bf16 for bf16-master indexes)
+        or a host array (fp32; converted to bf16 first for bf16-master indexes)."""
+        import torch
+
+        if isinstance(rows, torch.Tensor) and rows.is_cuda:
+            want = torch.bfloat16 if self.master_bf16 else torch.float32
+            if rows.device.index != self.device or rows.dtype != want or not rows.is_contiguous() or rows.shape[1] != self.dim:
+                raise ValueError(f"device rows must be contiguous {want} [n, {self.dim}] on cuda:{self.device}")
+            nat.check(self._lib.b200_index_add(self._h, ctypes.c_void_p(rows.data_ptr()), rows.shape[0], 1, self._stream()))
+            return
+        a = np.ascontiguousarray(rows.numpy() if isinstance(rows, torch.Tensor) else rows, dtype=np.float32)
+        if a.ndim != 2 or a.shape[1] != self.dim:
+            raise ValueError(f"rows must be [n, {self.dim}]")
+        if self.master_bf16:
+            a = torch.from_numpy(a).to(torch.bfloat16).view(torch.int16).numpy()
+        nat.check(self._lib.b200_index_add(self._h, ctypes.c_void_p(a.ctypes.data), a.shape[0], 0, self._stream()))
+
+    def search(self, queries: Any, k: int = 10, id_base: int = 0):
+        """``(ids[nq, k] int64, scores[nq, k] fp32)``; CUDA tensors in -> CUDA tensors out (asynchronous on
+        torch's current stream), host arrays in -> numpy out."""
+        import torch
+
+        if isinstance(queries, torch.Tensor) and queries.is_cuda:
+            if queries.device.index != self.device or not queries.is_contiguous() or queries.shape[1] != self.dim:
+                raise ValueError(f"device queries must be contiguous [nq, {self.dim}] on cuda:{self.device}")
+            if queries.dtype not in (torch.float32, torch.bfloat16):
+                raise ValueError("device queries must be float32 or bfloat16")
+            nq = queries.shape[0]
+            ids = torch.empty((nq, k), dtype=torch.int64, device=queries.device)
+            sc = torch.empty((nq, k), dtype=torch.float32, device=queries.device)
+            nat.check(self._lib.b200_index_search(
+                self._h, ctypes.c_void_p(queries.data_ptr()), 0 if queries.dtype == torch.float32 else 1, 1, nq, k,
+                id_base, ctypes.c_void_p(ids.data_ptr()), ctypes.c_void_p(sc.data_ptr()), 1, self._stream()))
+            return ids, sc
+        q = np.ascontiguousarray(queries, dtype=np.float32)
+        if q.ndim != 2 or q.shape[1] != self.dim:
+            raise ValueError(f"queries must be [nq, {self.dim}]")
+        ids = np.empty((q.shape[0], k), dtype=np.int64)
+        sc = np.empty((q.shape[0], k), dtype=np.float32)
+        nat.check(self._lib.b200_index_search(self._h, ctypes.c_void_p(q.ctypes.data), 0, 0, q.shape[0], k, id_base,
+                                              ctypes.c_void_p(ids.ctypes.data), ctypes.c_void_p(sc.ctypes.data), 0,
+                                              self._stream()))
+        return ids, sc
+
+    def get_rows(self, rows: Any) -> np.ndarray:
+        r = np.ascontiguousarray(rows, dtype=np.int64)
+        out = np.empty((len(r), self.dim), dtype=np.float32)
+        if len(r):
+            nat.check(self._lib.b200_index_get_rows(self._h, ctypes.c_void_p(r.ctypes.data), len(r),
+                                                    ctypes.c_void_p(out.ctypes.data), 0, self._stream()))
+        return out
+
+    def remove_rows(self, rows: Any) -> None:
+        r = np.ascontiguousarray(sorted(set(int(x) for x in rows)), dtype=np.int64)
+        if len(r):
+            nat.check(self._lib.b200_index_remove_rows(self._h, ctypes.c_void_p(r.ctypes.data), len(r), self._stream()))
+
+    def clear(self) -> None:
+        nat.check(self._lib.b200_index_clear(self._h))

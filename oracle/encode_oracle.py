@@ -164,6 +164,36 @@ def encode(cfg: EncoderConfig, w: dict[str, torch.Tensor], input_ids: torch.Tens
     return pool_normalize(hidden_states(cfg, w, input_ids, attention_mask), attention_mask)
 
 
+@torch.no_grad()
+def encode_fast(cfg: EncoderConfig, w: dict[str, torch.Tensor], input_ids: torch.Tensor,
+                attention_mask: torch.Tensor) -> torch.Tensor:
+    """Same arithmetic as :func:`encode`, written with the fused torch.nn.functional ops that
+    transformers' BertModel (sdpa attention) and therefore sentence-transformers run on CPU.  This
+    is the variant bench.py TIMES as the reference's CPU encode; tests pin it to :func:`encode`."""
+    import torch.nn.functional as F
+
+    ids = input_ids.long()
+    B, S = ids.shape
+    H, nh, dh = cfg.hidden, cfg.heads, cfg.head_dim
+    x = (F.embedding(ids, w["embeddings.word_embeddings.weight"])
+         + w["embeddings.position_embeddings.weight"][:S][None]
+         + w["embeddings.token_type_embeddings.weight"][0][None, None])
+    x = F.layer_norm(x, (H,), w["embeddings.LayerNorm.weight"], w["embeddings.LayerNorm.bias"], cfg.ln_eps)
+    keep = attention_mask.bool()[:, None, None, :]
+    for l in range(cfg.layers):
+        p = f"encoder.layer.{l}."
+        q = F.linear(x, w[p + "attention.self.query.weight"], w[p + "attention.self.query.bias"]).view(B, S, nh, dh).transpose(1, 2)
+        k = F.linear(x, w[p + "attention.self.key.weight"], w[p + "attention.self.key.bias"]).view(B, S, nh, dh).transpose(1, 2)
+        v = F.linear(x, w[p + "attention.self.value.weight"], w[p + "attention.self.value.bias"]).view(B, S, nh, dh).transpose(1, 2)
+        ctx = F.scaled_dot_product_attention(q, k, v, attn_mask=keep).transpose(1, 2).reshape(B, S, H)
+        x = F.layer_norm(F.linear(ctx, w[p + "attention.output.dense.weight"], w[p + "attention.output.dense.bias"]) + x,
+                         (H,), w[p + "attention.output.LayerNorm.weight"], w[p + "attention.output.LayerNorm.bias"], cfg.ln_eps)
+        h = F.gelu(F.linear(x, w[p + "intermediate.dense.weight"], w[p + "intermediate.dense.bias"]))
+        x = F.layer_norm(F.linear(h, w[p + "output.dense.weight"], w[p + "output.dense.bias"]) + x,
+                         (H,), w[p + "output.LayerNorm.weight"], w[p + "output.LayerNorm.bias"], cfg.ln_eps)
+    return pool_normalize(x, attention_mask)
+
+
 def synthetic_tokens(batch: int, seq: int, vocab: int = 30522, seed: int = 0, ragged: bool = False):
     """SURVEY.md section 8d synthetic chunks: ids ~ U{1000..vocab-1}, [CLS]=101 first, [SEP]=102
     last valid token; ``ragged`` draws lengths ~ U{32..seq} and pads with id 0 / mask 0."""

@@ -1,0 +1,159 @@
+"""Parity of the CUDA encoder with the fp32 oracle and with golden outputs generated from the
+reference's in-tree transformer provider / installed transformers.BertModel.
+
+Tolerance (BASELINE.json north_star): cosine >= 0.999 and max-abs <= 1e-2 against the fp32
+output; the GPU path computes with bf16 operands and fp32 accumulation."""
+import tempfile
+
+import numpy as np
+import pytest
+
+from conftest import pkg
+from oracle import encode_oracle as eo
+
+pytestmark = pytest.mark.gpu
+torch = pytest.importorskip("torch")
+
+COS_MIN = 0.999
+MAXABS = 1e-2
+
+
+def _check(got: np.ndarray, ref: np.ndarray):
+    assert got.shape == ref.shape and np.isfinite(got).all()
+    cos = (got * ref).sum(1) / (np.linalg.norm(got, axis=1) * np.linalg.norm(ref, axis=1))
+    assert cos.min() >= COS_MIN, f"min cosine {cos.min()}"
+    assert np.abs(got - ref).max() <= MAXABS, f"max abs err {np.abs(got - ref).max()}"
+    np.testing.assert_allclose(np.linalg.norm(got, axis=1), 1.0, atol=1e-5)   # L2-normalised output
+
+
+def _provider(arch_or_cfg, seed=0):
+    mio, prov = pkg("embedding.model_io"), pkg("embedding.provider")
+    with tempfile.TemporaryDirectory() as td:
+        mio.write_random_model(td, arch_or_cfg, seed=seed)
+        return prov.B200SentenceTransformerProvider(model_name=td, device="cuda:0")
+
+
+@pytest.fixture(scope="module")
+def minilm():
+    p = _provider("all-MiniLM-L6-v2", seed=0)
+    yield p
+    p.close()
+
+
+@pytest.fixture(scope="module")
+def minilm_weights():
+    return eo.make_weights(eo.MINILM_L6, seed=0)
+
+
+def test_hf_bertmodel_golden(minilm, encode_golden):
+    g = encode_golden
+    lens = g["hf_mask"].sum(1).astype(np.int32)
+    got = minilm.embed_tokens(g["hf_input_ids"].astype(np.int32), lens)
+    _check(got, g["hf_embeddings"])
+
+
+def test_reference_provider_golden_text_path(minilm, encode_golden):
+    """Text in, vector out, against huggingface_provider.py:71-103 run on the same model files."""
+    g = encode_golden
+    for i, t in enumerate(g["ref_texts"]):
+        v = np.array(minilm.embed(str(t)), dtype=np.float32)
+        assert v.shape == (384,)
+        _check(v[None], g["ref_embeddings"][i : i + 1])
+    batch = minilm.embed_array([str(t) for t in g["ref_texts"]])
+    _check(batch, g["ref_embeddings"])
+
+
+@pytest.mark.parametrize("B,S,ragged", [(8, 256, False), (33, 256, True), (5, 64, True), (1, 16, False), (3, 128, True)])
+def test_minilm_matches_fp32_oracle(minilm, minilm_weights, B, S, ragged):
+    ids, mask, lens = eo.synthetic_tokens(B, S, 30522, seed=B * 1000 + S, ragged=ragged)
+    got = minilm.embed_tokens(ids.numpy(), lens.numpy())
+    ref = eo.encode(eo.MINILM_L6, minilm_weights, ids, mask).numpy()
+    _check(got, ref)
+
+
+def test_device_tensors_and_determinism(minilm, minilm_weights):
+    ids, mask, lens = eo.synthetic_tokens(16, 256, 30522, seed=7, ragged=True)
+    d_ids, d_lens = ids.cuda().contiguous(), lens.cuda().contiguous()
+    a = minilm.embed_tokens(d_ids, d_lens)
+    b = minilm.embed_tokens(d_ids, d_lens)
+    torch.cuda.synchronize()
+    assert a.is_cuda and a.dtype == torch.float32 and torch.equal(a, b)       # bit-reproducible
+    _check(a.cpu().numpy(), eo.encode(eo.MINILM_L6, minilm_weights, ids, mask).numpy())
+    # padding must not leak: a row encoded alone equals the same row inside a padded batch
+    n = int(lens[3])
+    n16 = -(-n // 16) * 16
+    solo_ids = torch.zeros((1, n16), dtype=torch.int32)
+    solo_ids[0, :n] = ids[3, :n]
+    solo = minilm.embed_tokens(solo_ids.numpy(), np.array([n], np.int32))
+    np.testing.assert_allclose(solo[0], a[3].cpu().numpy(), atol=2e-3)
+
+
+def test_embed_contract(minilm):
+    """sentence_transformer_provider.py:88-91 and the attributes its tests assert."""
+    with pytest.raises(ValueError, match="Text cannot be None"):
+        minilm.embed(None)
+    with pytest.raises(ValueError, match="empty or whitespace-only"):
+        minilm.embed("   \n")
+    with pytest.raises(ValueError, match="empty or whitespace-only"):
+        minilm.embed_batch(["fine", ""])
+    v = minilm.embed("test")
+    assert isinstance(v, list) and len(v) == 384 and all(isinstance(x, float) for x in v)
+    assert minilm.dimension == 384 and minilm.device == "cuda:0" and minilm.cache_dir is None
+    out = minilm.embed_batch(["ba be bi", "bo bu " * 400, "ca"])
+    assert len(out) == 3 and all(len(r) == 384 for r in out)
+    np.testing.assert_allclose(np.array(out[0]), np.array(minilm.embed("ba be bi")), atol=2e-3)
+    assert minilm.embed_batch([]) == []
+
+
+def test_small_architectures_head_dims():
+    mio = pkg("embedding.model_io")
+    for hidden, heads, inter, S in [(128, 4, 256, 64), (256, 4, 512, 128), (512, 8, 1024, 32)]:
+        cfg = mio.EncoderConfig(vocab_size=2000, hidden=hidden, layers=2, heads=heads, intermediate=inter, max_pos=128,
+                                max_seq_length=128)
+        ocfg = eo.EncoderConfig(vocab_size=2000, hidden=hidden, layers=2, heads=heads, intermediate=inter, max_pos=128)
+        p = _provider(cfg, seed=3)
+        ids, mask, lens = eo.synthetic_tokens(6, S, 2000, seed=hidden, ragged=True)
+        got = p.embed_tokens(ids.numpy(), lens.numpy())
+        _check(got, eo.encode(ocfg, eo.make_weights(ocfg, seed=3), ids, mask).numpy())
+        p.close()
+
+
+@pytest.mark.slow
+def test_mpnet_base_class_matches_fp32_oracle():
+    """BASELINE.json configs[3] architecture: 768-d, 12 layers, 12 heads x 64, seq 384."""
+    p = _provider("all-mpnet-base-v2", seed=0)
+    ids, mask, lens = eo.synthetic_tokens(4, 384, 30522, seed=11, ragged=True)
+    got = p.embed_tokens(ids.numpy(), lens.numpy())
+    _check(got, eo.encode(eo.MPNET_BASE_CLASS, eo.make_weights(eo.MPNET_BASE_CLASS, seed=0), ids, mask).numpy())
+    p.close()
+
+
+@pytest.mark.slow
+def test_full_batch_512x256_properties_and_sampled_oracle(minilm, minilm_weights):
+    """BASELINE.json configs[1] encode half at full size: every row is checked for unit norm and
+    finiteness; a sample of rows is checked against the oracle."""
+    ids, mask, lens = eo.synthetic_tokens(512, 256, 30522, seed=0, ragged=False)
+    got = minilm.embed_tokens(ids.numpy(), lens.numpy())
+    assert got.shape == (512, 384) and np.isfinite(got).all()
+    np.testing.assert_allclose(np.linalg.norm(got, axis=1), 1.0, atol=1e-5)
+    sample = np.arange(0, 512, 64)
+    ref = eo.encode(eo.MINILM_L6, minilm_weights, ids[sample], mask[sample]).numpy()
+    _check(got[sample], ref)
+
+
+def test_factory_routes_cuda_to_b200_provider():
+    emb, cfgm, mio = pkg("embedding"), pkg("config"), pkg("embedding.model_io")
+    with tempfile.TemporaryDirectory() as td:
+        mio.write_random_model(td, mio.EncoderConfig(vocab_size=2000, hidden=128, layers=1, heads=4, intermediate=256,
+                                                     max_pos=64, max_seq_length=64), seed=1)
+        drv = cfgm.DriverConfig_EmbeddingBackend_Sentencetransformers(model_name=td, device="cuda:0", cache_dir=None)
+        p = emb.create_embedding_provider(cfgm.AdapterConfig_EmbeddingBackend(embedding_backend_type="SentenceTransformers", driver=drv))
+        assert isinstance(p, emb.B200SentenceTransformerProvider) and isinstance(p, emb.EmbeddingProvider)
+        assert p.model_name == td and len(p.embed("ba be")) == 128
+        p.close()
+    with pytest.raises(ValueError, match="embedding_backend config is required"):
+        emb.create_embedding_provider(None)
+    with pytest.raises(TypeError, match="DriverConfig_EmbeddingBackend_Sentencetransformers"):
+        emb.create_embedding_provider(cfgm.AdapterConfig_EmbeddingBackend(embedding_backend_type="sentencetransformers", driver=object()))
+    with pytest.raises(ValueError, match="Unknown embedding backend driver"):
+        emb.create_embedding_provider(cfgm.AdapterConfig_EmbeddingBackend(embedding_backend_type="nope", driver=None))
