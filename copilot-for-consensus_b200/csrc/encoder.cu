@@ -181,13 +181,15 @@ static int run_encoder(b200_encoder* e, const int32_t* d_ids, const int32_t* d_l
     // Q,K,V projections in one GEMM: qkv = x Wqkv^T + bqkv
     p.M = M; p.N = 3 * H; p.K = H; p.bias = L->bqkv.as<float>(); p.resid = nullptr; p.out = e->qkv.as<__nv_bfloat16>();
     B200_TRY(launch_gemm<EPI_BIAS>(e, e->map_x, L->map_wqkv, p, st));
-    B200_PROF("attention", 4.0 * batch * (double)seq * seq * H, 2.0 * 4.0 * n_tok * H, st);
-    if (dh == 32)
-      attention_kernel<32><<<dim3(heads, batch), 256, att_smem, st>>>(e->qkv.as<__nv_bfloat16>(), d_lens, seq, H,
-                                                                      e->ctx.as<__nv_bfloat16>(), vt_stride);
-    else
-      attention_kernel<64><<<dim3(heads, batch), 256, att_smem, st>>>(e->qkv.as<__nv_bfloat16>(), d_lens, seq, H,
-                                                                      e->ctx.as<__nv_bfloat16>(), vt_stride);
+    {
+      B200_PROF("attention", 4.0 * batch * (double)seq * seq * H, 2.0 * 4.0 * n_tok * H, st);
+      if (dh == 32)
+        attention_kernel<32><<<dim3(heads, batch), 256, att_smem, st>>>(e->qkv.as<__nv_bfloat16>(), d_lens, seq, H,
+                                                                        e->ctx.as<__nv_bfloat16>(), vt_stride);
+      else
+        attention_kernel<64><<<dim3(heads, batch), 256, att_smem, st>>>(e->qkv.as<__nv_bfloat16>(), d_lens, seq, H,
+                                                                        e->ctx.as<__nv_bfloat16>(), vt_stride);
+    }
     B200_CUDA(cudaGetLastError());
     // y = ctx Wo^T + bo + x ; x = LN(y)
     p.N = H; p.K = H; p.bias = L->bo.as<float>(); p.resid = x; p.out = y;

@@ -72,11 +72,12 @@ class ShardedSearch:
         if self.world == 1:
             return ids, sc
         nq = ids.shape[0]
-        all_ids = torch.empty((self.world, nq, k), dtype=ids.dtype, device=ids.device)
-        all_sc = torch.empty((self.world, nq, k), dtype=sc.dtype, device=sc.device)
+        # gathered along dim 0 ([world*nq, k]); viewed as [world, nq, k], the layout b200_merge_topk takes
+        all_ids = torch.empty((self.world * nq, k), dtype=ids.dtype, device=ids.device)
+        all_sc = torch.empty((self.world * nq, k), dtype=sc.dtype, device=sc.device)
         self._dist.all_gather_into_tensor(all_ids, ids.contiguous(), group=self._group)
         self._dist.all_gather_into_tensor(all_sc, sc.contiguous(), group=self._group)
-        return self._merge(all_ids, all_sc, k)
+        return self._merge(all_ids.view(self.world, nq, k), all_sc.view(self.world, nq, k), k)
 
     def search_local_queries(self, queries: Any, k: int = 10):
         """Each rank passes its OWN ``[nq_local, dim]`` queries (same count on every rank, e.g. the
@@ -89,9 +90,11 @@ class ShardedSearch:
         q_all = torch.empty((self.world * nq, queries.shape[1]), dtype=queries.dtype, device=queries.device)
         self._dist.all_gather_into_tensor(q_all, queries.contiguous(), group=self._group)
         ids, sc = self._search(q_all, k, self.row_offset)               # [world*nq, k] on this shard
-        all_ids = torch.empty((self.world, self.world * nq, k), dtype=ids.dtype, device=ids.device)
-        all_sc = torch.empty((self.world, self.world * nq, k), dtype=sc.dtype, device=sc.device)
+        all_ids = torch.empty((self.world * self.world * nq, k), dtype=ids.dtype, device=ids.device)
+        all_sc = torch.empty((self.world * self.world * nq, k), dtype=sc.dtype, device=sc.device)
         self._dist.all_gather_into_tensor(all_ids, ids.contiguous(), group=self._group)
         self._dist.all_gather_into_tensor(all_sc, sc.contiguous(), group=self._group)
         mine = slice(self.rank * nq, (self.rank + 1) * nq)
+        all_ids = all_ids.view(self.world, self.world * nq, k)
+        all_sc = all_sc.view(self.world, self.world * nq, k)
         return self._merge(all_ids[:, mine, :].contiguous(), all_sc[:, mine, :].contiguous(), k)

@@ -1,0 +1,84 @@
+"""Host-side logic that needs no GPU: factories' error contracts, config stand-ins, model-directory
+I/O, and that constructing the CUDA-backed classes without a GPU fails loudly."""
+import json
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from conftest import pkg
+
+
+def test_vector_store_factory_errors_need_no_gpu():
+    vs, cfgm = pkg("vectorstore"), pkg("config")
+    with pytest.raises(ValueError, match="vector_store config is required"):
+        vs.create_vector_store(None)
+    with pytest.raises(ValueError, match="Unknown vector_store driver: nope"):
+        vs.create_vector_store(cfgm.AdapterConfig_VectorStore(vector_store_type="nope", driver=None))
+    with pytest.raises(TypeError, match="Expected inmemory config, got object"):
+        vs.create_vector_store(cfgm.AdapterConfig_VectorStore(vector_store_type="INMEMORY", driver=object()))
+
+
+def test_embedding_factory_errors_need_no_gpu():
+    emb, cfgm = pkg("embedding"), pkg("config")
+    with pytest.raises(ValueError, match="embedding_backend config is required"):
+        emb.create_embedding_provider(None)
+    with pytest.raises(ValueError, match="Unknown embedding backend driver: nope"):
+        emb.create_embedding_provider(cfgm.AdapterConfig_EmbeddingBackend(embedding_backend_type="nope", driver=None))
+    with pytest.raises(TypeError, match="driver_config must be DriverConfig_EmbeddingBackend_Sentencetransformers"):
+        emb.create_embedding_provider(cfgm.AdapterConfig_EmbeddingBackend(embedding_backend_type="sentencetransformers", driver=object()))
+
+
+def test_config_standins_have_the_reference_defaults():
+    cfgm = pkg("config")
+    d = cfgm.DriverConfig_EmbeddingBackend_Sentencetransformers()
+    assert (d.model_name, d.device, d.cache_dir) == ("all-MiniLM-L6-v2", "cpu", None)   # embedding_backend.py:64-73
+    assert cfgm.DriverConfig_VectorStore_Inmemory() == cfgm.DriverConfig_VectorStore_Inmemory()
+
+
+def test_model_dir_roundtrip(tmp_path):
+    mio = pkg("embedding.model_io")
+    cfg = mio.EncoderConfig(vocab_size=1500, hidden=128, layers=2, heads=4, intermediate=256, max_pos=64, max_seq_length=48)
+    d = mio.write_random_model(str(tmp_path / "m"), cfg, seed=3)
+    assert mio.resolve_model_dir(d, None) == d
+    assert mio.resolve_model_dir("m", str(tmp_path)) == os.path.join(str(tmp_path), "m")
+    assert mio.resolve_model_dir("missing-model", str(tmp_path)) is None
+    cfg2, sd, vocab, lower = mio.load_model_dir(d)
+    assert cfg2 == cfg and lower is True and len(vocab) == 1500
+    want = mio.random_weights(cfg, seed=3)
+    assert sd.keys() == want.keys() and all(torch.equal(sd[k], want[k]) for k in want)
+    hf = json.load(open(os.path.join(d, "config.json")))
+    assert hf["hidden_size"] == 128 and hf["hidden_act"] == "gelu"
+    with pytest.raises(ValueError, match="hidden_act"):
+        mio.config_from_hf({**hf, "hidden_act": "relu"})
+
+
+def test_cuda_backed_classes_fail_loudly_without_gpu(tmp_path):
+    if torch.cuda.is_available():
+        pytest.skip("this check is for the GPU-less build container")
+    mio, prov = pkg("embedding.model_io"), pkg("embedding.provider")
+    d = mio.write_random_model(str(tmp_path / "m"), mio.EncoderConfig(vocab_size=1500, hidden=128, layers=1, heads=4,
+                                                                     intermediate=256, max_pos=64, max_seq_length=48))
+    with pytest.raises(RuntimeError, match="no CPU fallback|CUDA"):
+        prov.B200SentenceTransformerProvider(model_name=d, device="cuda:0")
+    with pytest.raises(ValueError, match="CUDA device"):
+        prov.B200SentenceTransformerProvider(model_name=d, device="cpu")
+    with pytest.raises(RuntimeError, match="not found locally"):
+        prov.B200SentenceTransformerProvider(model_name="all-MiniLM-L6-v2", device="cuda:0", cache_dir=str(tmp_path))
+    with pytest.raises(RuntimeError, match="no CPU fallback|CUDA"):
+        pkg("vectorstore").B200Index(384, device="cuda:0")
+
+
+def test_bench_reference_arm_prints_the_contract_line():
+    import subprocess
+    import sys
+
+    from conftest import ROOT
+
+    out = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--steps", "1", "--warmup", "0"],
+                         capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0, out.stderr[-500:]
+    line = json.loads(out.stdout.strip().splitlines()[-1])
+    assert line["impl"] == "reference" and line["unit"] == "chunks/s" and line["value"] > 0
+    assert line["cpu_baseline"]["kind"] == "port" and line["e2e"]["h2d_bytes_per_step"] == 0
