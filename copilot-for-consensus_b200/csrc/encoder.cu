@@ -62,7 +62,8 @@ struct b200_encoder {
   // activations, sized for m_cap rows
   int64_t m_cap = 0;
   DevBuf x, qkv, ctx, y, ffn, ids, lens, out;
-  CUtensorMap map_x, map_ctx, map_ffn;
+  CUtensorMap map_x, map_ctx, map_ffn;                      // A operands: box {64, 128}
+  CUtensorMap map_qkv_st, map_y_st, map_ffn_st, map_x_res;  // epilogue boxes {64, 32}: stores and the residual load
   std::mutex mu;
   ~b200_encoder() {
     for (auto* l : layers) delete l;
@@ -78,14 +79,24 @@ static int pick_block_n(int N) {
   return 0;
 }
 
+struct GemmIO {
+  const CUtensorMap* a;      // activations [M, K], box {64, 128}
+  const CUtensorMap* w;      // weights [N, K], box {64, BLOCK_N}
+  const CUtensorMap* out;    // output [M, N], box {64, 32} (TMA store)
+  const CUtensorMap* resid;  // residual [M, N], box {64, 32} (TMA load) or the same as out when unused
+};
+
 template <int BLOCK_N, int EPI>
-static int launch_gemm_t(const b200_encoder* e, const CUtensorMap& ma, const CUtensorMap& mb, GemmParams p,
-                         cudaStream_t st) {
+static int launch_gemm_t(const b200_encoder* e, const GemmIO& io, GemmParams p, cudaStream_t st) {
+  constexpr int NEPI = gemm_epi_warps(BLOCK_N);
   const size_t stage = (size_t)GEMM_A_STAGE_BYTES + (size_t)BLOCK_N * GEMM_BLOCK_K * 2;
   const size_t max_smem = 232448;
-  int nstage = (int)std::min<size_t>(8, (max_smem - 1024 - 256) / stage);
+  // staging boxes, barriers (2*nstage + 4 + NEPI, at most 8 stages), TMEM slot, per-warp bias slices
+  const size_t tail = (size_t)NEPI * GEMM_STAGING_BYTES + 8 * (2 * 8 + 4 + NEPI) + 16 + (size_t)NEPI * GEMM_OUT_CHUNK * 4;
+  int nstage = (int)std::min<size_t>(8, (max_smem - 1024 - tail) / stage);
+  if (nstage < 2) B200_FAIL(B200_ERR_UNSUPPORTED, "GEMM tile does not fit in shared memory");
   p.nstage = nstage;
-  const size_t smem = 1024 + (size_t)nstage * stage + 256;
+  const size_t smem = 1024 + (size_t)nstage * stage + tail;
   auto kern = gemm_bf16_kernel<BLOCK_N, EPI>;
   B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const int tiles = (p.M / GEMM_BLOCK_M) * (p.N / BLOCK_N);
@@ -94,19 +105,18 @@ static int launch_gemm_t(const b200_encoder* e, const CUtensorMap& ma, const CUt
     B200_PROF(EPI == EPI_BIAS ? "gemm_bias" : (EPI == EPI_BIAS_GELU ? "gemm_bias_gelu" : "gemm_bias_resid"),
               2.0 * p.M * (double)p.N * p.K,
               2.0 * ((double)p.M * p.K + (double)p.N * p.K + (double)p.M * p.N * (EPI == EPI_BIAS_RESID ? 2 : 1)), st);
-    kern<<<grid, GEMM_THREADS, smem, st>>>(ma, mb, p);
+    kern<<<grid, gemm_threads(BLOCK_N), smem, st>>>(*io.a, *io.w, *io.out, *io.resid, p);
   }
   B200_CUDA(cudaGetLastError());
   return B200_OK;
 }
 
 template <int EPI>
-static int launch_gemm(const b200_encoder* e, const CUtensorMap& ma, const CUtensorMap& mb, const GemmParams& p,
-                       cudaStream_t st) {
+static int launch_gemm(const b200_encoder* e, const GemmIO& io, const GemmParams& p, cudaStream_t st) {
   switch (pick_block_n(p.N)) {
-    case 192: return launch_gemm_t<192, EPI>(e, ma, mb, p, st);
-    case 128: return launch_gemm_t<128, EPI>(e, ma, mb, p, st);
-    case 64: return launch_gemm_t<64, EPI>(e, ma, mb, p, st);
+    case 192: return launch_gemm_t<192, EPI>(e, io, p, st);
+    case 128: return launch_gemm_t<128, EPI>(e, io, p, st);
+    case 64: return launch_gemm_t<64, EPI>(e, io, p, st);
   }
   B200_FAIL(B200_ERR_UNSUPPORTED, "GEMM N=%d is not a multiple of 64", p.N);
 }
@@ -135,15 +145,12 @@ static int ensure_activations(b200_encoder* e, int64_t m_rows, int batch, cudaSt
   B200_TRY(make_tma_2d_bf16(&e->map_x, e->x.p, (uint64_t)m, (uint64_t)H, GEMM_BLOCK_M, GEMM_BLOCK_K));
   B200_TRY(make_tma_2d_bf16(&e->map_ctx, e->ctx.p, (uint64_t)m, (uint64_t)H, GEMM_BLOCK_M, GEMM_BLOCK_K));
   B200_TRY(make_tma_2d_bf16(&e->map_ffn, e->ffn.p, (uint64_t)m, (uint64_t)I, GEMM_BLOCK_M, GEMM_BLOCK_K));
+  B200_TRY(make_tma_2d_bf16(&e->map_qkv_st, e->qkv.p, (uint64_t)m, (uint64_t)(3 * H), 32, GEMM_OUT_CHUNK));
+  B200_TRY(make_tma_2d_bf16(&e->map_y_st, e->y.p, (uint64_t)m, (uint64_t)H, 32, GEMM_OUT_CHUNK));
+  B200_TRY(make_tma_2d_bf16(&e->map_ffn_st, e->ffn.p, (uint64_t)m, (uint64_t)I, 32, GEMM_OUT_CHUNK));
+  B200_TRY(make_tma_2d_bf16(&e->map_x_res, e->x.p, (uint64_t)m, (uint64_t)H, 32, GEMM_OUT_CHUNK));
   e->m_cap = m;
   return B200_OK;
-}
-
-static int vt_stride_for(int S) {
-  // V^T row stride (elements) with (stride/2) % 32 == 4, so 32-bit fragment reads hit 32 banks
-  int words = S / 2;
-  int pad_words = ((4 - (words % 32)) % 32 + 32) % 32;
-  return (words + pad_words) * 2;
 }
 
 static int take(b200_encoder* e, const std::string& name, size_t numel, const std::vector<float>** out) {
@@ -169,8 +176,7 @@ static int run_encoder(b200_encoder* e, const int32_t* d_ids, const int32_t* d_l
       e->type0.as<__nv_bfloat16>(), e->emb_g.as<float>(), e->emb_b.as<float>(), e->cfg.ln_eps, x);
   B200_CUDA(cudaGetLastError());
 
-  const int vt_stride = vt_stride_for(seq);
-  const size_t att_smem = (size_t)seq * (dh + 8) * 2 + (size_t)dh * vt_stride * 2;
+  const size_t att_smem = 2 * (size_t)seq * (dh + 8) * 2;   // K and V tiles, rows padded by 16 bytes
   if (att_smem > 232448) B200_FAIL(B200_ERR_UNSUPPORTED, "sequence length %d needs %zu bytes of shared memory", seq, att_smem);
   if (dh == 32) B200_CUDA(cudaFuncSetAttribute(attention_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)att_smem));
   else B200_CUDA(cudaFuncSetAttribute(attention_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)att_smem));
@@ -179,29 +185,29 @@ static int run_encoder(b200_encoder* e, const int32_t* d_ids, const int32_t* d_l
     LayerWeights* L = e->layers[l];
     GemmParams p{};
     // Q,K,V projections in one GEMM: qkv = x Wqkv^T + bqkv
-    p.M = M; p.N = 3 * H; p.K = H; p.bias = L->bqkv.as<float>(); p.resid = nullptr; p.out = e->qkv.as<__nv_bfloat16>();
-    B200_TRY(launch_gemm<EPI_BIAS>(e, e->map_x, L->map_wqkv, p, st));
+    p.M = M; p.N = 3 * H; p.K = H; p.bias = L->bqkv.as<float>();
+    B200_TRY(launch_gemm<EPI_BIAS>(e, GemmIO{&e->map_x, &L->map_wqkv, &e->map_qkv_st, &e->map_qkv_st}, p, st));
     {
       B200_PROF("attention", 4.0 * batch * (double)seq * seq * H, 2.0 * 4.0 * n_tok * H, st);
       if (dh == 32)
         attention_kernel<32><<<dim3(heads, batch), 256, att_smem, st>>>(e->qkv.as<__nv_bfloat16>(), d_lens, seq, H,
-                                                                        e->ctx.as<__nv_bfloat16>(), vt_stride);
+                                                                        e->ctx.as<__nv_bfloat16>());
       else
         attention_kernel<64><<<dim3(heads, batch), 256, att_smem, st>>>(e->qkv.as<__nv_bfloat16>(), d_lens, seq, H,
-                                                                        e->ctx.as<__nv_bfloat16>(), vt_stride);
+                                                                        e->ctx.as<__nv_bfloat16>());
     }
     B200_CUDA(cudaGetLastError());
     // y = ctx Wo^T + bo + x ; x = LN(y)
-    p.N = H; p.K = H; p.bias = L->bo.as<float>(); p.resid = x; p.out = y;
-    B200_TRY(launch_gemm<EPI_BIAS_RESID>(e, e->map_ctx, L->map_wo, p, st));
+    p.N = H; p.K = H; p.bias = L->bo.as<float>();
+    B200_TRY(launch_gemm<EPI_BIAS_RESID>(e, GemmIO{&e->map_ctx, &L->map_wo, &e->map_y_st, &e->map_x_res}, p, st));
     layernorm_kernel<NV><<<(n_tok + wpb - 1) / wpb, wpb * 32, 0, st>>>(y, n_tok, L->ln1_g.as<float>(), L->ln1_b.as<float>(),
                                                                       e->cfg.ln_eps, x);
     B200_CUDA(cudaGetLastError());
     // ffn = gelu(x W1^T + b1) ; y = ffn W2^T + b2 + x ; x = LN(y)
-    p.N = I; p.K = H; p.bias = L->b1.as<float>(); p.resid = nullptr; p.out = e->ffn.as<__nv_bfloat16>();
-    B200_TRY(launch_gemm<EPI_BIAS_GELU>(e, e->map_x, L->map_w1, p, st));
-    p.N = H; p.K = I; p.bias = L->b2.as<float>(); p.resid = x; p.out = y;
-    B200_TRY(launch_gemm<EPI_BIAS_RESID>(e, e->map_ffn, L->map_w2, p, st));
+    p.N = I; p.K = H; p.bias = L->b1.as<float>();
+    B200_TRY(launch_gemm<EPI_BIAS_GELU>(e, GemmIO{&e->map_x, &L->map_w1, &e->map_ffn_st, &e->map_ffn_st}, p, st));
+    p.N = H; p.K = I; p.bias = L->b2.as<float>();
+    B200_TRY(launch_gemm<EPI_BIAS_RESID>(e, GemmIO{&e->map_ffn, &L->map_w2, &e->map_y_st, &e->map_x_res}, p, st));
     layernorm_kernel<NV><<<(n_tok + wpb - 1) / wpb, wpb * 32, 0, st>>>(y, n_tok, L->ln2_g.as<float>(), L->ln2_b.as<float>(),
                                                                       e->cfg.ln_eps, x);
     B200_CUDA(cudaGetLastError());

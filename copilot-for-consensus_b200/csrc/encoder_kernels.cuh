@@ -112,23 +112,32 @@ __global__ void __launch_bounds__(256) layernorm_kernel(const __nv_bfloat16* __r
 // =============================================================================================
 // GEMM: out[M,N] = epilogue( A[M,K] . W[N,K]^T ), bf16 in, fp32 accumulate in TMEM, bf16 out.
 // Persistent CTAs (one per SM) walk 128 x BLOCK_N output tiles; roles:
-//   warp 0 TMA producer | warp 1 MMA issuer | warp 2 TMEM allocator | warps 4..11 epilogue
+//   warp 0 TMA producer | warp 1 MMA issuer | warp 2 TMEM allocator | warps 4.. epilogue
 // Two TMEM accumulator stages let tile i's epilogue overlap tile i+1's MMAs.
+//
+// Epilogue: one warp per (32-row TMEM lane group, 64-column chunk).  The warp pulls its 32x64 fp32
+// block with ONE tcgen05.ld (x64), hands the accumulator stage back to the MMA warp, applies
+// bias / GELU / residual, packs to bf16 into a 4 KB shared-memory box in the 128-byte-swizzled
+// layout and stores it with ONE TMA store: fully coalesced 128-byte rows, no per-thread global
+// address generation.  The residual tile arrives the same way (TMA load into the same box, added in
+// place).  (A first version stored 16 bytes per thread straight to global memory: 32 different
+// cache lines per instruction, which made the L1/LSU wavefront rate -- not the MMA -- the bound.)
 // =============================================================================================
 constexpr int GEMM_BLOCK_M = 128;
 constexpr int GEMM_BLOCK_K = 64;
-constexpr int GEMM_THREADS = 384;
-constexpr int GEMM_EPI_WARPS = 8;
 constexpr int GEMM_A_STAGE_BYTES = GEMM_BLOCK_M * GEMM_BLOCK_K * 2;
+constexpr int GEMM_OUT_CHUNK = 64;                                  // columns per epilogue warp = 128 B of bf16
+constexpr int GEMM_STAGING_BYTES = 32 * GEMM_OUT_CHUNK * 2;         // 32 rows x 128 B per epilogue warp
+
+constexpr int gemm_epi_warps(int block_n) { return 4 * (block_n / GEMM_OUT_CHUNK); }
+constexpr int gemm_threads(int block_n) { return 128 + 32 * gemm_epi_warps(block_n); }
 
 enum { EPI_BIAS = 0, EPI_BIAS_GELU = 1, EPI_BIAS_RESID = 2 };
 
 struct GemmParams {
   int M, N, K;         // M multiple of 128, N multiple of BLOCK_N, K multiple of 64
   int nstage;
-  const float* bias;            // [N]
-  const __nv_bfloat16* resid;   // [M, N] (EPI_BIAS_RESID)
-  __nv_bfloat16* out;           // [M, N]
+  const float* bias;   // [N]
 };
 
 // GELU(x) = x * Phi(x) (the exact-erf form BERT uses).  Phi is evaluated as
@@ -147,24 +156,28 @@ B200_DEVINL float gelu_erf(float x) {
 }
 
 template <int BLOCK_N, int EPI>
-__global__ void __launch_bounds__(GEMM_THREADS, 1)
+__global__ void __launch_bounds__(gemm_threads(BLOCK_N), 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
+                 const __grid_constant__ CUtensorMap map_out, const __grid_constant__ CUtensorMap map_resid,
                  const GemmParams p) {
   constexpr uint32_t B_STAGE_BYTES = BLOCK_N * GEMM_BLOCK_K * 2;
   constexpr uint32_t STAGE_BYTES = GEMM_A_STAGE_BYTES + B_STAGE_BYTES;
   constexpr uint32_t IDESC = umma_idesc_bf16_f32(GEMM_BLOCK_M, BLOCK_N);
-  constexpr uint32_t TMEM_COLS = (2 * BLOCK_N <= 256) ? 256 : 512;
-  constexpr int HALF_N = BLOCK_N / 2;  // columns per epilogue warp
+  constexpr uint32_t TMEM_COLS = (2 * BLOCK_N <= 128) ? 128 : ((2 * BLOCK_N <= 256) ? 256 : 512);
+  constexpr int NEPI = gemm_epi_warps(BLOCK_N);
   static_assert(BLOCK_N % 64 == 0 && BLOCK_N <= 256, "BLOCK_N must be 64..256 in steps of 64");
 
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + (size_t)p.nstage * STAGE_BYTES);
-  uint64_t* full = bars;
-  uint64_t* empty = bars + p.nstage;
-  uint64_t* acc_full = bars + 2 * p.nstage;
-  uint64_t* acc_empty = acc_full + 2;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
+  uint8_t* staging = smem + (size_t)p.nstage * STAGE_BYTES;                 // [NEPI][4 KB], 1024-aligned
+  uint64_t* bars = reinterpret_cast<uint64_t*>(staging + (size_t)NEPI * GEMM_STAGING_BYTES);
+  uint64_t* full = bars;                       // [nstage]  TMA -> MMA
+  uint64_t* empty = bars + p.nstage;           // [nstage]  MMA -> TMA
+  uint64_t* acc_full = bars + 2 * p.nstage;    // [2]       MMA -> epilogue
+  uint64_t* acc_empty = acc_full + 2;          // [2]       epilogue -> MMA
+  uint64_t* resid_bar = acc_empty + 2;         // [NEPI]    residual box landed (one per epilogue warp)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(resid_bar + NEPI);
+  float* bias_smem = reinterpret_cast<float*>(tmem_slot + 4);               // [NEPI][64]
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -175,6 +188,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&map_a);
     tma_prefetch_desc(&map_b);
+    tma_prefetch_desc(&map_out);
+    if (EPI == EPI_BIAS_RESID) tma_prefetch_desc(&map_resid);
   }
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < p.nstage; ++i) {
@@ -183,8 +198,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&acc_full[i], 1);
-      mbar_init(&acc_empty[i], GEMM_EPI_WARPS);
+      mbar_init(&acc_empty[i], NEPI);
     }
+    for (int i = 0; i < NEPI; ++i) mbar_init(&resid_bar[i], 1);
     fence_mbar_init();
   }
   if (warp == 2) tmem_alloc(tmem_slot, TMEM_COLS);
@@ -194,6 +210,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
+    // ===== TMA producer =====
     if (lane == 0) {
       int s = 0;
       uint32_t ph = 0;
@@ -211,6 +228,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
       }
     }
   } else if (warp == 1) {
+    // ===== MMA issuer (one thread) =====
     if (lane == 0) {
       int s = 0;
       uint32_t ph = 0, it = 0;
@@ -236,60 +254,80 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
       }
     }
   } else if (warp >= 4) {
+    // ===== epilogue warp: TMEM lanes [32 wq, +32) x columns [64 chunk, +64) of every tile =====
     const int e = warp - 4;
-    const int wq = e & 3;        // TMEM lane group (= warp index % 4)
-    const int half = e >> 2;     // which half of the tile's columns
+    const int wq = e & 3;         // == warp % 4: the TMEM lane group this warp may read
+    const int chunk = e >> 2;
+    uint8_t* stg = staging + (size_t)e * GEMM_STAGING_BYTES;
+    float* sbias = bias_smem + e * GEMM_OUT_CHUNK;
+    uint64_t* rbar = &resid_bar[e];
+    uint8_t* my_row = stg + lane * 128;
+    const int sw = lane & 7;       // 128-byte swizzle: 16-byte chunk j of row r lives at chunk j ^ (r % 8)
     uint32_t it = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
       const uint32_t as = it & 1, aph = (it >> 1) & 1;
-      const int m = (tile / n_tiles) * GEMM_BLOCK_M + wq * 32 + lane;
-      const int n0 = (tile % n_tiles) * BLOCK_N + half * HALF_N;
-      mbar_wait(&acc_full[as], aph);
-      tc_fence_after();
-      const uint32_t taddr = tmem_base + ((uint32_t)(wq * 32) << 16) + as * BLOCK_N + half * HALF_N;
-      __nv_bfloat16* orow = p.out + (size_t)m * p.N + n0;
-      const __nv_bfloat16* rrow = (EPI == EPI_BIAS_RESID) ? p.resid + (size_t)m * p.N + n0 : nullptr;
-#pragma unroll 1
-      for (int c = 0; c < HALF_N / 32; ++c) {
-        uint32_t v[32];
-        tmem_ld32(taddr + c * 32, v);
-        tmem_ld_wait();
-#pragma unroll
-        for (int g = 0; g < 4; ++g) {  // 8 columns -> one 16-byte store
-          const float4 b0 = __ldg(reinterpret_cast<const float4*>(p.bias + n0 + c * 32 + g * 8));
-          const float4 b1 = __ldg(reinterpret_cast<const float4*>(p.bias + n0 + c * 32 + g * 8 + 4));
-          float f[8];
-          f[0] = __uint_as_float(v[g * 8 + 0]) + b0.x; f[1] = __uint_as_float(v[g * 8 + 1]) + b0.y;
-          f[2] = __uint_as_float(v[g * 8 + 2]) + b0.z; f[3] = __uint_as_float(v[g * 8 + 3]) + b0.w;
-          f[4] = __uint_as_float(v[g * 8 + 4]) + b1.x; f[5] = __uint_as_float(v[g * 8 + 5]) + b1.y;
-          f[6] = __uint_as_float(v[g * 8 + 6]) + b1.z; f[7] = __uint_as_float(v[g * 8 + 7]) + b1.w;
-          if (EPI == EPI_BIAS_GELU) {
-#pragma unroll
-            for (int j = 0; j < 8; ++j) f[j] = gelu_erf(f[j]);
-          }
-          if (EPI == EPI_BIAS_RESID) {
-            const uint4 r = *reinterpret_cast<const uint4*>(rrow + c * 32 + g * 8);
-            const __nv_bfloat162* r2 = reinterpret_cast<const __nv_bfloat162*>(&r);
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              f[2 * j] += __low2float(r2[j]);
-              f[2 * j + 1] += __high2float(r2[j]);
-            }
-          }
-          uint4 o;
-          __nv_bfloat162 t0 = __floats2bfloat162_rn(f[0], f[1]);
-          __nv_bfloat162 t1 = __floats2bfloat162_rn(f[2], f[3]);
-          __nv_bfloat162 t2 = __floats2bfloat162_rn(f[4], f[5]);
-          __nv_bfloat162 t3 = __floats2bfloat162_rn(f[6], f[7]);
-          o.x = *reinterpret_cast<uint32_t*>(&t0); o.y = *reinterpret_cast<uint32_t*>(&t1);
-          o.z = *reinterpret_cast<uint32_t*>(&t2); o.w = *reinterpret_cast<uint32_t*>(&t3);
-          *reinterpret_cast<uint4*>(orow + c * 32 + g * 8) = o;
+      const int m0 = (tile / n_tiles) * GEMM_BLOCK_M + wq * 32;
+      const int n0 = (tile % n_tiles) * BLOCK_N + chunk * GEMM_OUT_CHUNK;
+      __syncwarp();
+      sbias[lane] = __ldg(p.bias + n0 + lane);
+      sbias[lane + 32] = __ldg(p.bias + n0 + 32 + lane);
+      if (lane == 0) {
+        tma_store_wait_read();   // the previous tile's store has finished reading this warp's box
+        if (EPI == EPI_BIAS_RESID) {
+          mbar_arrive_expect_tx(rbar, GEMM_STAGING_BYTES);
+          tma_load_2d(stg, &map_resid, rbar, n0, m0);
         }
       }
-      tc_fence_before();
+      __syncwarp();
+      mbar_wait(&acc_full[as], aph);
+      tc_fence_after();
+      uint32_t v[64];
+      tmem_ld64(tmem_base + ((uint32_t)(wq * 32) << 16) + as * BLOCK_N + chunk * GEMM_OUT_CHUNK, v);
+      tmem_ld_wait();
+      tc_fence_before();         // this warp's share of the accumulator stage is in registers
       __syncwarp();
       if (lane == 0) mbar_arrive(&acc_empty[as]);
+      if (EPI == EPI_BIAS_RESID) mbar_wait(rbar, it & 1);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {   // 8 columns = one 16-byte piece of this thread's row
+        const float4 b0 = *reinterpret_cast<const float4*>(sbias + j * 8);
+        const float4 b1 = *reinterpret_cast<const float4*>(sbias + j * 8 + 4);
+        float f[8];
+        f[0] = __uint_as_float(v[j * 8 + 0]) + b0.x; f[1] = __uint_as_float(v[j * 8 + 1]) + b0.y;
+        f[2] = __uint_as_float(v[j * 8 + 2]) + b0.z; f[3] = __uint_as_float(v[j * 8 + 3]) + b0.w;
+        f[4] = __uint_as_float(v[j * 8 + 4]) + b1.x; f[5] = __uint_as_float(v[j * 8 + 5]) + b1.y;
+        f[6] = __uint_as_float(v[j * 8 + 6]) + b1.z; f[7] = __uint_as_float(v[j * 8 + 7]) + b1.w;
+        if (EPI == EPI_BIAS_GELU) {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) f[i] = gelu_erf(f[i]);
+        }
+        uint4* slot = reinterpret_cast<uint4*>(my_row + ((j ^ sw) << 4));
+        if (EPI == EPI_BIAS_RESID) {
+          const uint4 r = *slot;
+          const __nv_bfloat162* r2 = reinterpret_cast<const __nv_bfloat162*>(&r);
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            f[2 * i] += __low2float(r2[i]);
+            f[2 * i + 1] += __high2float(r2[i]);
+          }
+        }
+        uint4 o;
+        __nv_bfloat162 t0 = __floats2bfloat162_rn(f[0], f[1]);
+        __nv_bfloat162 t1 = __floats2bfloat162_rn(f[2], f[3]);
+        __nv_bfloat162 t2 = __floats2bfloat162_rn(f[4], f[5]);
+        __nv_bfloat162 t3 = __floats2bfloat162_rn(f[6], f[7]);
+        o.x = *reinterpret_cast<uint32_t*>(&t0); o.y = *reinterpret_cast<uint32_t*>(&t1);
+        o.z = *reinterpret_cast<uint32_t*>(&t2); o.w = *reinterpret_cast<uint32_t*>(&t3);
+        *slot = o;
+      }
+      fence_proxy_async();       // generic-proxy writes -> visible to the TMA (async proxy)
+      __syncwarp();
+      if (lane == 0) {
+        tma_store_2d(&map_out, stg, n0, m0);
+        tma_store_commit();
+      }
     }
+    if (lane == 0) tma_store_wait_all();
   }
 
   tc_fence_before();
@@ -301,10 +339,13 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
 }
 
 // =============================================================================================
-// K3: attention for one (sequence, head) per CTA.  8 warps; K and V^T of the head sit in shared
-// memory; each warp owns 16 query rows per pass and walks the keys in blocks of 64 with an online
-// softmax (fp32), QK^T and PV on mma.sync m16n8k16 bf16 tiles.  qkv is [tokens, 3H] with columns
-// [Q | K | V], head h at offset h*DH inside each third; ctx is [tokens, H].
+// K3: attention for one (sequence, head) per CTA.  8 warps; K and V of the head sit in shared
+// memory (row-major, rows padded by 16 bytes so that ldmatrix phases are bank-conflict free); each
+// warp owns 16 query rows per pass and walks the keys in blocks of 64 with an online softmax (fp32);
+// QK^T and PV run on mma.sync m16n8k16 bf16 tiles whose B fragments come from ldmatrix (.trans for
+// V).  qkv is [tokens, 3H] with columns [Q | K | V], head h at offset h*DH inside each third; ctx
+// is [tokens, H].  Query tiles that lie entirely in the padding are skipped: nothing reads them
+// (padded keys are masked, padded rows are excluded from pooling).
 // =============================================================================================
 B200_DEVINL void mma_bf16_16816(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
   asm volatile(
@@ -312,21 +353,31 @@ B200_DEVINL void mma_bf16_16816(float (&c)[4], const uint32_t (&a)[4], uint32_t 
       : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
       : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
 }
+B200_DEVINL void ldmatrix_x4(uint32_t (&r)[4], const void* smem_row) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
+               : "r"(smem_u32(smem_row)));
+}
+B200_DEVINL void ldmatrix_x4_trans(uint32_t (&r)[4], const void* smem_row) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
+               : "r"(smem_u32(smem_row)));
+}
 B200_DEVINL uint32_t pack_bf16(float lo, float hi) {
   __nv_bfloat162 t = __floats2bfloat162_rn(lo, hi);
   return *reinterpret_cast<uint32_t*>(&t);
 }
 
 template <int DH>
-__global__ void __launch_bounds__(256) attention_kernel(const __nv_bfloat16* __restrict__ qkv,
-                                                        const int32_t* __restrict__ lens, int S, int H,
-                                                        __nv_bfloat16* __restrict__ ctx, int vt_stride) {
-  constexpr int KSTR = DH + 8;          // K row stride (elements): conflict-free 32-bit fragment reads
+__global__ void __launch_bounds__(256, (DH == 32) ? 2 : 1)
+attention_kernel(const __nv_bfloat16* __restrict__ qkv, const int32_t* __restrict__ lens, int S, int H,
+                 __nv_bfloat16* __restrict__ ctx) {
+  constexpr int KSTR = DH + 8;          // row stride (elements) of the K and V tiles
   constexpr int KSTEPS = DH / 16;       // k-steps of QK^T
   constexpr int ONT = DH / 8;           // output n-tiles
   extern __shared__ __align__(16) uint8_t att_smem[];
   __nv_bfloat16* Ks = reinterpret_cast<__nv_bfloat16*>(att_smem);   // [S][KSTR]
-  __nv_bfloat16* Vt = Ks + (size_t)S * KSTR;                         // [DH][vt_stride]
+  __nv_bfloat16* Vs = Ks + (size_t)S * KSTR;                         // [S][KSTR]
 
   const int h = blockIdx.x, b = blockIdx.y;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -335,7 +386,7 @@ __global__ void __launch_bounds__(256) attention_kernel(const __nv_bfloat16* __r
   const size_t tok0 = (size_t)b * S;
   const int ld = 3 * H;
 
-  // stage K (row-major) and V (transposed) for keys [0, len16); keys >= len are zero-filled
+  // stage K and V for keys [0, len16); keys >= len are zero-filled (and masked below)
   constexpr int PIECES = DH / 8;  // 16-byte pieces per row
   for (int i = threadIdx.x; i < len16 * PIECES; i += blockDim.x) {
     const int t = i / PIECES, pc = i % PIECES;
@@ -346,16 +397,15 @@ __global__ void __launch_bounds__(256) attention_kernel(const __nv_bfloat16* __r
       vv = *reinterpret_cast<const uint4*>(base + 2 * H);
     }
     *reinterpret_cast<uint4*>(Ks + (size_t)t * KSTR + pc * 8) = kv;
-    const __nv_bfloat16* ve = reinterpret_cast<const __nv_bfloat16*>(&vv);
-#pragma unroll
-    for (int j = 0; j < 8; ++j) Vt[(size_t)(pc * 8 + j) * vt_stride + t] = ve[j];
+    *reinterpret_cast<uint4*>(Vs + (size_t)t * KSTR + pc * 8) = vv;
   }
   __syncthreads();
 
   const float scale_log2 = rsqrtf((float)DH) * 1.4426950408889634f;
   const int r = lane >> 2, cq = (lane & 3) * 2;
+  const int lm = lane >> 3, lr = lane & 7;   // ldmatrix: this lane addresses row lr of matrix lm
 
-  for (int q0 = warp * 16; q0 < S; q0 += 8 * 16) {
+  for (int q0 = warp * 16; q0 < len16; q0 += 8 * 16) {
     // Q fragments for this warp's 16 rows
     uint32_t qa[KSTEPS][4];
     {
@@ -381,11 +431,15 @@ __global__ void __launch_bounds__(256) attention_kernel(const __nv_bfloat16* __r
       for (int nt = 0; nt < 8; ++nt) {
         s[nt][0] = s[nt][1] = s[nt][2] = s[nt][3] = 0.f;
         if (nt < nkt) {
-          const __nv_bfloat16* kr = Ks + (size_t)(kb + nt * 8 + r) * KSTR + cq;
+          // matrices of one ldmatrix.x4: K[keys nt*8.., dims 8*lm .. 8*lm+7] -> b0/b1 of two k-steps
+          const __nv_bfloat16* krow = Ks + (size_t)(kb + nt * 8 + lr) * KSTR + lm * 8;
 #pragma unroll
-          for (int ks = 0; ks < KSTEPS; ++ks)
-            mma_bf16_16816(s[nt], qa[ks], *reinterpret_cast<const uint32_t*>(kr + ks * 16),
-                           *reinterpret_cast<const uint32_t*>(kr + ks * 16 + 8));
+          for (int kk = 0; kk < KSTEPS / 2; ++kk) {
+            uint32_t kf[4];
+            ldmatrix_x4(kf, krow + kk * 32);
+            mma_bf16_16816(s[nt], qa[2 * kk], kf[0], kf[1]);
+            mma_bf16_16816(s[nt], qa[2 * kk + 1], kf[2], kf[3]);
+          }
         }
       }
       // scale into the log2 domain, mask keys >= len, block row max
@@ -429,11 +483,14 @@ __global__ void __launch_bounds__(256) attention_kernel(const __nv_bfloat16* __r
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
         if (j * 2 < nkt) {
+          // matrices of one ldmatrix.x4.trans: V[keys 16j + 8*(lm&1).., dims 8*(2*ip + (lm>>1))..]
+          const __nv_bfloat16* vrow = Vs + (size_t)(kb + j * 16 + (lm & 1) * 8 + lr) * KSTR + (lm >> 1) * 8;
 #pragma unroll
-          for (int i = 0; i < ONT; ++i) {
-            const __nv_bfloat16* vr = Vt + (size_t)(i * 8 + r) * vt_stride + kb + j * 16 + cq;
-            mma_bf16_16816(o[i], pa[j], *reinterpret_cast<const uint32_t*>(vr),
-                           *reinterpret_cast<const uint32_t*>(vr + 8));
+          for (int ip = 0; ip < ONT / 2; ++ip) {
+            uint32_t vf[4];
+            ldmatrix_x4_trans(vf, vrow + ip * 16);
+            mma_bf16_16816(o[2 * ip], pa[j], vf[0], vf[1]);
+            mma_bf16_16816(o[2 * ip + 1], pa[j], vf[2], vf[3]);
           }
         }
       }

@@ -262,26 +262,38 @@ sim_topk_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant
       tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(wq * 32) << 16) + as * BLOCK_N;
       const uint32_t col0 = (tile0 + t) * BLOCK_N;
+      // Software-pipelined drain: the tcgen05.ld of chunk c+1 is in flight while chunk c is
+      // scanned; the accumulator stage goes back to the MMA warp as soon as its last chunk is in
+      // registers.
+      constexpr int NCH = BLOCK_N / 32;
+      uint32_t v[2][32];
+      tmem_ld32(taddr, v[0]);
 #pragma unroll 1
-      for (int c = 0; c < BLOCK_N / 32; ++c) {
-        uint32_t v[32];
-        tmem_ld32(taddr + c * 32, v);
-        tmem_ld_wait();
-        float m = __uint_as_float(v[0]);
+      for (int c2 = 0; c2 < NCH; c2 += 2) {
 #pragma unroll
-        for (int j = 1; j < 32; ++j) m = fmaxf(m, __uint_as_float(v[j]));
-        if (m > thr) {
-          const uint32_t base = col0 + c * 32;
+        for (int u = 0; u < 2; ++u) {
+          const int c = c2 + u;
+          tmem_ld_wait_dep(v[u]);
+          if (c + 1 < NCH) {
+            tmem_ld32(taddr + (c + 1) * 32, v[u ^ 1]);
+          } else {
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&acc_empty[as]);
+          }
+          float m = __uint_as_float(v[u][0]);
 #pragma unroll
-          for (int j = 0; j < 32; ++j) {
-            const float s = __uint_as_float(v[j]);
-            if (s > thr && base + j < p.n_rows) thr = topk_insert<KP>(my_s, my_i, s, base + j);
+          for (int j = 1; j < 32; ++j) m = fmaxf(m, __uint_as_float(v[u][j]));
+          if (m > thr) {
+            const uint32_t base = col0 + c * 32;
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+              const float s = __uint_as_float(v[u][j]);
+              if (s > thr && base + j < p.n_rows) thr = topk_insert<KP>(my_s, my_i, s, base + j);
+            }
           }
         }
       }
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&acc_empty[as]);
     }
     // this split's candidates for this query
     if (qg < p.nq) {
