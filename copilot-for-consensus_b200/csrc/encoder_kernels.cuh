@@ -363,6 +363,12 @@ B200_DEVINL void ldmatrix_x4_trans(uint32_t (&r)[4], const void* smem_row) {
                : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
                : "r"(smem_u32(smem_row)));
 }
+// 2^x on the SFU, flush-to-zero; 2^(-inf) = 0
+B200_DEVINL float fast_exp2(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
 B200_DEVINL uint32_t pack_bf16(float lo, float hi) {
   __nv_bfloat162 t = __floats2bfloat162_rn(lo, hi);
   return *reinterpret_cast<uint32_t*>(&t);
@@ -442,16 +448,22 @@ attention_kernel(const __nv_bfloat16* __restrict__ qkv, const int32_t* __restric
           }
         }
       }
-      // scale into the log2 domain, mask keys >= len, block row max
+      // block row max on the raw scores; keys >= len are masked only in the block that holds the
+      // boundary (full blocks skip the compare/select per element)
+      if (kb + 64 > len) {
+#pragma unroll
+        for (int nt = 0; nt < 8; ++nt) {
+          const int key = kb + nt * 8 + cq;
+          const bool v0 = (nt < nkt) && key < len, v1 = (nt < nkt) && key + 1 < len;
+          s[nt][0] = v0 ? s[nt][0] : -INFINITY;
+          s[nt][1] = v1 ? s[nt][1] : -INFINITY;
+          s[nt][2] = v0 ? s[nt][2] : -INFINITY;
+          s[nt][3] = v1 ? s[nt][3] : -INFINITY;
+        }
+      }
       float bm_lo = -INFINITY, bm_hi = -INFINITY;
 #pragma unroll
       for (int nt = 0; nt < 8; ++nt) {
-        const int key = kb + nt * 8 + cq;
-        const bool v0 = (nt < nkt) && key < len, v1 = (nt < nkt) && key + 1 < len;
-        s[nt][0] = v0 ? s[nt][0] * scale_log2 : -INFINITY;
-        s[nt][1] = v1 ? s[nt][1] * scale_log2 : -INFINITY;
-        s[nt][2] = v0 ? s[nt][2] * scale_log2 : -INFINITY;
-        s[nt][3] = v1 ? s[nt][3] * scale_log2 : -INFINITY;
         bm_lo = fmaxf(bm_lo, fmaxf(s[nt][0], s[nt][1]));
         bm_hi = fmaxf(bm_hi, fmaxf(s[nt][2], s[nt][3]));
       }
@@ -460,25 +472,23 @@ attention_kernel(const __nv_bfloat16* __restrict__ qkv, const int32_t* __restric
       bm_hi = fmaxf(bm_hi, __shfl_xor_sync(0xffffffffu, bm_hi, 1));
       bm_hi = fmaxf(bm_hi, __shfl_xor_sync(0xffffffffu, bm_hi, 2));
       const float mn_lo = fmaxf(m_lo, bm_lo), mn_hi = fmaxf(m_hi, bm_hi);  // finite: key 0 is always valid
-      const float al_lo = exp2f(m_lo - mn_lo), al_hi = exp2f(m_hi - mn_hi);
+      const float al_lo = fast_exp2((m_lo - mn_lo) * scale_log2), al_hi = fast_exp2((m_hi - mn_hi) * scale_log2);
       m_lo = mn_lo; m_hi = mn_hi;
       l_lo *= al_lo; l_hi *= al_hi;
 #pragma unroll
       for (int i = 0; i < ONT; ++i) { o[i][0] *= al_lo; o[i][1] *= al_lo; o[i][2] *= al_hi; o[i][3] *= al_hi; }
-      // P = exp2(s - m) and PV; P is rounded to bf16 once and the same rounded values feed the
-      // row sums, so numerator and denominator stay consistent
+      // P = 2^((s - m) * scale * log2 e): one FFMA + one MUFU per element; P is rounded to bf16 for
+      // the PV tensor tiles, the row sums accumulate the unrounded values
+      const float ms_lo = m_lo * scale_log2, ms_hi = m_hi * scale_log2;
       uint32_t pa[4][4];
 #pragma unroll
       for (int nt = 0; nt < 8; ++nt) {
-        const float p0 = exp2f(s[nt][0] - m_lo), p1 = exp2f(s[nt][1] - m_lo);
-        const float p2 = exp2f(s[nt][2] - m_hi), p3 = exp2f(s[nt][3] - m_hi);
-        const uint32_t u_lo = pack_bf16(p0, p1), u_hi = pack_bf16(p2, p3);
-        const __nv_bfloat162 b_lo = *reinterpret_cast<const __nv_bfloat162*>(&u_lo);
-        const __nv_bfloat162 b_hi = *reinterpret_cast<const __nv_bfloat162*>(&u_hi);
-        l_lo += __low2float(b_lo) + __high2float(b_lo);
-        l_hi += __low2float(b_hi) + __high2float(b_hi);
-        pa[nt >> 1][(nt & 1) * 2 + 0] = u_lo;
-        pa[nt >> 1][(nt & 1) * 2 + 1] = u_hi;
+        const float p0 = fast_exp2(fmaf(s[nt][0], scale_log2, -ms_lo)), p1 = fast_exp2(fmaf(s[nt][1], scale_log2, -ms_lo));
+        const float p2 = fast_exp2(fmaf(s[nt][2], scale_log2, -ms_hi)), p3 = fast_exp2(fmaf(s[nt][3], scale_log2, -ms_hi));
+        l_lo += p0 + p1;
+        l_hi += p2 + p3;
+        pa[nt >> 1][(nt & 1) * 2 + 0] = pack_bf16(p0, p1);
+        pa[nt >> 1][(nt & 1) * 2 + 1] = pack_bf16(p2, p3);
       }
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
