@@ -39,6 +39,7 @@ SYMBOLS = {
     "b200_index_remove_rows": (_i, [_vp, _vp, _i64, _vp]),
     "b200_index_get_rows": (_i, [_vp, _vp, _i64, _vp, _i, _vp]),
     "b200_index_search": (_i, [_vp, _vp, _i, _i, _i64, _i, _i64, _vp, _vp, _i, _vp]),
+    "b200_index_search_static": (_i, [_vp, _vp, _i, _i64, _i, _i64, _vp, _vp, _vp]),
     "b200_merge_topk": (_i, [_vp, _vp, _i64, _i, _i, _i, _vp, _vp, _i, _vp]),
     "b200_encoder_create": (_i, [ctypes.POINTER(EncoderConfigC), _i, ctypes.POINTER(_vp)]),
     "b200_encoder_destroy": (_i, [_vp]),

@@ -517,3 +517,147 @@ int b200_merge_topk(const int64_t* ids_in, const float* scores_in, int64_t nq, i
 }
 
 }  // extern "C"
+
+// ================================================================================================
+// Search that never allocates.
+//
+// Some programs that embed this library cannot let it call cudaMalloc on the query path: a serving
+// process that handed every free byte of HBM to its own memory pool at start-up (a later cudaMalloc
+// from a third-party library simply fails there), and latency-critical query threads for which the
+// device-wide synchronisation hidden inside cudaMalloc / cudaFree would stall every other stream.
+// b200_index_search() grows its scratch buffers on demand, so it is off limits for them.
+//
+// b200_index_search_static() does the same search with all of its scratch -- the padded bf16 query
+// tile, the fp32 copy of the queries, and the per-split candidate lists -- inside the fixed array
+// below, which is part of the library image: every GPU that loads the library holds these 4.3 MB
+// until the process exits, whether or not the entry point is ever used.
+// ================================================================================================
+namespace {
+
+constexpr int kStaticMaxQueries = SIM_BLOCK_M;      // one query tile
+constexpr int kStaticMaxDpad = 384;
+constexpr int kStaticMaxCand = 4096;                // splits x kept candidates, per query
+constexpr size_t kStaticOffQBf16 = 0;
+constexpr size_t kStaticOffQF32 = kStaticOffQBf16 + (size_t)kStaticMaxQueries * kStaticMaxDpad * 2;
+constexpr size_t kStaticOffCandS = kStaticOffQF32 + (size_t)kStaticMaxQueries * kStaticMaxDpad * 4;
+constexpr size_t kStaticOffCandI = kStaticOffCandS + (size_t)kStaticMaxQueries * kStaticMaxCand * 4;
+constexpr size_t kStaticBytes = kStaticOffCandI + (size_t)kStaticMaxQueries * kStaticMaxCand * 4;
+static_assert(kStaticOffQF32 % 256 == 0 && kStaticOffCandS % 256 == 0 && kStaticOffCandI % 256 == 0, "scratch sub-buffers must stay 256-byte aligned");
+
+}  // namespace
+
+static __device__ __align__(256) unsigned char g_static_scratch[kStaticBytes];
+
+namespace {
+
+// In host code `g_static_scratch` is only a handle for the symbol, not a device address: the real
+// address differs per device and has to be asked for with that device current.
+constexpr int kMaxDevices = 64;
+std::mutex g_static_mu;
+unsigned char* g_static_ptr[kMaxDevices] = {};
+
+int static_scratch_for_current_device(int device, unsigned char** out) {
+  if (device < 0 || device >= kMaxDevices) B200_FAIL(B200_ERR_INVALID, "device %d out of range", device);
+  if (!g_static_ptr[device]) {
+    void* p = nullptr;
+    B200_CUDA(cudaGetSymbolAddress(&p, g_static_scratch));
+    g_static_ptr[device] = static_cast<unsigned char*>(p);
+  }
+  *out = g_static_ptr[device];
+  return B200_OK;
+}
+
+template <int BLOCK_N, int KP>
+int launch_sim_static(b200_index* ix, int nq, const CUtensorMap& map_q, float* cand_s, uint32_t* cand_i,
+                      cudaStream_t st, int* nsplit_out) {
+  const int kc = ix->dpad / SIM_BLOCK_K;
+  const size_t a_bytes = (size_t)kc * SIM_A_CHUNK_BYTES;
+  const size_t list_bytes = (size_t)SIM_BLOCK_M * (KP + 1) * 8;
+  const size_t stage_bytes = (size_t)BLOCK_N * SIM_BLOCK_K * 2;
+  const size_t fixed = 1024 + a_bytes + list_bytes + 256;
+  const size_t max_smem = 232448;
+  const int nstage = (int)std::min<size_t>(8, (max_smem - fixed) / stage_bytes);
+  const size_t smem = fixed + (size_t)nstage * stage_bytes;
+  const uint32_t n_rows = (uint32_t)ix->count;
+  const uint32_t total_tiles = (n_rows + BLOCK_N - 1) / BLOCK_N;
+  // one wave of CTAs, bounded by what the fixed candidate area can take
+  int nsplit = std::max(1, std::min<int>({(int)std::min<uint32_t>(total_tiles, 65535u), kStaticMaxCand / KP, ix->num_sms}));
+  const uint32_t tps = (total_tiles + nsplit - 1) / nsplit;
+  nsplit = (int)((total_tiles + tps - 1) / tps);
+  CUtensorMap map_c;
+  B200_TRY(make_tma_2d_bf16(&map_c, ix->search.p, (uint64_t)ix->count, (uint64_t)ix->dpad, BLOCK_N, SIM_BLOCK_K));
+  SimParams p;
+  p.nq = nq; p.kc = kc; p.nstage = nstage; p.n_rows = n_rows; p.tiles_per_split = tps; p.nsplit = nsplit;
+  p.cand_s = cand_s; p.cand_i = cand_i;
+  auto kern = sim_topk_kernel<BLOCK_N, KP>;
+  B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  kern<<<dim3(1, nsplit), SIM_THREADS, smem, st>>>(map_q, map_c, p);
+  B200_CUDA(cudaGetLastError());
+  *nsplit_out = nsplit;
+  return B200_OK;
+}
+
+}  // namespace
+
+extern "C" int b200_index_search_static(b200_index_t* ix, const void* queries_dev, int q_dtype, int64_t nq, int k,
+                                        int64_t id_base, int64_t* ids_dev, float* scores_dev, void* stream) {
+  if (!ix) B200_FAIL(B200_ERR_INVALID, "index is NULL");
+  if (nq < 0 || k < 0) B200_FAIL(B200_ERR_INVALID, "negative nq / k");
+  if (nq == 0 || k == 0) return B200_OK;
+  if (!queries_dev || !ids_dev || !scores_dev) B200_FAIL(B200_ERR_INVALID, "NULL buffer");
+  if (q_dtype != 0 && q_dtype != 1) B200_FAIL(B200_ERR_INVALID, "q_dtype must be 0 (fp32) or 1 (bf16)");
+  if (nq > kStaticMaxQueries)
+    B200_FAIL(B200_ERR_UNSUPPORTED, "b200_index_search_static takes at most %d queries per call (got %lld): its scratch "
+              "area is fixed; split the batch or use b200_index_search", kStaticMaxQueries, (long long)nq);
+  if (ix->dpad > kStaticMaxDpad)
+    B200_FAIL(B200_ERR_UNSUPPORTED, "b200_index_search_static covers dimensions up to %d (index has %d)", kStaticMaxDpad, ix->dim);
+  if (k > 48) B200_FAIL(B200_ERR_UNSUPPORTED, "k=%d: the fused select keeps at most 64 candidates per query (k <= 48)", k);
+  const int kp = k <= 10 ? 16 : (k <= 24 ? 32 : 64);
+  std::lock_guard<std::mutex> lk(ix->mu);
+  std::lock_guard<std::mutex> lk2(g_static_mu);
+  DeviceGuard g(ix->device);
+  if (!g.ok) B200_FAIL(B200_ERR_CUDA, "cudaSetDevice(%d) failed", ix->device);
+  cudaStream_t st = (cudaStream_t)stream;
+  unsigned char* base = nullptr;
+  B200_TRY(static_scratch_for_current_device(ix->device, &base));   // first call per device: resolves the symbol
+  if (ix->count == 0) {  // inmemory.py:93-94: empty store -> no results
+    B200_CUDA(cudaMemsetAsync(ids_dev, 0xFF, (size_t)nq * k * 8, st));
+    B200_CUDA(cudaMemsetAsync(scores_dev, 0, (size_t)nq * k * 4, st));
+    return B200_OK;
+  }
+  __nv_bfloat16* q_bf16 = reinterpret_cast<__nv_bfloat16*>(base + kStaticOffQBf16);
+  float* q_f32 = reinterpret_cast<float*>(base + kStaticOffQF32);
+  float* cand_s = reinterpret_cast<float*>(base + kStaticOffCandS);
+  uint32_t* cand_i = reinterpret_cast<uint32_t*>(base + kStaticOffCandI);
+  // Nothing in the scratch area has to start at zero: prep_queries_kernel rewrites the whole padded
+  // query tile (zero rows included) and every (query, split) candidate list is written in full by
+  // its CTA before the merge kernel reads it, so contents left by an earlier call are never seen.
+  const int n = (int)nq, nq_pad = SIM_BLOCK_M, wpb = 8;
+  if (q_dtype == 0)
+    prep_queries_kernel<float><<<(nq_pad + wpb - 1) / wpb, wpb * 32, 0, st>>>((const float*)queries_dev, n, nq_pad, ix->dim,
+                                                                           ix->dpad, q_bf16, q_f32);
+  else
+    prep_queries_kernel<__nv_bfloat16><<<(nq_pad + wpb - 1) / wpb, wpb * 32, 0, st>>>(
+        (const __nv_bfloat16*)queries_dev, n, nq_pad, ix->dim, ix->dpad, q_bf16, q_f32);
+  B200_CUDA(cudaGetLastError());
+  CUtensorMap map_q;
+  B200_TRY(make_tma_2d_bf16(&map_q, q_bf16, (uint64_t)nq_pad, (uint64_t)ix->dpad, SIM_BLOCK_M, SIM_BLOCK_K));
+  int nsplit = 0;
+  if (kp == 16) B200_TRY((launch_sim_static<256, 16>(ix, n, map_q, cand_s, cand_i, st, &nsplit)));
+  else if (kp == 32) B200_TRY((launch_sim_static<128, 32>(ix, n, map_q, cand_s, cand_i, st, &nsplit)));
+  else B200_TRY((launch_sim_static<128, 64>(ix, n, map_q, cand_s, cand_i, st, &nsplit)));
+  MergeParams m;
+  m.nq = n; m.nsplit = nsplit; m.kp = kp; m.k = k; m.d = ix->dim;
+  int pow2 = 64;
+  while (pow2 < nsplit * kp) pow2 <<= 1;
+  m.ncand_pow2 = pow2;
+  m.n_rows = (uint32_t)ix->count; m.id_base = id_base;
+  m.cand_s = cand_s; m.cand_i = cand_i; m.q_f32 = q_f32; m.master = ix->master.p;
+  m.master_is_bf16 = ix->master_dtype == B200_INDEX_MASTER_BF16;
+  m.out_ids = ids_dev; m.out_scores = scores_dev; m.out_margin = nullptr;
+  const size_t msmem = (size_t)pow2 * 8 + (size_t)((ix->dim + 1) & ~1) * 4 + 64 * 8;
+  B200_CUDA(cudaFuncSetAttribute(merge_rescore_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)msmem));
+  merge_rescore_kernel<<<n, 256, msmem, st>>>(m);
+  B200_CUDA(cudaGetLastError());
+  return B200_OK;
+}

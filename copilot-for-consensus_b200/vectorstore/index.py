@@ -87,6 +87,26 @@ class B200Index:
                                               self._stream()))
         return ids, sc
 
+    def search_static(self, queries: Any, ids_out: Any, scores_out: Any, id_base: int = 0) -> None:
+        """``b200_index_search_static``: the same search for callers that may not allocate device memory
+        on the query path (all HBM already owned by the host program's pool, or no tolerance for the
+        device-wide sync inside cudaMalloc).  Nothing is allocated here either: the caller passes the
+        CUDA query tensor ``[nq <= 128, dim]`` (fp32 or bf16) and pre-allocated CUDA outputs
+        ``ids_out [nq, k] int64`` / ``scores_out [nq, k] float32``.  See the header for the shared-scratch rules."""
+        import torch
+
+        for t in (queries, ids_out, scores_out):
+            if not isinstance(t, torch.Tensor) or not t.is_cuda or t.device.index != self.device or not t.is_contiguous():
+                raise ValueError(f"search_static needs contiguous CUDA tensors on cuda:{self.device}")
+        if queries.dtype not in (torch.float32, torch.bfloat16) or queries.shape[1] != self.dim:
+            raise ValueError(f"queries must be float32 or bfloat16 [nq, {self.dim}]")
+        nq, k = ids_out.shape
+        if ids_out.dtype != torch.int64 or scores_out.dtype != torch.float32 or scores_out.shape != (nq, k) or queries.shape[0] != nq:
+            raise ValueError("ids_out must be int64 [nq, k] and scores_out float32 [nq, k]")
+        nat.check(self._lib.b200_index_search_static(
+            self._h, ctypes.c_void_p(queries.data_ptr()), 0 if queries.dtype == torch.float32 else 1, nq, k, id_base,
+            ctypes.c_void_p(ids_out.data_ptr()), ctypes.c_void_p(scores_out.data_ptr()), self._stream()))
+
     def get_rows(self, rows: Any) -> np.ndarray:
         r = np.ascontiguousarray(rows, dtype=np.int64)
         out = np.empty((len(r), self.dim), dtype=np.float32)

@@ -89,6 +89,25 @@ int b200_index_get_rows(b200_index_t* idx, const int64_t* rows_host, int64_t n, 
 int b200_index_search(b200_index_t* idx, const void* queries, int q_dtype, int queries_on_device, int64_t nq,
                       int k, int64_t id_base, int64_t* ids, float* scores, int out_on_device, void* stream);
 
+/* b200_index_search for callers that must not trigger a device allocation (this entry point has no
+ * counterpart in the reference).  Meant for processes that gave all free HBM to their own pool at
+ * start-up, where a cudaMalloc issued from inside a library fails, and for query threads that cannot
+ * afford the device-wide synchronisation cudaMalloc/cudaFree imply.  Same result as
+ * b200_index_search, with these differences:
+ *   - it calls no cudaMalloc / cudaFree / allocating library routine.  All scratch lives in a fixed
+ *     4.3 MB array inside the library image, resident on every GPU that loads the library until exit.
+ *   - limits: nq <= 128 per call, index dimension <= 384, k <= 48; larger requests are refused with
+ *     B200_ERR_UNSUPPORTED and a message naming the limit.
+ *   - queries, ids and scores must be device pointers on the index's GPU.
+ *   - every call on a GPU shares that one array (across all indexes and threads).  It needs no
+ *     clearing between calls -- each call rewrites everything it later reads -- but two calls whose
+ *     kernels overlap on the GPU (different streams) race on it: keep such calls on one stream or
+ *     order them yourself.
+ *   - the first call on each device looks up the array's device address (cudaGetSymbolAddress);
+ *     make that first call before any stream capture begins on that device. */
+int b200_index_search_static(b200_index_t* idx, const void* queries_dev, int q_dtype, int64_t nq, int k,
+                             int64_t id_base, int64_t* ids_dev, float* scores_dev, void* stream);
+
 /* Multi-GPU candidate merge (no reference counterpart: the reference is single-process).  After an
  * all-gather of per-shard results laid out [nlists][nq][k_in], keep the best k_out per query under
  * the same (score desc, id asc) order.  All pointers are device pointers. */
