@@ -10,7 +10,7 @@
 //                                  the tcgen05 tiles stream through TMA (768 B/row at dim 384)
 //   master  fp32|bf16 [capacity, dim]  the caller's rows, untouched: SearchResult.vector and the
 //                                  exact fp32 rescoring of the KP survivors per query
-//   cand_*  [nq, nsplit, KP]       per-split candidate lists (scratch between K8 and K9)
+//   cand    u64 [nq, nsplit, KP]   per-split candidate keys (scratch between K8 and K9)
 #include <algorithm>
 #include <vector>
 
@@ -115,7 +115,7 @@ using namespace b200;
 struct b200_index {
   int dim = 0, dpad = 0, device = 0, master_dtype = 0, num_sms = 148;
   int64_t count = 0, capacity = 0;
-  DevBuf search, master, stage, q_bf16, q_f32, cand_s, cand_i, out_ids, out_scores, tmp;
+  DevBuf search, master, stage, q_bf16, q_f32, cand, gbkt, out_ids, out_scores, tmp;
   std::mutex mu;
   size_t master_elt() const { return master_dtype == B200_INDEX_MASTER_BF16 ? 2 : 4; }
 };
@@ -170,15 +170,16 @@ static int launch_sim(b200_index* ix, int nq, int nqt, const CUtensorMap& map_q,
   const uint32_t tps = (total_tiles + nsplit - 1) / nsplit;
 
   const size_t cand_n = (size_t)nqt * SIM_BLOCK_M * nsplit * KP;
-  B200_TRY(ix->cand_s.grow(cand_n * 4, 0, st));
-  B200_TRY(ix->cand_i.grow(cand_n * 4, 0, st));
+  B200_TRY(ix->cand.grow(cand_n * 8, 0, st));
+  B200_TRY(ix->gbkt.grow((size_t)nqt * SIM_BLOCK_M * KP * 4, 0, st));
+  B200_CUDA(cudaMemsetAsync(ix->gbkt.p, 0, (size_t)nqt * SIM_BLOCK_M * KP * 4, st));   // bucket bests start at "none"
 
   CUtensorMap map_c;
   B200_TRY(make_tma_2d_bf16(&map_c, ix->search.p, (uint64_t)ix->count, (uint64_t)ix->dpad, BLOCK_N, SIM_BLOCK_K));
 
   SimParams p;
   p.nq = nq; p.kc = kc; p.nstage = nstage; p.n_rows = n_rows; p.tiles_per_split = tps; p.nsplit = nsplit;
-  p.cand_s = ix->cand_s.as<float>(); p.cand_i = ix->cand_i.as<uint32_t>();
+  p.cand = ix->cand.as<uint64_t>(); p.gbkt = ix->gbkt.as<uint32_t>(); p.use_bound = nsplit >= KP;
   auto kern = sim_topk_kernel<BLOCK_N, KP>;
   B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   {
@@ -220,7 +221,7 @@ static int search_chunk(b200_index* ix, const void* q_dev, int q_dtype, int nq, 
   while (pow2 < nsplit * kp) pow2 <<= 1;
   m.ncand_pow2 = pow2;
   m.n_rows = (uint32_t)ix->count; m.id_base = id_base;
-  m.cand_s = ix->cand_s.as<float>(); m.cand_i = ix->cand_i.as<uint32_t>();
+  m.cand = ix->cand.as<uint64_t>();
   m.q_f32 = ix->q_f32.as<float>(); m.master = ix->master.p;
   m.master_is_bf16 = ix->master_dtype == B200_INDEX_MASTER_BF16;
   m.out_ids = ids_dev; m.out_scores = sc_dev; m.out_margin = nullptr;
@@ -539,10 +540,12 @@ constexpr int kStaticMaxDpad = 384;
 constexpr int kStaticMaxCand = 4096;                // splits x kept candidates, per query
 constexpr size_t kStaticOffQBf16 = 0;
 constexpr size_t kStaticOffQF32 = kStaticOffQBf16 + (size_t)kStaticMaxQueries * kStaticMaxDpad * 2;
-constexpr size_t kStaticOffCandS = kStaticOffQF32 + (size_t)kStaticMaxQueries * kStaticMaxDpad * 4;
-constexpr size_t kStaticOffCandI = kStaticOffCandS + (size_t)kStaticMaxQueries * kStaticMaxCand * 4;
-constexpr size_t kStaticBytes = kStaticOffCandI + (size_t)kStaticMaxQueries * kStaticMaxCand * 4;
-static_assert(kStaticOffQF32 % 256 == 0 && kStaticOffCandS % 256 == 0 && kStaticOffCandI % 256 == 0, "scratch sub-buffers must stay 256-byte aligned");
+constexpr size_t kStaticOffCand = kStaticOffQF32 + (size_t)kStaticMaxQueries * kStaticMaxDpad * 4;
+constexpr size_t kStaticOffGthr = kStaticOffCand + (size_t)kStaticMaxQueries * kStaticMaxCand * 8;
+constexpr size_t kStaticBktBytes = (size_t)kStaticMaxQueries * 64 * 4;   // [128 queries][up to 64 buckets]
+constexpr size_t kStaticBytes = kStaticOffGthr + kStaticBktBytes;
+static_assert(kStaticOffQF32 % 256 == 0 && kStaticOffCand % 256 == 0 && kStaticOffGthr % 256 == 0,
+              "scratch sub-buffers must stay 256-byte aligned");
 
 }  // namespace
 
@@ -568,7 +571,7 @@ int static_scratch_for_current_device(int device, unsigned char** out) {
 }
 
 template <int BLOCK_N, int KP>
-int launch_sim_static(b200_index* ix, int nq, const CUtensorMap& map_q, float* cand_s, uint32_t* cand_i,
+int launch_sim_static(b200_index* ix, int nq, const CUtensorMap& map_q, uint64_t* cand, uint32_t* gthr,
                       cudaStream_t st, int* nsplit_out) {
   const int kc = ix->dpad / SIM_BLOCK_K;
   const size_t a_bytes = (size_t)kc * SIM_A_CHUNK_BYTES;
@@ -588,7 +591,7 @@ int launch_sim_static(b200_index* ix, int nq, const CUtensorMap& map_q, float* c
   B200_TRY(make_tma_2d_bf16(&map_c, ix->search.p, (uint64_t)ix->count, (uint64_t)ix->dpad, BLOCK_N, SIM_BLOCK_K));
   SimParams p;
   p.nq = nq; p.kc = kc; p.nstage = nstage; p.n_rows = n_rows; p.tiles_per_split = tps; p.nsplit = nsplit;
-  p.cand_s = cand_s; p.cand_i = cand_i;
+  p.cand = cand; p.gbkt = gthr; p.use_bound = nsplit >= KP;
   auto kern = sim_topk_kernel<BLOCK_N, KP>;
   B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   kern<<<dim3(1, nsplit), SIM_THREADS, smem, st>>>(map_q, map_c, p);
@@ -627,11 +630,14 @@ extern "C" int b200_index_search_static(b200_index_t* ix, const void* queries_de
   }
   __nv_bfloat16* q_bf16 = reinterpret_cast<__nv_bfloat16*>(base + kStaticOffQBf16);
   float* q_f32 = reinterpret_cast<float*>(base + kStaticOffQF32);
-  float* cand_s = reinterpret_cast<float*>(base + kStaticOffCandS);
-  uint32_t* cand_i = reinterpret_cast<uint32_t*>(base + kStaticOffCandI);
-  // Nothing in the scratch area has to start at zero: prep_queries_kernel rewrites the whole padded
-  // query tile (zero rows included) and every (query, split) candidate list is written in full by
-  // its CTA before the merge kernel reads it, so contents left by an earlier call are never seen.
+  uint64_t* cand = reinterpret_cast<uint64_t*>(base + kStaticOffCand);
+  uint32_t* gthr = reinterpret_cast<uint32_t*>(base + kStaticOffGthr);
+  // The array keeps whatever the previous call left.  The only part that must start at zero is the
+  // table of per-bucket best scores the CTAs share (32 KB): it is cleared here, on the caller's stream.
+  // Everything else is rewritten in full before it is read: prep_queries_kernel writes the whole
+  // padded query tile (zero rows included) and every (query, split) candidate set is stored by its
+  // CTA before the merge kernel looks at it.
+  B200_CUDA(cudaMemsetAsync(gthr, 0, kStaticBktBytes, st));
   const int n = (int)nq, nq_pad = SIM_BLOCK_M, wpb = 8;
   if (q_dtype == 0)
     prep_queries_kernel<float><<<(nq_pad + wpb - 1) / wpb, wpb * 32, 0, st>>>((const float*)queries_dev, n, nq_pad, ix->dim,
@@ -643,16 +649,16 @@ extern "C" int b200_index_search_static(b200_index_t* ix, const void* queries_de
   CUtensorMap map_q;
   B200_TRY(make_tma_2d_bf16(&map_q, q_bf16, (uint64_t)nq_pad, (uint64_t)ix->dpad, SIM_BLOCK_M, SIM_BLOCK_K));
   int nsplit = 0;
-  if (kp == 16) B200_TRY((launch_sim_static<256, 16>(ix, n, map_q, cand_s, cand_i, st, &nsplit)));
-  else if (kp == 32) B200_TRY((launch_sim_static<128, 32>(ix, n, map_q, cand_s, cand_i, st, &nsplit)));
-  else B200_TRY((launch_sim_static<128, 64>(ix, n, map_q, cand_s, cand_i, st, &nsplit)));
+  if (kp == 16) B200_TRY((launch_sim_static<256, 16>(ix, n, map_q, cand, gthr, st, &nsplit)));
+  else if (kp == 32) B200_TRY((launch_sim_static<128, 32>(ix, n, map_q, cand, gthr, st, &nsplit)));
+  else B200_TRY((launch_sim_static<128, 64>(ix, n, map_q, cand, gthr, st, &nsplit)));
   MergeParams m;
   m.nq = n; m.nsplit = nsplit; m.kp = kp; m.k = k; m.d = ix->dim;
   int pow2 = 64;
   while (pow2 < nsplit * kp) pow2 <<= 1;
   m.ncand_pow2 = pow2;
   m.n_rows = (uint32_t)ix->count; m.id_base = id_base;
-  m.cand_s = cand_s; m.cand_i = cand_i; m.q_f32 = q_f32; m.master = ix->master.p;
+  m.cand = cand; m.q_f32 = q_f32; m.master = ix->master.p;
   m.master_is_bf16 = ix->master_dtype == B200_INDEX_MASTER_BF16;
   m.out_ids = ids_dev; m.out_scores = scores_dev; m.out_margin = nullptr;
   const size_t msmem = (size_t)pow2 * 8 + (size_t)((ix->dim + 1) & ~1) * 4 + 64 * 8;

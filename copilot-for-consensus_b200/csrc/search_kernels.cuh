@@ -121,24 +121,37 @@ struct SimParams {
   uint32_t n_rows;        // valid corpus rows
   uint32_t tiles_per_split;
   int nsplit;
-  float* cand_s;          // [nq_tiles*128][nsplit][KP]
-  uint32_t* cand_i;
+  uint64_t* cand;         // [nq][nsplit][KP] packed (score, row) keys, 0 = empty slot
+  uint32_t* gbkt;         // [nq][KP] per-query, per-bucket best score seen by any CTA of the bucket
+                          // (orderable bits, 0 = nothing yet), zeroed before the launch; see the drain
+  int use_bound;          // 1 when there are at least KP splits (one bucket per kept candidate)
 };
 
-// Sorted-descending insertion into one query's candidate list (shared memory, thread-private
-// row).  Equal scores keep the earlier (lower) row first: rows are scanned in ascending order,
-// so a strict '<' on the shift is the reference's stable-sort tie rule (inmemory.py:118).
+// (score, row) -> one 64-bit key whose unsigned order is "better first": higher score, then lower
+// row.  0 is reserved for "empty slot" (no real key is 0: orderable(-inf) is already 0x007FFFFF).
+B200_DEVINL uint64_t pack_key(float s, uint32_t id) {
+  return ((uint64_t)f32_orderable(s) << 32) | (uint64_t)(~id);
+}
+
+// One query's candidate set: KP unsorted keys in shared memory (a thread-private row) plus the
+// position of the current worst one.  A new candidate overwrites the worst, then the worst is
+// found again with KP independent loads -- no shifting, so an insert costs ~4*KP instructions
+// whatever its rank (a sorted list made inserts the bottleneck once every TMEM lane carries a live
+// query).  Rows arrive in ascending order and the caller only inserts when score > worst score, so
+// among equal scores the earlier row stays: the reference's stable-sort tie rule (inmemory.py:118).
+// Returns (float bits of the worst score, -inf while the set is not full) << 32 | worst position.
 template <int KP>
-__device__ __noinline__ float topk_insert(float* cs, uint32_t* ci, float s, uint32_t id) {
-  int j = KP - 1;
-  while (j > 0 && cs[j - 1] < s) {
-    cs[j] = cs[j - 1];
-    ci[j] = ci[j - 1];
-    --j;
+__device__ __noinline__ uint64_t topk_replace_worst(uint64_t* keys, int wpos, float s, uint32_t id) {
+  keys[wpos] = pack_key(s, id);
+  uint64_t w = keys[0];
+  int wp = 0;
+#pragma unroll
+  for (int i = 1; i < KP; ++i) {
+    const uint64_t k = keys[i];
+    if (k < w) { w = k; wp = i; }
   }
-  cs[j] = s;
-  ci[j] = id;
-  return cs[KP - 1];
+  const float thr = w ? orderable_f32((uint32_t)(w >> 32)) : -INFINITY;
+  return ((uint64_t)__float_as_uint(thr) << 32) | (uint32_t)wp;
 }
 
 template <int BLOCK_N, int KP>
@@ -154,9 +167,8 @@ sim_topk_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* sA = smem;
   uint8_t* sB = sA + (size_t)p.kc * SIM_A_CHUNK_BYTES;
-  float* cs = reinterpret_cast<float*>(sB + (size_t)p.nstage * B_STAGE_BYTES);
-  uint32_t* ci = reinterpret_cast<uint32_t*>(cs + SIM_BLOCK_M * (KP + 1));
-  uint64_t* bars = reinterpret_cast<uint64_t*>(ci + SIM_BLOCK_M * (KP + 1));
+  uint64_t* ckeys = reinterpret_cast<uint64_t*>(sB + (size_t)p.nstage * B_STAGE_BYTES);   // [128][KP+1]
+  uint64_t* bars = ckeys + SIM_BLOCK_M * (KP + 1);
   uint64_t* full = bars;                       // [nstage]  TMA -> MMA
   uint64_t* empty = bars + p.nstage;           // [nstage]  MMA -> TMA
   uint64_t* acc_full = bars + 2 * p.nstage;    // [2]       MMA -> drain
@@ -190,11 +202,8 @@ sim_topk_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant
     fence_mbar_init();
   }
   if (warp == 2) tmem_alloc(tmem_slot, TMEM_COLS);
-  // candidate lists start empty: -inf scores, no-row ids
-  for (int i = threadIdx.x; i < SIM_BLOCK_M * (KP + 1); i += SIM_THREADS) {
-    cs[i] = -INFINITY;
-    ci[i] = kNoRow;
-  }
+  // candidate sets start empty
+  for (int i = threadIdx.x; i < SIM_BLOCK_M * (KP + 1); i += SIM_THREADS) ckeys[i] = 0;
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -253,11 +262,40 @@ sim_topk_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant
     const int wq = warp - 4;                   // TMEM lane group this warp may read
     const int row = wq * 32 + lane;
     const int qg = qtile * SIM_BLOCK_M + row;
-    float* my_s = cs + row * (KP + 1);
-    uint32_t* my_i = ci + row * (KP + 1);
-    float thr = (qg < p.nq) ? -INFINITY : INFINITY;  // padded query rows never insert
+    uint64_t* my_keys = ckeys + row * (KP + 1);      // odd stride in 8-byte words: conflict-free
+    int wpos = 0;
+    const bool live = qg < p.nq;
+    // thr = max(score of this CTA's own worst kept candidate, just below the cross-CTA bound).
+    //
+    // The cross-CTA bound: the CTAs scanning one query tile are dealt into KP buckets (split % KP)
+    // and every CTA publishes the best score it has inserted so far into its bucket's slot
+    // (atomicMax).  Each non-empty slot is the score of a real row and the buckets cover disjoint
+    // row ranges, so the MINIMUM over the KP slots has at least KP distinct rows at or above it: it
+    // is a lower bound on the query's final KP-th best score.  Its quality is global -- the bucket
+    // maxima are, roughly, the best rows of the whole corpus scanned so far -- whereas a CTA's own
+    // KP-th best only reflects its own slice.  Without it half of all 32-column chunks of a fully
+    // populated query tile reach the per-column insert path; with it a few percent do.  The bound is
+    // applied non-strictly (rows EQUAL to it still pass, hence "just below"): ties at the boundary
+    // must all survive so that the lower row can win in the merge, whichever slice it sits in.
+    float thr_own = live ? -INFINITY : INFINITY;     // padded query rows never insert
+    float thr = thr_own, best_own = -INFINITY;
+    const bool bound_on = live && p.use_bound;
+    uint32_t* my_bkt = p.gbkt + (size_t)(live ? qg : 0) * KP;
     for (uint32_t t = 0; t < ntiles; ++t) {
       const uint32_t as = t & 1, aph = (t >> 1) & 1;
+      if (bound_on) {
+        uint32_t gb = 0xFFFFFFFFu;
+#pragma unroll
+        for (int i = 0; i < KP / 4; ++i) {
+          const uint4 b4 = __ldcg(reinterpret_cast<const uint4*>(my_bkt) + i);
+          gb = min(min(gb, b4.x), min(b4.y, min(b4.z, b4.w)));
+        }
+        if (gb) {                                             // every bucket has reported
+          float below = orderable_f32(gb - 1);                  // previous float in the total order
+          if (below == 0.f) below = __uint_as_float(0x80000001u);  // -0 compares equal to +0: step past it
+          thr = fmaxf(thr, below);
+        }
+      }
       mbar_wait(&acc_full[as], aph);
       tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(wq * 32) << 16) + as * BLOCK_N;
@@ -289,7 +327,16 @@ sim_topk_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant
 #pragma unroll
             for (int j = 0; j < 32; ++j) {
               const float s = __uint_as_float(v[u][j]);
-              if (s > thr && base + j < p.n_rows) thr = topk_insert<KP>(my_s, my_i, s, base + j);
+              if (s > thr && base + j < p.n_rows) {
+                const uint64_t r = topk_replace_worst<KP>(my_keys, wpos, s, base + j);
+                thr_own = __uint_as_float((uint32_t)(r >> 32));
+                wpos = (int)(uint32_t)r;
+                thr = fmaxf(thr, thr_own);
+                if (s > best_own) {
+                  best_own = s;
+                  if (bound_on) atomicMax(my_bkt + (split % KP), f32_orderable(s));
+                }
+              }
             }
           }
         }
@@ -299,10 +346,7 @@ sim_topk_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant
     if (qg < p.nq) {
       const size_t o = ((size_t)qg * p.nsplit + split) * KP;
 #pragma unroll 4
-      for (int j = 0; j < KP; ++j) {
-        p.cand_s[o + j] = my_s[j];
-        p.cand_i[o + j] = my_i[j];
-      }
+      for (int j = 0; j < KP; ++j) p.cand[o + j] = my_keys[j];
     }
   }
 
@@ -345,10 +389,6 @@ B200_DEVINL float canon_score(const float* __restrict__ qh, const TV* __restrict
   return p;
 }
 
-B200_DEVINL uint64_t pack_key(float s, uint32_t id) {
-  return ((uint64_t)f32_orderable(s) << 32) | (uint64_t)(~id);
-}
-
 // descending bitonic sort of n (power of two) 64-bit keys in shared memory, whole CTA
 B200_DEVINL void bitonic_sort_desc(uint64_t* keys, int n) {
   for (int k = 2; k <= n; k <<= 1) {
@@ -381,8 +421,7 @@ struct MergeParams {
   int ncand_pow2;
   uint32_t n_rows;
   int64_t id_base;
-  const float* cand_s;
-  const uint32_t* cand_i;
+  const uint64_t* cand;     // [nq][nsplit][kp] packed keys from K8, 0 = empty
   const float* q_f32;       // [nq, d] raw queries
   const void* master;       // [n_rows, d] raw rows, fp32 or bf16
   int master_is_bf16;
@@ -403,12 +442,7 @@ __global__ void __launch_bounds__(256) merge_rescore_kernel(const MergeParams p)
   const int ncand = p.nsplit * p.kp;
   const size_t o = (size_t)q * ncand;
   for (int i = threadIdx.x; i < p.ncand_pow2; i += blockDim.x) {
-    uint64_t key = 0;
-    if (i < ncand) {
-      const uint32_t id = p.cand_i[o + i];
-      if (id != kNoRow) key = pack_key(p.cand_s[o + i], id);
-    }
-    keys[i] = key;
+    keys[i] = (i < ncand) ? p.cand[o + i] : 0;
   }
   // q_hat = q / (||q|| + 1e-8)   (inmemory.py:108)
   const float* qraw = p.q_f32 + (size_t)q * p.d;

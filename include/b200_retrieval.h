@@ -99,10 +99,10 @@ int b200_index_search(b200_index_t* idx, const void* queries, int q_dtype, int q
  *   - limits: nq <= 128 per call, index dimension <= 384, k <= 48; larger requests are refused with
  *     B200_ERR_UNSUPPORTED and a message naming the limit.
  *   - queries, ids and scores must be device pointers on the index's GPU.
- *   - every call on a GPU shares that one array (across all indexes and threads).  It needs no
- *     clearing between calls -- each call rewrites everything it later reads -- but two calls whose
- *     kernels overlap on the GPU (different streams) race on it: keep such calls on one stream or
- *     order them yourself.
+ *   - every call on a GPU shares that one array (across all indexes and threads).  The caller never
+ *     has to clear it -- each call zeroes the 32 KB that must start at zero and rewrites the rest
+ *     before reading it -- but two calls whose kernels overlap on the GPU (different streams) race on
+ *     it: keep such calls on one stream or order them yourself.
  *   - the first call on each device looks up the array's device address (cudaGetSymbolAddress);
  *     make that first call before any stream capture begins on that device. */
 int b200_index_search_static(b200_index_t* idx, const void* queries_dev, int q_dtype, int64_t nq, int k,
