@@ -171,8 +171,10 @@ static int launch_sim(b200_index* ix, int nq, int nqt, const CUtensorMap& map_q,
 
   const size_t cand_n = (size_t)nqt * SIM_BLOCK_M * nsplit * KP;
   B200_TRY(ix->cand.grow(cand_n * 8, 0, st));
-  B200_TRY(ix->gbkt.grow((size_t)nqt * SIM_BLOCK_M * KP * 4, 0, st));
-  B200_CUDA(cudaMemsetAsync(ix->gbkt.p, 0, (size_t)nqt * SIM_BLOCK_M * KP * 4, st));   // bucket bests start at "none"
+  // [nq_pad][KP] bucket bests followed by [nq_pad] single-CTA bounds; both start at "none"
+  const size_t bkt_words = (size_t)nqt * SIM_BLOCK_M * (KP + 1);
+  B200_TRY(ix->gbkt.grow(bkt_words * 4, 0, st));
+  B200_CUDA(cudaMemsetAsync(ix->gbkt.p, 0, bkt_words * 4, st));
 
   CUtensorMap map_c;
   B200_TRY(make_tma_2d_bf16(&map_c, ix->search.p, (uint64_t)ix->count, (uint64_t)ix->dpad, BLOCK_N, SIM_BLOCK_K));
@@ -180,13 +182,18 @@ static int launch_sim(b200_index* ix, int nq, int nqt, const CUtensorMap& map_q,
   SimParams p;
   p.nq = nq; p.kc = kc; p.nstage = nstage; p.n_rows = n_rows; p.tiles_per_split = tps; p.nsplit = nsplit;
   p.cand = ix->cand.as<uint64_t>(); p.gbkt = ix->gbkt.as<uint32_t>(); p.use_bound = nsplit >= KP;
+  p.gthr = ix->gbkt.as<uint32_t>() + (size_t)nqt * SIM_BLOCK_M * KP;
+  p.refresh_mask = 0; p.use_gthr = 1; p.split_major = 0;
+  if (const char* e = getenv("B200_SIM_REFRESH")) p.refresh_mask = (uint32_t)atoi(e);   // tuning knobs (benchmarks only)
+  if (const char* e = getenv("B200_SIM_BOUND")) { const int m = atoi(e); p.use_bound = (m & 1) && nsplit >= KP; p.use_gthr = (m >> 1) & 1; p.split_major = (m >> 2) & 1; }
   auto kern = sim_topk_kernel<BLOCK_N, KP>;
   B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   {
     // algorithmic work of one pass: every corpus row read once (768 B at dim 384) and 2*dpad flops
     // per (query, row) pair
     B200_PROF("sim_topk", 2.0 * nq * (double)n_rows * ix->dpad, (double)n_rows * ix->dpad * 2.0, st);
-    kern<<<dim3(nqt, nsplit), SIM_THREADS, smem, st>>>(map_q, map_c, p);
+      if (p.split_major) kern<<<dim3(nsplit, nqt), SIM_THREADS, smem, st>>>(map_q, map_c, p);
+    else kern<<<dim3(nqt, nsplit), SIM_THREADS, smem, st>>>(map_q, map_c, p);
   }
   B200_CUDA(cudaGetLastError());
   *nsplit_out = nsplit;
@@ -542,7 +549,7 @@ constexpr size_t kStaticOffQBf16 = 0;
 constexpr size_t kStaticOffQF32 = kStaticOffQBf16 + (size_t)kStaticMaxQueries * kStaticMaxDpad * 2;
 constexpr size_t kStaticOffCand = kStaticOffQF32 + (size_t)kStaticMaxQueries * kStaticMaxDpad * 4;
 constexpr size_t kStaticOffGthr = kStaticOffCand + (size_t)kStaticMaxQueries * kStaticMaxCand * 8;
-constexpr size_t kStaticBktBytes = (size_t)kStaticMaxQueries * 64 * 4;   // [128 queries][up to 64 buckets]
+constexpr size_t kStaticBktBytes = (size_t)kStaticMaxQueries * (64 + 1) * 4;   // [128][up to 64 buckets] + [128] bounds
 constexpr size_t kStaticBytes = kStaticOffGthr + kStaticBktBytes;
 static_assert(kStaticOffQF32 % 256 == 0 && kStaticOffCand % 256 == 0 && kStaticOffGthr % 256 == 0,
               "scratch sub-buffers must stay 256-byte aligned");
@@ -592,6 +599,8 @@ int launch_sim_static(b200_index* ix, int nq, const CUtensorMap& map_q, uint64_t
   SimParams p;
   p.nq = nq; p.kc = kc; p.nstage = nstage; p.n_rows = n_rows; p.tiles_per_split = tps; p.nsplit = nsplit;
   p.cand = cand; p.gbkt = gthr; p.use_bound = nsplit >= KP;
+  p.gthr = gthr + (size_t)kStaticMaxQueries * KP;
+  p.refresh_mask = 0; p.use_gthr = 0; p.split_major = 0;
   auto kern = sim_topk_kernel<BLOCK_N, KP>;
   B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   kern<<<dim3(1, nsplit), SIM_THREADS, smem, st>>>(map_q, map_c, p);
@@ -633,7 +642,7 @@ extern "C" int b200_index_search_static(b200_index_t* ix, const void* queries_de
   uint64_t* cand = reinterpret_cast<uint64_t*>(base + kStaticOffCand);
   uint32_t* gthr = reinterpret_cast<uint32_t*>(base + kStaticOffGthr);
   // The array keeps whatever the previous call left.  The only part that must start at zero is the
-  // table of per-bucket best scores the CTAs share (32 KB): it is cleared here, on the caller's stream.
+  // table of score bounds the CTAs share (33 KB): it is cleared here, on the caller's stream.
   // Everything else is rewritten in full before it is read: prep_queries_kernel writes the whole
   // padded query tile (zero rows included) and every (query, split) candidate set is stored by its
   // CTA before the merge kernel looks at it.

@@ -125,6 +125,10 @@ struct SimParams {
   uint32_t* gbkt;         // [nq][KP] per-query, per-bucket best score seen by any CTA of the bucket
                           // (orderable bits, 0 = nothing yet), zeroed before the launch; see the drain
   int use_bound;          // 1 when there are at least KP splits (one bucket per kept candidate)
+  uint32_t* gthr;         // [nq] best "worst kept score" of any CTA whose set is full (orderable bits, 0 = none)
+  uint32_t refresh_mask;  // the shared bounds are re-read every (refresh_mask + 1) tiles
+  int use_gthr;
+  int split_major;        // 1: blockIdx.x = split, blockIdx.y = query tile (all splits of a tile run together)
 };
 
 // (score, row) -> one 64-bit key whose unsigned order is "better first": higher score, then lower
@@ -178,8 +182,8 @@ sim_topk_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  const int qtile = blockIdx.x;
-  const int split = blockIdx.y;
+  const int qtile = p.split_major ? blockIdx.y : blockIdx.x;
+  const int split = p.split_major ? blockIdx.x : blockIdx.y;
 
   const uint32_t total_tiles = (p.n_rows + BLOCK_N - 1) / BLOCK_N;
   const uint32_t tile0 = (uint32_t)split * p.tiles_per_split;
@@ -274,7 +278,10 @@ sim_topk_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant
     // is a lower bound on the query's final KP-th best score.  Its quality is global -- the bucket
     // maxima are, roughly, the best rows of the whole corpus scanned so far -- whereas a CTA's own
     // KP-th best only reflects its own slice.  Without it half of all 32-column chunks of a fully
-    // populated query tile reach the per-column insert path; with it a few percent do.  The bound is
+    // populated query tile reach the per-column insert path; with it a few percent do.  Until all
+    // KP buckets have reported (the first waves of a multi-wave launch) the weaker bound gthr[q] --
+    // the best KP-th-best of any single CTA, which alone holds KP rows at least that good -- stands
+    // in.  Both bounds are
     // applied non-strictly (rows EQUAL to it still pass, hence "just below"): ties at the boundary
     // must all survive so that the lower row can win in the merge, whichever slice it sits in.
     float thr_own = live ? -INFINITY : INFINITY;     // padded query rows never insert
@@ -283,14 +290,16 @@ sim_topk_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant
     uint32_t* my_bkt = p.gbkt + (size_t)(live ? qg : 0) * KP;
     for (uint32_t t = 0; t < ntiles; ++t) {
       const uint32_t as = t & 1, aph = (t >> 1) & 1;
-      if (bound_on) {
+      if (live && (t & p.refresh_mask) == 0) {
         uint32_t gb = 0xFFFFFFFFu;
+        if (!bound_on) gb = 0;
 #pragma unroll
         for (int i = 0; i < KP / 4; ++i) {
           const uint4 b4 = __ldcg(reinterpret_cast<const uint4*>(my_bkt) + i);
           gb = min(min(gb, b4.x), min(b4.y, min(b4.z, b4.w)));
         }
-        if (gb) {                                             // every bucket has reported
+        if (p.use_gthr) gb = max(gb, __ldcg(p.gthr + qg));   // bucket bound is 0 until every bucket has reported
+        if (gb) {
           float below = orderable_f32(gb - 1);                  // previous float in the total order
           if (below == 0.f) below = __uint_as_float(0x80000001u);  // -0 compares equal to +0: step past it
           thr = fmaxf(thr, below);
@@ -332,6 +341,7 @@ sim_topk_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant
                 thr_own = __uint_as_float((uint32_t)(r >> 32));
                 wpos = (int)(uint32_t)r;
                 thr = fmaxf(thr, thr_own);
+                if (p.use_gthr && thr_own > -INFINITY) atomicMax(p.gthr + qg, f32_orderable(thr_own));   // set is full
                 if (s > best_own) {
                   best_own = s;
                   if (bound_on) atomicMax(my_bkt + (split % KP), f32_orderable(s));

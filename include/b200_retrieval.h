@@ -100,7 +100,7 @@ int b200_index_search(b200_index_t* idx, const void* queries, int q_dtype, int q
  *     B200_ERR_UNSUPPORTED and a message naming the limit.
  *   - queries, ids and scores must be device pointers on the index's GPU.
  *   - every call on a GPU shares that one array (across all indexes and threads).  The caller never
- *     has to clear it -- each call zeroes the 32 KB that must start at zero and rewrites the rest
+ *     has to clear it -- each call zeroes the 33 KB that must start at zero and rewrites the rest
  *     before reading it -- but two calls whose kernels overlap on the GPU (different streams) race on
  *     it: keep such calls on one stream or order them yourself.
  *   - the first call on each device looks up the array's device address (cudaGetSymbolAddress);

@@ -19,7 +19,13 @@ idx = vs.B200Index(384, device=0, master_dtype="bfloat16", capacity=n)
 for c0 in range(0, n, 1 << 20):
     m = min(1 << 20, n - c0)
     idx.add(torch.randn((m, 384), generator=g, device=dev).bfloat16().contiguous())
-for nq in (1, 8, 32, 64, 128, 256, 512, 4096):
+settings = [("", "")] if len(sys.argv) < 3 else [tuple(x.split(":")) for x in sys.argv[2].split(",")]
+for refresh, bound in settings:
+  if refresh != "":
+    os.environ["B200_SIM_REFRESH"] = refresh
+    os.environ["B200_SIM_BOUND"] = bound
+    print(f"== refresh_mask={refresh} bound_mode={bound} (1=buckets 2=single-CTA 3=both)")
+  for nq in (1, 32, 128, 512, 4096):
     q = torch.randn((nq, 384), generator=g, device=dev).bfloat16().contiguous()
     for _ in range(2):
         idx.search(q, 10)
