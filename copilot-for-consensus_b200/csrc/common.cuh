@@ -165,6 +165,30 @@ B200_DEVINL void tmem_ld64(uint32_t taddr, uint32_t (&r)[64]) {
                : "r"(taddr)
                : "memory");
 }
+// 32 lanes x 16 consecutive 32-bit columns <- 16 registers per thread (thread i -> TMEM lane base+i)
+B200_DEVINL void tmem_st16(uint32_t taddr, const uint32_t (&r)[16]) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], "
+      "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};" ::"r"(taddr),
+      "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]), "r"(r[9]),
+      "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15])
+      : "memory");
+}
+B200_DEVINL void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+
+// D[tmem] (+)= A[tmem] * B[smem]^T: the A operand (bf16, two values per 32-bit column, row m in
+// TMEM lane m) comes from tensor memory, e.g. softmax probabilities written back over the scores.
+B200_DEVINL void umma_bf16_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t"
+      "}\n" ::"r"(tmem_d),
+      "r"(tmem_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+
 B200_DEVINL void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 // Same wait, but tied to the destination registers of an earlier tmem_ld32 so that the compiler
 // cannot move their first use above it.  Lets a second tmem_ld32 (into another array) be issued
@@ -195,11 +219,25 @@ B200_DEVINL uint64_t umma_smem_desc_sw128(uint32_t smem_addr_bytes) {
   d |= static_cast<uint64_t>(2) << 61;
   return d;
 }
+// General form: layout type 2 = SWIZZLE_128B, 4 = SWIZZLE_64B, 6 = SWIZZLE_32B; sbo / lbo in bytes.
+B200_DEVINL uint64_t umma_smem_desc(uint32_t smem_addr_bytes, uint32_t layout_type, uint32_t sbo, uint32_t lbo) {
+  uint64_t d = 0;
+  d |= static_cast<uint64_t>((smem_addr_bytes & 0x3FFFFu) >> 4);
+  d |= static_cast<uint64_t>((lbo >> 4) & 0x3FFFu) << 16;
+  d |= static_cast<uint64_t>((sbo >> 4) & 0x3FFFu) << 32;
+  d |= static_cast<uint64_t>(1) << 46;
+  d |= static_cast<uint64_t>(layout_type) << 61;
+  return d;
+}
 // kind::f16 instruction descriptor: fp32 accumulator, bf16 A and B, both K-major, dense.
 //   [4,6) D format (1 = f32)   [7,10) A format (1 = bf16)   [10,13) B format (1 = bf16)
 //   [15] A major (0 = K)       [16] B major (0 = K)          [17,23) N >> 3       [24,29) M >> 4
 __host__ __device__ constexpr uint32_t umma_idesc_bf16_f32(uint32_t M, uint32_t N) {
   return (1u << 4) | (1u << 7) | (1u << 10) | ((N >> 3) << 17) | ((M >> 4) << 24);
+}
+// same, with the B operand MN-major (its N index is the contiguous one in shared memory)
+__host__ __device__ constexpr uint32_t umma_idesc_bf16_f32_bmn(uint32_t M, uint32_t N) {
+  return umma_idesc_bf16_f32(M, N) | (1u << 16);
 }
 
 // ---------------------------------------------------------------------------------------------

@@ -98,6 +98,10 @@ struct DevBuf {
 int make_tma_2d_bf16(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint32_t box_rows,
                      uint32_t box_cols);
 
+// Same for a 64-byte swizzle (box_cols = 32 bf16), used by the attention kernel's Q/K/V tiles.
+int make_tma_2d_bf16_sw64(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint32_t box_rows,
+                          uint32_t box_cols);
+
 int check_device_is_sm100(int device);
 
 // Optional per-kernel timing (off by default): when enabled through b200_profile_enable, each
