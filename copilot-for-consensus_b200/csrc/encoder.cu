@@ -186,10 +186,11 @@ static int run_encoder(b200_encoder* e, const int32_t* d_ids, const int32_t* d_l
   // other shapes use the mma.sync one.  B200_ATTENTION=legacy forces the latter (A/B timing).
   const char* att_env = getenv("B200_ATTENTION");
   const bool use_att_tc = dh == ATT_DH && seq <= ATT_MAX_S && seq % 32 == 0 && !(att_env && strcmp(att_env, "legacy") == 0);
-  const size_t att_tc_smem = 1024 + 2 * (size_t)ATT_STAGE_BYTES + 256;
-  CUtensorMap map_att;
+  const size_t att_tc_smem = 1024 + 2 * (size_t)ATT_STAGE_BYTES + 256;   // alignment slack, two stages, barriers
+  CUtensorMap map_att_q, map_att_kv;
   if (use_att_tc) {
-    B200_TRY(make_tma_2d_bf16_sw64(&map_att, e->qkv.p, (uint64_t)e->m_cap, (uint64_t)(3 * H), (uint32_t)seq, ATT_DH));
+    B200_TRY(make_tma_2d_bf16_sw64(&map_att_q, e->qkv.p, (uint64_t)e->m_cap, (uint64_t)(3 * H), (uint32_t)std::min(seq, 128), ATT_DH));
+    B200_TRY(make_tma_2d_bf16_sw64(&map_att_kv, e->qkv.p, (uint64_t)e->m_cap, (uint64_t)(3 * H), (uint32_t)seq, ATT_DH));
     B200_CUDA(cudaFuncSetAttribute(attention_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)att_tc_smem));
   }
 
@@ -201,10 +202,10 @@ static int run_encoder(b200_encoder* e, const int32_t* d_ids, const int32_t* d_l
     B200_TRY(launch_gemm<EPI_BIAS>(e, GemmIO{&e->map_x, &L->map_wqkv, &e->map_qkv_st, &e->map_qkv_st}, p, st));
     if (use_att_tc) {
       AttParams ap;
-      ap.S = seq; ap.H = H; ap.heads = heads; ap.n_items = batch * heads; ap.lens = d_lens;
-      ap.ctx = e->ctx.as<__nv_bfloat16>(); ap.v_mn_major = 1;
+      ap.S = seq; ap.H = H; ap.heads = heads; ap.n_mt = (seq + 127) / 128; ap.n_units = batch * heads * ap.n_mt;
+      ap.lens = d_lens; ap.ctx = e->ctx.as<__nv_bfloat16>();
       B200_PROF("attention", 4.0 * batch * (double)seq * seq * H, 2.0 * 4.0 * n_tok * H, st);
-      attention_tc_kernel<<<std::min(ap.n_items, e->num_sms), ATT_THREADS, att_tc_smem, st>>>(map_att, ap);
+      attention_tc_kernel<<<std::min(ap.n_units, 2 * e->num_sms), ATT_THREADS, att_tc_smem, st>>>(map_att_q, map_att_kv, ap);
     } else {
       B200_PROF("attention", 4.0 * batch * (double)seq * seq * H, 2.0 * 4.0 * n_tok * H, st);
       if (dh == 32)
