@@ -27,7 +27,8 @@ struct LayerWeights {
   DevBuf wqkv, wo, w1, w2;              // bf16
   DevBuf bqkv, bo, b1, b2;              // fp32
   DevBuf ln1_g, ln1_b, ln2_g, ln2_b;    // fp32
-  CUtensorMap map_wqkv, map_wo, map_w1, map_w2;
+  CUtensorMap map_wqkv, map_wo, map_w1, map_w2;           // box rows = BLOCK_N
+  CUtensorMap map_wqkv_h, map_wo_h, map_w1_h, map_w2_h;   // box rows = BLOCK_N / 2 (one CTA's share in a CTA pair)
 };
 
 uint16_t f32_to_bf16_host(float f) {
@@ -83,14 +84,15 @@ static int pick_block_n(int N) {
 struct GemmIO {
   const CUtensorMap* a;      // activations [M, K], box {64, 128}
   const CUtensorMap* w;      // weights [N, K], box {64, BLOCK_N}
+  const CUtensorMap* w2;     // weights [N, K], box {64, BLOCK_N / 2} (CTA-pair kernel) or nullptr
   const CUtensorMap* out;    // output [M, N], box {64, 32} (TMA store)
   const CUtensorMap* resid;  // residual [M, N], box {64, 32} (TMA load) or the same as out when unused
 };
 
-template <int BLOCK_N, int EPI>
+template <int BLOCK_N, int EPI, int CG>
 static int launch_gemm_t(const b200_encoder* e, const GemmIO& io, GemmParams p, cudaStream_t st) {
   constexpr int NEPI = gemm_epi_warps(BLOCK_N);
-  const size_t stage = (size_t)GEMM_A_STAGE_BYTES + (size_t)BLOCK_N * GEMM_BLOCK_K * 2;
+  const size_t stage = (size_t)GEMM_A_STAGE_BYTES + (size_t)(BLOCK_N / CG) * GEMM_BLOCK_K * 2;
   const size_t max_smem = 232448;
   // staging boxes, barriers (2*nstage + 4 + NEPI, at most 8 stages), TMEM slot, per-warp bias slices
   const size_t tail = (size_t)NEPI * GEMM_STAGING_BYTES + 8 * (2 * 8 + 4 + NEPI) + 16 + (size_t)NEPI * GEMM_OUT_CHUNK * 4;
@@ -98,15 +100,28 @@ static int launch_gemm_t(const b200_encoder* e, const GemmIO& io, GemmParams p, 
   if (nstage < 2) B200_FAIL(B200_ERR_UNSUPPORTED, "GEMM tile does not fit in shared memory");
   p.nstage = nstage;
   const size_t smem = 1024 + (size_t)nstage * stage + tail;
-  auto kern = gemm_bf16_kernel<BLOCK_N, EPI>;
+  auto kern = gemm_bf16_kernel<BLOCK_N, EPI, CG>;
   B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  const int tiles = (p.M / GEMM_BLOCK_M) * (p.N / BLOCK_N);
-  const int grid = std::min(tiles, e->num_sms);
+  const int tiles = (p.M / (GEMM_BLOCK_M * CG)) * (p.N / BLOCK_N);
+  const int grid = std::min(tiles, e->num_sms / CG) * CG;
   {
     B200_PROF(EPI == EPI_BIAS ? "gemm_bias" : (EPI == EPI_BIAS_GELU ? "gemm_bias_gelu" : "gemm_bias_resid"),
               2.0 * p.M * (double)p.N * p.K,
               2.0 * ((double)p.M * p.K + (double)p.N * p.K + (double)p.M * p.N * (EPI == EPI_BIAS_RESID ? 2 : 1)), st);
-    kern<<<grid, gemm_threads(BLOCK_N), smem, st>>>(*io.a, *io.w, *io.out, *io.resid, p);
+    if (CG == 1) {
+      kern<<<grid, gemm_threads(BLOCK_N), smem, st>>>(*io.a, *io.w, *io.out, *io.resid, p);
+    } else {
+      cudaLaunchConfig_t cfg{};
+      cfg.gridDim = dim3(grid);
+      cfg.blockDim = dim3(gemm_threads(BLOCK_N));
+      cfg.dynamicSmemBytes = smem;
+      cfg.stream = st;
+      cudaLaunchAttribute attr[1];
+      attr[0].id = cudaLaunchAttributeClusterDimension;
+      attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+      cfg.attrs = attr; cfg.numAttrs = 1;
+      B200_CUDA(cudaLaunchKernelEx(&cfg, kern, *io.a, *io.w2, *io.out, *io.resid, p));
+    }
   }
   B200_CUDA(cudaGetLastError());
   return B200_OK;
@@ -114,16 +129,19 @@ static int launch_gemm_t(const b200_encoder* e, const GemmIO& io, GemmParams p, 
 
 template <int EPI>
 static int launch_gemm(const b200_encoder* e, const GemmIO& io, const GemmParams& p, cudaStream_t st) {
+  // CTA pairs need whole 256-row tiles; B200_GEMM_CG=1 forces single-CTA tiles (A/B timing)
+  const char* cg_env = getenv("B200_GEMM_CG");
+  const bool pair = (p.M % (2 * GEMM_BLOCK_M) == 0) && io.w2 != nullptr && !(cg_env && atoi(cg_env) == 1);
   switch (pick_block_n(p.N)) {
-    case 192: return launch_gemm_t<192, EPI>(e, io, p, st);
-    case 128: return launch_gemm_t<128, EPI>(e, io, p, st);
-    case 64: return launch_gemm_t<64, EPI>(e, io, p, st);
+    case 192: return pair ? launch_gemm_t<192, EPI, 2>(e, io, p, st) : launch_gemm_t<192, EPI, 1>(e, io, p, st);
+    case 128: return pair ? launch_gemm_t<128, EPI, 2>(e, io, p, st) : launch_gemm_t<128, EPI, 1>(e, io, p, st);
+    case 64: return launch_gemm_t<64, EPI, 1>(e, io, p, st);
   }
   B200_FAIL(B200_ERR_UNSUPPORTED, "GEMM N=%d is not a multiple of 64", p.N);
 }
 
-static int weight_map(CUtensorMap* m, const DevBuf& w, int N, int K) {
-  return make_tma_2d_bf16(m, w.p, (uint64_t)N, (uint64_t)K, (uint32_t)pick_block_n(N), GEMM_BLOCK_K);
+static int weight_map(CUtensorMap* m, const DevBuf& w, int N, int K, int cg = 1) {
+  return make_tma_2d_bf16(m, w.p, (uint64_t)N, (uint64_t)K, (uint32_t)(pick_block_n(N) / cg), GEMM_BLOCK_K);
 }
 
 static int ensure_activations(b200_encoder* e, int64_t m_rows, int batch, cudaStream_t st) {
@@ -131,7 +149,7 @@ static int ensure_activations(b200_encoder* e, int64_t m_rows, int batch, cudaSt
   B200_TRY(e->lens.grow((size_t)std::max(batch, 1) * 4, 0, st));
   B200_TRY(e->out.grow((size_t)std::max(batch, 1) * H * 4, 0, st));
   if (m_rows <= e->m_cap) return B200_OK;
-  const int64_t m = (m_rows + 127) / 128 * 128;
+  const int64_t m = (m_rows + 255) / 256 * 256;   // whole 256-row tiles for the CTA-pair GEMM
   B200_TRY(e->ids.grow((size_t)m * 4, 0, st));
   B200_TRY(e->x.grow((size_t)m * H * 2, 0, st));
   B200_TRY(e->qkv.grow((size_t)m * 3 * H * 2, 0, st));
@@ -168,7 +186,7 @@ static int run_encoder(b200_encoder* e, const int32_t* d_ids, const int32_t* d_l
                        cudaStream_t st) {
   const int H = e->cfg.hidden, I = e->cfg.intermediate, heads = e->cfg.heads, dh = H / heads;
   const int n_tok = batch * seq;
-  const int M = (n_tok + 127) / 128 * 128;
+  const int M = (n_tok + 255) / 256 * 256;
   const int wpb = 8;
   __nv_bfloat16* x = e->x.as<__nv_bfloat16>();
   __nv_bfloat16* y = e->y.as<__nv_bfloat16>();
@@ -199,7 +217,7 @@ static int run_encoder(b200_encoder* e, const int32_t* d_ids, const int32_t* d_l
     GemmParams p{};
     // Q,K,V projections in one GEMM: qkv = x Wqkv^T + bqkv
     p.M = M; p.N = 3 * H; p.K = H; p.bias = L->bqkv.as<float>();
-    B200_TRY(launch_gemm<EPI_BIAS>(e, GemmIO{&e->map_x, &L->map_wqkv, &e->map_qkv_st, &e->map_qkv_st}, p, st));
+    B200_TRY(launch_gemm<EPI_BIAS>(e, GemmIO{&e->map_x, &L->map_wqkv, &L->map_wqkv_h, &e->map_qkv_st, &e->map_qkv_st}, p, st));
     if (use_att_tc) {
       AttParams ap;
       ap.S = seq; ap.H = H; ap.heads = heads; ap.n_mt = (seq + 127) / 128; ap.n_units = batch * heads * ap.n_mt;
@@ -218,15 +236,15 @@ static int run_encoder(b200_encoder* e, const int32_t* d_ids, const int32_t* d_l
     B200_CUDA(cudaGetLastError());
     // y = ctx Wo^T + bo + x ; x = LN(y)
     p.N = H; p.K = H; p.bias = L->bo.as<float>();
-    B200_TRY(launch_gemm<EPI_BIAS_RESID>(e, GemmIO{&e->map_ctx, &L->map_wo, &e->map_y_st, &e->map_x_res}, p, st));
+    B200_TRY(launch_gemm<EPI_BIAS_RESID>(e, GemmIO{&e->map_ctx, &L->map_wo, &L->map_wo_h, &e->map_y_st, &e->map_x_res}, p, st));
     layernorm_kernel<NV><<<(n_tok + wpb - 1) / wpb, wpb * 32, 0, st>>>(y, n_tok, L->ln1_g.as<float>(), L->ln1_b.as<float>(),
                                                                       e->cfg.ln_eps, x);
     B200_CUDA(cudaGetLastError());
     // ffn = gelu(x W1^T + b1) ; y = ffn W2^T + b2 + x ; x = LN(y)
     p.N = I; p.K = H; p.bias = L->b1.as<float>();
-    B200_TRY(launch_gemm<EPI_BIAS_GELU>(e, GemmIO{&e->map_x, &L->map_w1, &e->map_ffn_st, &e->map_ffn_st}, p, st));
+    B200_TRY(launch_gemm<EPI_BIAS_GELU>(e, GemmIO{&e->map_x, &L->map_w1, &L->map_w1_h, &e->map_ffn_st, &e->map_ffn_st}, p, st));
     p.N = H; p.K = I; p.bias = L->b2.as<float>();
-    B200_TRY(launch_gemm<EPI_BIAS_RESID>(e, GemmIO{&e->map_ffn, &L->map_w2, &e->map_y_st, &e->map_x_res}, p, st));
+    B200_TRY(launch_gemm<EPI_BIAS_RESID>(e, GemmIO{&e->map_ffn, &L->map_w2, &L->map_w2_h, &e->map_y_st, &e->map_x_res}, p, st));
     layernorm_kernel<NV><<<(n_tok + wpb - 1) / wpb, wpb * 32, 0, st>>>(y, n_tok, L->ln2_g.as<float>(), L->ln2_b.as<float>(),
                                                                       e->cfg.ln_eps, x);
     B200_CUDA(cudaGetLastError());
@@ -335,6 +353,10 @@ int b200_encoder_finalize(b200_encoder_t* e) {
     B200_TRY(weight_map(&L->map_wo, L->wo, (int)H, (int)H));
     B200_TRY(weight_map(&L->map_w1, L->w1, (int)I, (int)H));
     B200_TRY(weight_map(&L->map_w2, L->w2, (int)H, (int)I));
+    B200_TRY(weight_map(&L->map_wqkv_h, L->wqkv, (int)(3 * H), (int)H, 2));
+    B200_TRY(weight_map(&L->map_wo_h, L->wo, (int)H, (int)H, 2));
+    B200_TRY(weight_map(&L->map_w1_h, L->w1, (int)I, (int)H, 2));
+    B200_TRY(weight_map(&L->map_w2_h, L->w2, (int)H, (int)I, 2));
   }
   e->pending.clear();
   e->finalized = true;

@@ -155,34 +155,45 @@ B200_DEVINL float gelu_erf(float x) {
   return fmaf(hx, th, hx);
 }
 
-template <int BLOCK_N, int EPI>
+// CG = 1: one CTA per 128 x BLOCK_N tile.  CG = 2: a CTA pair (cluster of 2, cta_group::2) per
+// 256 x BLOCK_N tile -- each CTA loads its own 128 rows of A but only HALF of the weight tile, and the
+// leader's single MMA drives both SMs' tensor cores.  That halves the weight bytes every SM pulls
+// through L2 per flop (the CG = 1 kernel saturates the L2 -> SM path at ~77 flop/B) and leaves room
+// for a deeper TMA ring.
+template <int BLOCK_N, int EPI, int CG>
 __global__ void __launch_bounds__(gemm_threads(BLOCK_N), 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                  const __grid_constant__ CUtensorMap map_out, const __grid_constant__ CUtensorMap map_resid,
                  const GemmParams p) {
-  constexpr uint32_t B_STAGE_BYTES = BLOCK_N * GEMM_BLOCK_K * 2;
+  constexpr uint32_t B_ROWS = BLOCK_N / CG;                      // weight rows this CTA loads per stage
+  constexpr uint32_t B_STAGE_BYTES = B_ROWS * GEMM_BLOCK_K * 2;
   constexpr uint32_t STAGE_BYTES = GEMM_A_STAGE_BYTES + B_STAGE_BYTES;
-  constexpr uint32_t IDESC = umma_idesc_bf16_f32(GEMM_BLOCK_M, BLOCK_N);
+  constexpr uint32_t IDESC = umma_idesc_bf16_f32(GEMM_BLOCK_M * CG, BLOCK_N);
   constexpr uint32_t TMEM_COLS = (2 * BLOCK_N <= 128) ? 128 : ((2 * BLOCK_N <= 256) ? 256 : 512);
   constexpr int NEPI = gemm_epi_warps(BLOCK_N);
   static_assert(BLOCK_N % 64 == 0 && BLOCK_N <= 256, "BLOCK_N must be 64..256 in steps of 64");
+  static_assert(CG == 1 || CG == 2, "CTA group is 1 or 2");
+  static_assert(STAGE_BYTES % 1024 == 0, "stages must keep the 1024-byte swizzle alignment");
 
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* staging = smem + (size_t)p.nstage * STAGE_BYTES;                 // [NEPI][4 KB], 1024-aligned
   uint64_t* bars = reinterpret_cast<uint64_t*>(staging + (size_t)NEPI * GEMM_STAGING_BYTES);
-  uint64_t* full = bars;                       // [nstage]  TMA -> MMA
-  uint64_t* empty = bars + p.nstage;           // [nstage]  MMA -> TMA
-  uint64_t* acc_full = bars + 2 * p.nstage;    // [2]       MMA -> epilogue
-  uint64_t* acc_empty = acc_full + 2;          // [2]       epilogue -> MMA
+  uint64_t* full = bars;                       // [nstage]  TMA -> MMA          (leader's copy is the one used)
+  uint64_t* empty = bars + p.nstage;           // [nstage]  MMA -> TMA          (one per CTA)
+  uint64_t* acc_full = bars + 2 * p.nstage;    // [2]       MMA -> epilogue     (one per CTA)
+  uint64_t* acc_empty = acc_full + 2;          // [2]       epilogue -> MMA     (leader's copy is the one used)
   uint64_t* resid_bar = acc_empty + 2;         // [NEPI]    residual box landed (one per epilogue warp)
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(resid_bar + NEPI);
   float* bias_smem = reinterpret_cast<float*>(tmem_slot + 4);               // [NEPI][64]
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+  const int rank = (CG == 2) ? (int)cluster_ctarank() : 0;
+  const bool leader = rank == 0;
   const int n_tiles = p.N / BLOCK_N;
-  const int total_tiles = (p.M / GEMM_BLOCK_M) * n_tiles;
+  const int total_tiles = (p.M / (GEMM_BLOCK_M * CG)) * n_tiles;   // tiles of the CTA group
+  const int group = blockIdx.x / CG, n_groups = gridDim.x / CG;
   const int num_k = p.K / GEMM_BLOCK_K;
 
   if (warp == 0 && lane == 0) {
@@ -193,47 +204,58 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
   }
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < p.nstage; ++i) {
-      mbar_init(&full[i], 1);
+      mbar_init(&full[i], CG);                 // one arrival per CTA of the group
       mbar_init(&empty[i], 1);
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&acc_full[i], 1);
-      mbar_init(&acc_empty[i], NEPI);
+      mbar_init(&acc_empty[i], NEPI * CG);
     }
     for (int i = 0; i < NEPI; ++i) mbar_init(&resid_bar[i], 1);
     fence_mbar_init();
   }
-  if (warp == 2) tmem_alloc(tmem_slot, TMEM_COLS);
+  if (warp == 2) {
+    if (CG == 2) tmem_alloc_2sm(tmem_slot, TMEM_COLS);
+    else tmem_alloc(tmem_slot, TMEM_COLS);
+  }
   tc_fence_before();
-  __syncthreads();
+  if (CG == 2) cluster_sync_all();             // the peer's barriers are initialised before anyone signals them
+  else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
-    // ===== TMA producer =====
+    // ===== TMA producer (every CTA loads its own A rows and its share of the weight tile) =====
     if (lane == 0) {
       int s = 0;
       uint32_t ph = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-        const int m0 = (tile / n_tiles) * GEMM_BLOCK_M;
-        const int n0 = (tile % n_tiles) * BLOCK_N;
+      for (int tile = group; tile < total_tiles; tile += n_groups) {
+        const int m0 = (tile / n_tiles) * (GEMM_BLOCK_M * CG) + rank * GEMM_BLOCK_M;
+        const int n0 = (tile % n_tiles) * BLOCK_N + rank * (int)B_ROWS;
         for (int kb = 0; kb < num_k; ++kb) {
           mbar_wait(&empty[s], ph ^ 1);
-          mbar_arrive_expect_tx(&full[s], STAGE_BYTES);
           uint8_t* sa = smem + (size_t)s * STAGE_BYTES;
-          tma_load_2d(sa, &map_a, &full[s], kb * GEMM_BLOCK_K, m0);
-          tma_load_2d(sa + GEMM_A_STAGE_BYTES, &map_b, &full[s], kb * GEMM_BLOCK_K, n0);
+          if (CG == 2) {
+            if (leader) mbar_arrive_expect_tx(&full[s], STAGE_BYTES * CG);
+            else mbar_arrive_leader(&full[s]);
+            tma_load_2d_2sm(sa, &map_a, &full[s], kb * GEMM_BLOCK_K, m0);
+            tma_load_2d_2sm(sa + GEMM_A_STAGE_BYTES, &map_b, &full[s], kb * GEMM_BLOCK_K, n0);
+          } else {
+            mbar_arrive_expect_tx(&full[s], STAGE_BYTES);
+            tma_load_2d(sa, &map_a, &full[s], kb * GEMM_BLOCK_K, m0);
+            tma_load_2d(sa + GEMM_A_STAGE_BYTES, &map_b, &full[s], kb * GEMM_BLOCK_K, n0);
+          }
           if (++s == p.nstage) { s = 0; ph ^= 1; }
         }
       }
     }
   } else if (warp == 1) {
-    // ===== MMA issuer (one thread) =====
-    if (lane == 0) {
+    // ===== MMA issuer (one thread of the leader CTA) =====
+    if (lane == 0 && leader) {
       int s = 0;
       uint32_t ph = 0, it = 0;
       const uint32_t smem_addr = smem_u32(smem);
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
+      for (int tile = group; tile < total_tiles; tile += n_groups, ++it) {
         const uint32_t as = it & 1, aph = (it >> 1) & 1;
         mbar_wait(&acc_empty[as], aph ^ 1);
         tc_fence_after();
@@ -245,16 +267,18 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
           const uint64_t da = umma_smem_desc_sw128(a_addr);
           const uint64_t db = umma_smem_desc_sw128(a_addr + GEMM_A_STAGE_BYTES);
 #pragma unroll
-          for (int k = 0; k < GEMM_BLOCK_K / 16; ++k)
-            umma_bf16(tacc, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), IDESC, (uint32_t)((kb | k) != 0));
-          umma_commit(&empty[s]);
+          for (int k = 0; k < GEMM_BLOCK_K / 16; ++k) {
+            if (CG == 2) umma_bf16_2sm(tacc, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), IDESC, (uint32_t)((kb | k) != 0));
+            else umma_bf16(tacc, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), IDESC, (uint32_t)((kb | k) != 0));
+          }
+          if (CG == 2) umma_commit_2sm(&empty[s]); else umma_commit(&empty[s]);
           if (++s == p.nstage) { s = 0; ph ^= 1; }
         }
-        umma_commit(&acc_full[as]);
+        if (CG == 2) umma_commit_2sm(&acc_full[as]); else umma_commit(&acc_full[as]);
       }
     }
   } else if (warp >= 4) {
-    // ===== epilogue warp: TMEM lanes [32 wq, +32) x columns [64 chunk, +64) of every tile =====
+    // ===== epilogue warp: TMEM lanes [32 wq, +32) x columns [64 chunk, +64) of this CTA's 128 rows =====
     const int e = warp - 4;
     const int wq = e & 3;         // == warp % 4: the TMEM lane group this warp may read
     const int chunk = e >> 2;
@@ -264,9 +288,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     uint8_t* my_row = stg + lane * 128;
     const int sw = lane & 7;       // 128-byte swizzle: 16-byte chunk j of row r lives at chunk j ^ (r % 8)
     uint32_t it = 0;
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
+    for (int tile = group; tile < total_tiles; tile += n_groups, ++it) {
       const uint32_t as = it & 1, aph = (it >> 1) & 1;
-      const int m0 = (tile / n_tiles) * GEMM_BLOCK_M + wq * 32;
+      const int m0 = (tile / n_tiles) * (GEMM_BLOCK_M * CG) + rank * GEMM_BLOCK_M + wq * 32;
       const int n0 = (tile % n_tiles) * BLOCK_N + chunk * GEMM_OUT_CHUNK;
       __syncwarp();
       sbias[lane] = __ldg(p.bias + n0 + lane);
@@ -286,7 +310,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
       tmem_ld_wait();
       tc_fence_before();         // this warp's share of the accumulator stage is in registers
       __syncwarp();
-      if (lane == 0) mbar_arrive(&acc_empty[as]);
+      if (lane == 0) {
+        if (CG == 2) mbar_arrive_leader(&acc_empty[as]); else mbar_arrive(&acc_empty[as]);
+      }
       if (EPI == EPI_BIAS_RESID) mbar_wait(rbar, it & 1);
 #pragma unroll
       for (int j = 0; j < 8; ++j) {   // 8 columns = one 16-byte piece of this thread's row
@@ -331,10 +357,12 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
   }
 
   tc_fence_before();
-  __syncthreads();
+  if (CG == 2) cluster_sync_all();             // no CTA leaves while its peer may still signal its barriers
+  else __syncthreads();
   if (warp == 2) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, TMEM_COLS);
+    if (CG == 2) tmem_dealloc_2sm(tmem_base, TMEM_COLS);
+    else tmem_dealloc(tmem_base, TMEM_COLS);
   }
 }
 
