@@ -151,14 +151,17 @@ static int index_reserve_locked(b200_index* ix, int64_t cap, cudaStream_t st) {
   return B200_OK;
 }
 
-template <int BLOCK_N, int KP>
+// CG = 2 runs CTA pairs (two query tiles per cluster); nqt is then the even number of query tiles.
+template <int BLOCK_N, int KP, int CG>
 static int launch_sim(b200_index* ix, int nq, int nqt, const CUtensorMap& map_q, cudaStream_t st, int* nsplit_out) {
   const int kc = ix->dpad / SIM_BLOCK_K;
   const size_t a_bytes = (size_t)kc * SIM_A_CHUNK_BYTES;
   const size_t list_bytes = (size_t)SIM_BLOCK_M * (KP + 1) * 8;
-  const size_t stage_bytes = (size_t)BLOCK_N * SIM_BLOCK_K * 2;
+  const size_t stage_bytes = (size_t)(BLOCK_N / CG) * SIM_BLOCK_K * 2;
   const size_t fixed = 1024 + a_bytes + list_bytes + 256;
   const size_t max_smem = 232448;  // 227 KB opt-in limit per CTA
+  const int units = nqt / CG;              // CTA groups per corpus slice
+  const int slots = ix->num_sms / CG;      // CTA groups resident at once
   if (fixed + 2 * stage_bytes > max_smem)
     B200_FAIL(B200_ERR_UNSUPPORTED, "dimension %d needs %zu bytes of shared memory for the query tile", ix->dim, fixed);
   int nstage = (int)std::min<size_t>(8, (max_smem - fixed) / stage_bytes);
@@ -173,12 +176,12 @@ static int launch_sim(b200_index* ix, int nq, int nqt, const CUtensorMap& map_q,
   int best = 1;
   double best_cost = 1e300;
   for (int w = 1; w <= 12; ++w) {
-    int ns = std::min(max_split, std::max(1, (ix->num_sms * w) / nqt));
+    int ns = std::min(max_split, std::max(1, (slots * w) / units));
     const uint32_t t = (total_tiles + ns - 1) / ns;
     ns = (int)((total_tiles + t - 1) / t);
     if (w > 1 && t < 8) break;
-    const long items = (long)ns * nqt;
-    const long waves = (items + ix->num_sms - 1) / ix->num_sms;
+    const long items = (long)ns * units;
+    const long waves = (items + slots - 1) / slots;
     const double cost = (double)waves * ((double)t + 2.0);
     if (cost < best_cost * 0.995) { best_cost = cost; best = ns; }
   }
@@ -193,7 +196,7 @@ static int launch_sim(b200_index* ix, int nq, int nqt, const CUtensorMap& map_q,
   B200_CUDA(cudaMemsetAsync(ix->gbkt.p, 0, bkt_words * 4, st));
 
   CUtensorMap map_c;
-  B200_TRY(make_tma_2d_bf16(&map_c, ix->search.p, (uint64_t)ix->count, (uint64_t)ix->dpad, BLOCK_N, SIM_BLOCK_K));
+  B200_TRY(make_tma_2d_bf16(&map_c, ix->search.p, (uint64_t)ix->count, (uint64_t)ix->dpad, BLOCK_N / CG, SIM_BLOCK_K));
 
   SimParams p;
   p.nq = nq; p.kc = kc; p.nstage = nstage; p.n_rows = n_rows; p.tiles_per_split = tps; p.nsplit = nsplit;
@@ -202,14 +205,29 @@ static int launch_sim(b200_index* ix, int nq, int nqt, const CUtensorMap& map_q,
   p.refresh_mask = 0; p.use_gthr = 1; p.split_major = 0;
   if (const char* e = getenv("B200_SIM_REFRESH")) p.refresh_mask = (uint32_t)atoi(e);   // tuning knobs (benchmarks only)
   if (const char* e = getenv("B200_SIM_BOUND")) { const int m = atoi(e); p.use_bound = (m & 1) && nsplit >= KP; p.use_gthr = (m >> 1) & 1; p.split_major = (m >> 2) & 1; }
-  auto kern = sim_topk_kernel<BLOCK_N, KP>;
+  if (CG == 2) p.split_major = 0;
+  auto kern = sim_topk_kernel<BLOCK_N, KP, CG>;
   B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   {
     // algorithmic work of one pass: every corpus row read once (768 B at dim 384) and 2*dpad flops
     // per (query, row) pair
     B200_PROF("sim_topk", 2.0 * nq * (double)n_rows * ix->dpad, (double)n_rows * ix->dpad * 2.0, st);
-      if (p.split_major) kern<<<dim3(nsplit, nqt), SIM_THREADS, smem, st>>>(map_q, map_c, p);
-    else kern<<<dim3(nqt, nsplit), SIM_THREADS, smem, st>>>(map_q, map_c, p);
+    if (CG == 2) {
+      cudaLaunchConfig_t cfg{};
+      cfg.gridDim = dim3(nqt, nsplit);          // consecutive blockIdx.x = the two CTAs of a pair
+      cfg.blockDim = dim3(SIM_THREADS);
+      cfg.dynamicSmemBytes = smem;
+      cfg.stream = st;
+      cudaLaunchAttribute attr[1];
+      attr[0].id = cudaLaunchAttributeClusterDimension;
+      attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+      cfg.attrs = attr; cfg.numAttrs = 1;
+      B200_CUDA(cudaLaunchKernelEx(&cfg, kern, map_q, map_c, p));
+    } else if (p.split_major) {
+      kern<<<dim3(nsplit, nqt), SIM_THREADS, smem, st>>>(map_q, map_c, p);
+    } else {
+      kern<<<dim3(nqt, nsplit), SIM_THREADS, smem, st>>>(map_q, map_c, p);
+    }
   }
   B200_CUDA(cudaGetLastError());
   *nsplit_out = nsplit;
@@ -218,7 +236,12 @@ static int launch_sim(b200_index* ix, int nq, int nqt, const CUtensorMap& map_q,
 
 static int search_chunk(b200_index* ix, const void* q_dev, int q_dtype, int nq, int k, int kp, int64_t id_base,
                         int64_t* ids_dev, float* sc_dev, cudaStream_t st) {
-  const int nqt = (nq + SIM_BLOCK_M - 1) / SIM_BLOCK_M;
+  int nqt = (nq + SIM_BLOCK_M - 1) / SIM_BLOCK_M;
+  // CTA pairs (two query tiles per cluster) for k <= 10 once there are at least two query tiles; an odd
+  // tile count is padded with an empty tile.  B200_SIM_CG=1 forces single-CTA tiles (A/B timing).
+  const char* cg_env = getenv("B200_SIM_CG");
+  const bool pair = kp == 16 && nqt >= 2 && !(cg_env && atoi(cg_env) == 1);
+  if (pair) nqt = (nqt + 1) & ~1;
   const int nq_pad = nqt * SIM_BLOCK_M;
   B200_TRY(ix->q_bf16.grow((size_t)nq_pad * ix->dpad * 2, 0, st));
   B200_TRY(ix->q_f32.grow((size_t)nq * ix->dim * 4, 0, st));
@@ -234,9 +257,10 @@ static int search_chunk(b200_index* ix, const void* q_dev, int q_dtype, int nq, 
   CUtensorMap map_q;
   B200_TRY(make_tma_2d_bf16(&map_q, ix->q_bf16.p, (uint64_t)nq_pad, (uint64_t)ix->dpad, SIM_BLOCK_M, SIM_BLOCK_K));
   int nsplit = 0;
-  if (kp == 16) B200_TRY((launch_sim<256, 16>(ix, nq, nqt, map_q, st, &nsplit)));
-  else if (kp == 32) B200_TRY((launch_sim<128, 32>(ix, nq, nqt, map_q, st, &nsplit)));
-  else B200_TRY((launch_sim<128, 64>(ix, nq, nqt, map_q, st, &nsplit)));
+  if (pair) B200_TRY((launch_sim<256, 16, 2>(ix, nq, nqt, map_q, st, &nsplit)));
+  else if (kp == 16) B200_TRY((launch_sim<256, 16, 1>(ix, nq, nqt, map_q, st, &nsplit)));
+  else if (kp == 32) B200_TRY((launch_sim<128, 32, 1>(ix, nq, nqt, map_q, st, &nsplit)));
+  else B200_TRY((launch_sim<128, 64, 1>(ix, nq, nqt, map_q, st, &nsplit)));
 
   MergeParams m;
   m.nq = nq; m.nsplit = nsplit; m.kp = kp; m.k = k; m.d = ix->dim;
@@ -617,7 +641,7 @@ int launch_sim_static(b200_index* ix, int nq, const CUtensorMap& map_q, uint64_t
   p.cand = cand; p.gbkt = gthr; p.use_bound = nsplit >= KP;
   p.gthr = gthr + (size_t)kStaticMaxQueries * KP;
   p.refresh_mask = 0; p.use_gthr = 0; p.split_major = 0;
-  auto kern = sim_topk_kernel<BLOCK_N, KP>;
+  auto kern = sim_topk_kernel<BLOCK_N, KP, 1>;
   B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   kern<<<dim3(1, nsplit), SIM_THREADS, smem, st>>>(map_q, map_c, p);
   B200_CUDA(cudaGetLastError());

@@ -158,12 +158,20 @@ __device__ __noinline__ uint64_t topk_replace_worst(uint64_t* keys, int wpos, fl
   return ((uint64_t)__float_as_uint(thr) << 32) | (uint32_t)wp;
 }
 
-template <int BLOCK_N, int KP>
+// CG = 1: one CTA per (query tile, corpus slice).  CG = 2: a CTA pair (cluster of 2, cta_group::2)
+// per (two query tiles, corpus slice): each CTA keeps its own 128 queries resident and loads only
+// HALF of every corpus tile; the leader's MMA (M = 256) drives both SMs' tensor cores and each CTA
+// drains the scores of its own queries from its own TMEM.  Half the corpus bytes per SM per flop
+// means the same shared-memory ring hides twice the latency and the L2 -> SM path carries half the
+// traffic -- the two things that kept the single-CTA kernel at ~60 % of the tensor roofline.
+template <int BLOCK_N, int KP, int CG>
 __global__ void __launch_bounds__(SIM_THREADS, 1)
 sim_topk_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_c,
                 const SimParams p) {
-  constexpr uint32_t B_STAGE_BYTES = BLOCK_N * SIM_BLOCK_K * 2;
-  constexpr uint32_t IDESC = umma_idesc_bf16_f32(SIM_BLOCK_M, BLOCK_N);
+  constexpr uint32_t B_ROWS = BLOCK_N / CG;                     // corpus rows this CTA loads per tile
+  constexpr uint32_t B_STAGE_BYTES = B_ROWS * SIM_BLOCK_K * 2;
+  constexpr uint32_t IDESC = umma_idesc_bf16_f32(SIM_BLOCK_M * CG, BLOCK_N);
+  static_assert(CG == 1 || CG == 2, "CTA group is 1 or 2");
   constexpr uint32_t TMEM_COLS = 2 * BLOCK_N;  // two accumulator stages
   static_assert(TMEM_COLS == 256 || TMEM_COLS == 512, "TMEM allocation must be a power of two");
 
@@ -182,8 +190,10 @@ sim_topk_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  const int qtile = p.split_major ? blockIdx.y : blockIdx.x;
-  const int split = p.split_major ? blockIdx.x : blockIdx.y;
+  const int qtile = (CG == 1 && p.split_major) ? blockIdx.y : blockIdx.x;   // CTA pair = query tiles (2i, 2i+1)
+  const int split = (CG == 1 && p.split_major) ? blockIdx.x : blockIdx.y;
+  const int rank = (CG == 2) ? (int)cluster_ctarank() : 0;
+  const bool leader = rank == 0;
 
   const uint32_t total_tiles = (p.n_rows + BLOCK_N - 1) / BLOCK_N;
   const uint32_t tile0 = (uint32_t)split * p.tiles_per_split;
@@ -195,45 +205,62 @@ sim_topk_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant
   }
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < p.nstage; ++i) {
-      mbar_init(&full[i], 1);
+      mbar_init(&full[i], CG);      // one arrival per CTA of the group (the leader's copy is used)
       mbar_init(&empty[i], 1);
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&acc_full[i], 1);
-      mbar_init(&acc_empty[i], 4);  // one arrival per drain warp
+      mbar_init(&acc_empty[i], 4 * CG);  // one arrival per drain warp of the group (leader's copy)
     }
-    mbar_init(a_full, 1);
+    mbar_init(a_full, CG);
     fence_mbar_init();
   }
-  if (warp == 2) tmem_alloc(tmem_slot, TMEM_COLS);
+  if (warp == 2) {
+    if (CG == 2) tmem_alloc_2sm(tmem_slot, TMEM_COLS);
+    else tmem_alloc(tmem_slot, TMEM_COLS);
+  }
   // candidate sets start empty
   for (int i = threadIdx.x; i < SIM_BLOCK_M * (KP + 1); i += SIM_THREADS) ckeys[i] = 0;
   tc_fence_before();
-  __syncthreads();
+  if (CG == 2) cluster_sync_all();   // the peer's barriers exist before anyone signals them
+  else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
     // ===== TMA producer =====
     if (lane == 0 && ntiles > 0) {
-      mbar_arrive_expect_tx(a_full, (uint32_t)p.kc * SIM_A_CHUNK_BYTES);
-      for (int c = 0; c < p.kc; ++c)
-        tma_load_2d(sA + (size_t)c * SIM_A_CHUNK_BYTES, &map_q, a_full, c * SIM_BLOCK_K, qtile * SIM_BLOCK_M);
+      if (CG == 2) {
+        if (leader) mbar_arrive_expect_tx(a_full, (uint32_t)p.kc * SIM_A_CHUNK_BYTES * CG);
+        else mbar_arrive_leader(a_full);
+        for (int c = 0; c < p.kc; ++c)
+          tma_load_2d_2sm(sA + (size_t)c * SIM_A_CHUNK_BYTES, &map_q, a_full, c * SIM_BLOCK_K, qtile * SIM_BLOCK_M);
+      } else {
+        mbar_arrive_expect_tx(a_full, (uint32_t)p.kc * SIM_A_CHUNK_BYTES);
+        for (int c = 0; c < p.kc; ++c)
+          tma_load_2d(sA + (size_t)c * SIM_A_CHUNK_BYTES, &map_q, a_full, c * SIM_BLOCK_K, qtile * SIM_BLOCK_M);
+      }
       int s = 0;
       uint32_t ph = 0;
       for (uint32_t t = 0; t < ntiles; ++t) {
-        const int32_t row = (int32_t)((tile0 + t) * BLOCK_N);
+        const int32_t row = (int32_t)((tile0 + t) * BLOCK_N + rank * B_ROWS);
         for (int c = 0; c < p.kc; ++c) {
           mbar_wait(&empty[s], ph ^ 1);
-          mbar_arrive_expect_tx(&full[s], B_STAGE_BYTES);
-          tma_load_2d(sB + (size_t)s * B_STAGE_BYTES, &map_c, &full[s], c * SIM_BLOCK_K, row);
+          if (CG == 2) {
+            if (leader) mbar_arrive_expect_tx(&full[s], B_STAGE_BYTES * CG);
+            else mbar_arrive_leader(&full[s]);
+            tma_load_2d_2sm(sB + (size_t)s * B_STAGE_BYTES, &map_c, &full[s], c * SIM_BLOCK_K, row);
+          } else {
+            mbar_arrive_expect_tx(&full[s], B_STAGE_BYTES);
+            tma_load_2d(sB + (size_t)s * B_STAGE_BYTES, &map_c, &full[s], c * SIM_BLOCK_K, row);
+          }
           if (++s == p.nstage) { s = 0; ph ^= 1; }
         }
       }
     }
   } else if (warp == 1) {
-    // ===== MMA issuer (one thread) =====
-    if (lane == 0 && ntiles > 0) {
+    // ===== MMA issuer (one thread of the leader CTA) =====
+    if (lane == 0 && ntiles > 0 && leader) {
       mbar_wait(a_full, 0);
       tc_fence_after();
       const uint32_t a_addr = smem_u32(sA);
@@ -253,12 +280,13 @@ sim_topk_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant
 #pragma unroll
           for (int k = 0; k < SIM_BLOCK_K / 16; ++k) {
             // +32 bytes per K=16 step inside the 128-byte swizzle row: +2 in the >>4 address field
-            umma_bf16(tacc, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), IDESC, (uint32_t)((c | k) != 0));
+            if (CG == 2) umma_bf16_2sm(tacc, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), IDESC, (uint32_t)((c | k) != 0));
+            else umma_bf16(tacc, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), IDESC, (uint32_t)((c | k) != 0));
           }
-          umma_commit(&empty[s]);  // stage reusable once these MMAs have read it
+          if (CG == 2) umma_commit_2sm(&empty[s]); else umma_commit(&empty[s]);   // stage reusable once read
           if (++s == p.nstage) { s = 0; ph ^= 1; }
         }
-        umma_commit(&acc_full[as]);  // accumulator tile complete
+        if (CG == 2) umma_commit_2sm(&acc_full[as]); else umma_commit(&acc_full[as]);   // accumulator tile complete
       }
     }
   } else if (warp >= 4) {
@@ -326,25 +354,43 @@ sim_topk_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant
           } else {
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(&acc_empty[as]);
+            if (lane == 0) {
+              if (CG == 2) mbar_arrive_leader(&acc_empty[as]); else mbar_arrive(&acc_empty[as]);
+            }
           }
-          float m = __uint_as_float(v[u][0]);
+          // maxima of the chunk's four 8-column groups (independent chains: the one drain warp of an
+          // SM sub-partition has nobody to hide a 31-deep FMNMX chain behind); the insert path below
+          // only walks the groups that actually hold a candidate
+          float g[4];
 #pragma unroll
-          for (int j = 1; j < 32; ++j) m = fmaxf(m, __uint_as_float(v[u][j]));
+          for (int q4 = 0; q4 < 4; ++q4) {
+            const float a0 = fmaxf(__uint_as_float(v[u][q4 * 8 + 0]), __uint_as_float(v[u][q4 * 8 + 1]));
+            const float a1 = fmaxf(__uint_as_float(v[u][q4 * 8 + 2]), __uint_as_float(v[u][q4 * 8 + 3]));
+            const float a2 = fmaxf(__uint_as_float(v[u][q4 * 8 + 4]), __uint_as_float(v[u][q4 * 8 + 5]));
+            const float a3 = fmaxf(__uint_as_float(v[u][q4 * 8 + 6]), __uint_as_float(v[u][q4 * 8 + 7]));
+            g[q4] = fmaxf(fmaxf(a0, a1), fmaxf(a2, a3));
+          }
+          const float m = fmaxf(fmaxf(g[0], g[1]), fmaxf(g[2], g[3]));
           if (m > thr) {
             const uint32_t base = col0 + c * 32;
 #pragma unroll
-            for (int j = 0; j < 32; ++j) {
-              const float s = __uint_as_float(v[u][j]);
-              if (s > thr && base + j < p.n_rows) {
-                const uint64_t r = topk_replace_worst<KP>(my_keys, wpos, s, base + j);
-                thr_own = __uint_as_float((uint32_t)(r >> 32));
-                wpos = (int)(uint32_t)r;
-                thr = fmaxf(thr, thr_own);
-                if (p.use_gthr && thr_own > -INFINITY) atomicMax(p.gthr + qg, f32_orderable(thr_own));   // set is full
-                if (s > best_own) {
-                  best_own = s;
-                  if (bound_on) atomicMax(my_bkt + (split % KP), f32_orderable(s));
+            for (int q4 = 0; q4 < 4; ++q4) {
+              if (g[q4] > thr) {
+#pragma unroll
+                for (int jj = 0; jj < 8; ++jj) {
+                  const int j = q4 * 8 + jj;
+                  const float s = __uint_as_float(v[u][j]);
+                  if (s > thr && base + j < p.n_rows) {
+                    const uint64_t r = topk_replace_worst<KP>(my_keys, wpos, s, base + j);
+                    thr_own = __uint_as_float((uint32_t)(r >> 32));
+                    wpos = (int)(uint32_t)r;
+                    thr = fmaxf(thr, thr_own);
+                    if (p.use_gthr && thr_own > -INFINITY) atomicMax(p.gthr + qg, f32_orderable(thr_own));   // set is full
+                    if (s > best_own) {
+                      best_own = s;
+                      if (bound_on) atomicMax(my_bkt + (split % KP), f32_orderable(s));
+                    }
+                  }
                 }
               }
             }
@@ -361,10 +407,12 @@ sim_topk_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant
   }
 
   tc_fence_before();
-  __syncthreads();
+  if (CG == 2) cluster_sync_all();   // no CTA leaves while its peer may still signal its barriers
+  else __syncthreads();
   if (warp == 2) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, TMEM_COLS);
+    if (CG == 2) tmem_dealloc_2sm(tmem_base, TMEM_COLS);
+    else tmem_dealloc(tmem_base, TMEM_COLS);
   }
 }
 
