@@ -36,10 +36,54 @@ struct AttParams {
   __nv_bfloat16* ctx;
 };
 
+#ifdef B200_ATT_TIMING
+// Development aid (not compiled into the shipped library): per-phase clock totals of the softmax
+// warps, accumulated by one lane per CTA.  [0] wait for scores, [1] pass 1, [2] pass 2, [3] wait for
+// output, [4] output, [5] units.
+__device__ unsigned long long g_att_timing[8];
+#define ATT_STAMP(var) const long long var = clock64()
+#define ATT_ACC(i, a, b) do { if (wq == 0 && lane == 0) atomicAdd(&g_att_timing[i], (unsigned long long)((b) - (a))); } while (0)
+#else
+#define ATT_STAMP(var)
+#define ATT_ACC(i, a, b)
+#endif
+
 B200_DEVINL float att_exp2(float x) {
   float y;
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
+}
+
+// Probabilities of one 32-key chunk of a row: p = 2^(s*scale - ms) for the first `valid` keys, 0 for
+// the rest (padding); accumulates the row sum and packs bf16 pairs.
+B200_DEVINL void att_probs(const uint32_t (&v)[32], int valid, float scale_log2, float ms, float& sum0, float& sum1,
+                           uint32_t (&pk)[16]) {
+  if (valid >= 32) {
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+      const float p0 = att_exp2(fmaf(__uint_as_float(v[2 * j]), scale_log2, -ms));
+      const float p1 = att_exp2(fmaf(__uint_as_float(v[2 * j + 1]), scale_log2, -ms));
+      sum0 += p0;
+      sum1 += p1;
+      __nv_bfloat162 t = __floats2bfloat162_rn(p0, p1);
+      pk[j] = *reinterpret_cast<uint32_t*>(&t);
+    }
+  } else if (valid > 0) {
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+      float p0 = att_exp2(fmaf(__uint_as_float(v[2 * j]), scale_log2, -ms));
+      float p1 = att_exp2(fmaf(__uint_as_float(v[2 * j + 1]), scale_log2, -ms));
+      if (2 * j >= valid) p0 = 0.f;
+      if (2 * j + 1 >= valid) p1 = 0.f;
+      sum0 += p0;
+      sum1 += p1;
+      __nv_bfloat162 t = __floats2bfloat162_rn(p0, p1);
+      pk[j] = *reinterpret_cast<uint32_t*>(&t);
+    }
+  } else {
+#pragma unroll
+    for (int j = 0; j < 16; ++j) pk[j] = 0u;
+  }
 }
 
 __global__ void __launch_bounds__(ATT_THREADS, 2)
@@ -51,10 +95,11 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_cons
   uint64_t* full = bars;            // [2] TMA -> MMA: Q, K, V of a unit landed
   uint64_t* kv_empty = bars + 2;    // [2] MMA -> TMA: the unit's MMAs have read the stage
   uint64_t* s_full = bars + 4;      // MMA -> softmax: scores ready
-  uint64_t* p_ready = bars + 5;     // softmax -> MMA: probabilities written to TMEM
-  uint64_t* o_full = bars + 6;      // MMA -> softmax: output tile ready
-  uint64_t* t_free = bars + 7;      // softmax -> MMA: TMEM reusable
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 8);
+  uint64_t* o_full = bars + 5;      // MMA -> softmax: output tile ready
+  uint64_t* t_free = bars + 6;      // softmax -> MMA: TMEM reusable
+  uint64_t* p_ready = bars + 8;     // [4] softmax -> MMA: probabilities of one 64-key group written to TMEM
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 12);
+  int4* meta = reinterpret_cast<int4*>(bars + 14);   // [2] per stage: {token row base, head, query tile, length}
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int S = p.S;
@@ -70,7 +115,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_cons
       mbar_init(&kv_empty[i], 1);
     }
     mbar_init(s_full, 1);
-    mbar_init(p_ready, 4);    // one arrival per softmax warp
+    for (int i = 0; i < 4; ++i) mbar_init(&p_ready[i], 4);    // one arrival per softmax warp
     mbar_init(o_full, 1);
     mbar_init(t_free, 4);
     fence_mbar_init();
@@ -89,8 +134,10 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_cons
       for (int u = blockIdx.x; u < p.n_units; u += gridDim.x, ++it) {
         const int st = it & 1, item = u / p.n_mt, mt = u - item * p.n_mt;
         const int b = item / p.heads, h = item - b * p.heads;
+        const int len = p.lens[b];
         mbar_wait(&kv_empty[st], ((it >> 1) & 1) ^ 1);
         uint8_t* base = smem + st * ATT_STAGE_BYTES;
+        meta[st] = make_int4(b * S, h, mt, max(1, min(len, S)));   // published by the arrive below
         mbar_arrive_expect_tx(&full[st], q_bytes + 2 * kv_bytes);
         tma_load_2d(base, &map_q, &full[st], h * ATT_DH, b * S + mt * 128);                                  // Q tile
         tma_load_2d(base + ATT_Q_BYTES, &map_kv, &full[st], p.H + h * ATT_DH, b * S);                        // K
@@ -102,8 +149,9 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_cons
     if (lane == 0) {
       const uint32_t idesc_s = umma_idesc_bf16_f32(128, (uint32_t)S);        // scores: N = S keys
       const uint32_t idesc_o = umma_idesc_bf16_f32_bmn(128, ATT_DH);         // output: N = 32 dims, V MN-major
-      const uint32_t tS = tmem_base;                 // scores fp32 [0, S); later P bf16 pairs [0, S/2)
-      const uint32_t tO = tmem_base + 128;           // output fp32, 32 columns
+      const uint32_t tS = tmem_base;                 // scores fp32, columns [0, S)
+      const uint32_t tO = tmem_base;                 // output fp32, columns [0, 32) once scores chunk 0 is consumed
+      const uint32_t tP = tmem_base + 32;            // probabilities, bf16 pairs: 8 columns per 16-key step
       uint32_t it = 0;
       for (int u = blockIdx.x; u < p.n_units; u += gridDim.x, ++it) {
         const int st = it & 1;
@@ -119,13 +167,18 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_cons
           umma_bf16(tS, dq, dk, idesc_s, (uint32_t)(k != 0));
         }
         umma_commit(s_full);
-        mbar_wait(p_ready, it & 1);
-        tc_fence_after();
+        // P V in groups of 64 keys, each issued as soon as the softmax warps have written that group's
+        // probabilities, so that only the last group's MMAs remain when the softmax pass ends
         const int ksteps = S / 16;
-        for (int k = 0; k < ksteps; ++k) {
-          // V as an MN-major B operand: 16 keys per step = 16 rows of 64 bytes = 1024 bytes
-          const uint64_t dv = umma_smem_desc(sbase + ATT_Q_BYTES + ATT_KV_BYTES + k * 1024, 4, 512, 16384);
-          umma_bf16_ts(tO, tS + k * 8, dv, idesc_o, (uint32_t)(k != 0));
+        for (int g = 0; g * 4 < ksteps; ++g) {
+          mbar_wait(&p_ready[g], it & 1);
+          tc_fence_after();
+          const int k1 = min(ksteps, g * 4 + 4);
+          for (int k = g * 4; k < k1; ++k) {
+            // V as an MN-major B operand: 16 keys per step = 16 rows of 64 bytes = 1024 bytes
+            const uint64_t dv = umma_smem_desc(sbase + ATT_Q_BYTES + ATT_KV_BYTES + k * 1024, 4, 512, 16384);
+            umma_bf16_ts(tO, tP + k * 8, dv, idesc_o, (uint32_t)(k != 0));
+          }
         }
         umma_commit(o_full);
         umma_commit(&kv_empty[st]);   // the stage is free once every MMA issued so far has finished
@@ -138,16 +191,17 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_cons
     const float scale_log2 = rsqrtf((float)ATT_DH) * 1.4426950408889634f;
     const int nch = S / 32;
     uint32_t it = 0;
-    int len_next = 1;
-    if ((int)blockIdx.x < p.n_units) len_next = p.lens[(blockIdx.x / p.n_mt) / p.heads];
     for (int u = blockIdx.x; u < p.n_units; u += gridDim.x, ++it) {
-      const int item = u / p.n_mt, mt = u - item * p.n_mt;
-      const int b = item / p.heads, h = item - b * p.heads;
-      const int row = mt * 128 + wq * 32 + lane;               // query position in the sequence
-      const int len = max(1, min(len_next, S));
-      if (u + (int)gridDim.x < p.n_units) len_next = p.lens[((u + gridDim.x) / p.n_mt) / p.heads];   // hide the load
+      const int st = it & 1;
+      ATT_STAMP(t0);
+      mbar_wait(&full[st], (it >> 1) & 1);                     // the producer's unit record is visible
+      const int4 um = meta[st];
+      const int row = um.z * 128 + wq * 32 + lane;             // query position in the sequence
+      const int len = um.w;
+      __nv_bfloat16* dst = p.ctx + ((size_t)um.x + row) * p.H + um.y * ATT_DH;
       mbar_wait(s_full, it & 1);
       tc_fence_after();
+      ATT_STAMP(t1);
       // Both passes walk the row in 32-column chunks with the tcgen05.ld of chunk c+1 in flight while
       // chunk c is processed (two register buffers); keys >= len only ever sit in the last chunks.
       const int nfull = len >> 5;                      // chunks made of valid keys only
@@ -188,70 +242,47 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_cons
         tmem_ld_wait();                                // drain a load that may still be in flight
       }
       const float ms = mx * scale_log2;
-      // pass 2: probabilities (bf16, packed) written back over the scores; row sum in fp32
+      ATT_STAMP(t2);
+      // pass 2: probabilities (bf16, packed two per column) and the fp32 row sum.  TMEM layout from
+      // here on: output accumulator in columns [0, 32) (scores chunk 0, consumed first), probabilities
+      // of chunk c in columns [32 + 16c, 48 + 16c) -- always below the scores still unread, except for
+      // chunk 0, whose store therefore waits until chunk 1 has been drained into registers.
       float sum0 = 0.f, sum1 = 0.f;
+      const uint32_t tP = tS + 32;
       tmem_ld32(tS, v[0]);
 #pragma unroll 1
-      for (int c2 = 0; c2 < nfull; c2 += 2) {
-#pragma unroll
-        for (int u = 0; u < 2; ++u) {
-          const int c = c2 + u;
-          if (c < nfull) {
-            tmem_ld_wait_dep(v[u]);
-            if (c + 1 < nch) tmem_ld32(tS + (c + 1) * 32, v[u ^ 1]);
-            uint32_t pk[16];
-#pragma unroll
-            for (int j = 0; j < 16; ++j) {
-              const float p0 = att_exp2(fmaf(__uint_as_float(v[u][2 * j]), scale_log2, -ms));
-              const float p1 = att_exp2(fmaf(__uint_as_float(v[u][2 * j + 1]), scale_log2, -ms));
-              sum0 += p0;
-              sum1 += p1;
-              __nv_bfloat162 t = __floats2bfloat162_rn(p0, p1);
-              pk[j] = *reinterpret_cast<uint32_t*>(&t);
-            }
-            tmem_st16(tS + c * 16, pk);
-          }
-        }
-      }
-      for (int c = nfull; c < nch; ++c) {              // boundary chunk (masked), then all-padding chunks (zeros)
-        uint32_t pk[16];
-        if (c == nfull && rem) {
-          uint32_t w[32];
-          tmem_ld32(tS + c * 32, w);                   // (re-)load: keeps this rare path simple
-          tmem_ld_wait();
-#pragma unroll
-          for (int j = 0; j < 16; ++j) {
-            float p0 = att_exp2(fmaf(__uint_as_float(w[2 * j]), scale_log2, -ms));
-            float p1 = att_exp2(fmaf(__uint_as_float(w[2 * j + 1]), scale_log2, -ms));
-            if (2 * j >= rem) p0 = 0.f;
-            if (2 * j + 1 >= rem) p1 = 0.f;
-            sum0 += p0;
-            sum1 += p1;
-            __nv_bfloat162 t = __floats2bfloat162_rn(p0, p1);
-            pk[j] = *reinterpret_cast<uint32_t*>(&t);
-          }
+      for (int c = 0, g = 0; c < nch; c += 2, ++g) {
+        uint32_t pk0[16], pk1[16];
+        tmem_ld_wait_dep(v[0]);
+        if (c + 1 < nch) tmem_ld32(tS + (c + 1) * 32, v[1]);
+        att_probs(v[0], len - c * 32, scale_log2, ms, sum0, sum1, pk0);
+        if (c + 1 < nch) {
+          tmem_ld_wait_dep(v[1]);
+          tmem_st16(tP + c * 16, pk0);
+          if (c + 2 < nch) tmem_ld32(tS + (c + 2) * 32, v[0]);
+          att_probs(v[1], len - (c + 1) * 32, scale_log2, ms, sum0, sum1, pk1);
+          tmem_st16(tP + (c + 1) * 16, pk1);
         } else {
-#pragma unroll
-          for (int j = 0; j < 16; ++j) pk[j] = 0u;
+          tmem_st16(tP + c * 16, pk0);
         }
-        tmem_st16(tS + c * 16, pk);
+        tmem_st_wait();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&p_ready[g]);     // this 64-key group may enter the P V product
       }
-      tmem_st_wait();
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(p_ready);
       // output tile: O / sum -> bf16 -> ctx[b, row, h*32 .. +32]
+      ATT_STAMP(t3);
       mbar_wait(o_full, it & 1);
       tc_fence_after();
+      ATT_STAMP(t4);
       uint32_t o[32];
-      tmem_ld32(tS + 128, o);
+      tmem_ld32(tS, o);
       tmem_ld_wait();
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(t_free);
       if (row < S) {
         const float inv = 1.0f / (sum0 + sum1);
-        __nv_bfloat16* dst = p.ctx + ((size_t)b * S + row) * p.H + h * ATT_DH;
 #pragma unroll
         for (int g = 0; g < 4; ++g) {
           uint4 w;
@@ -264,6 +295,10 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_cons
           *reinterpret_cast<uint4*>(dst + g * 8) = w;
         }
       }
+#ifdef B200_ATT_TIMING
+      ATT_STAMP(t5);
+      ATT_ACC(0, t0, t1); ATT_ACC(1, t1, t2); ATT_ACC(2, t2, t3); ATT_ACC(3, t3, t4); ATT_ACC(4, t4, t5); ATT_ACC(5, 0, 1);
+#endif
     }
   }
 

@@ -223,7 +223,7 @@ static int run_encoder(b200_encoder* e, const int32_t* d_ids, const int32_t* d_l
       ap.S = seq; ap.H = H; ap.heads = heads; ap.n_mt = (seq + 127) / 128; ap.n_units = batch * heads * ap.n_mt;
       ap.lens = d_lens; ap.ctx = e->ctx.as<__nv_bfloat16>();
       B200_PROF("attention", 4.0 * batch * (double)seq * seq * H, 2.0 * 4.0 * n_tok * H, st);
-      attention_tc_kernel<<<std::min(ap.n_units, 2 * e->num_sms), ATT_THREADS, att_tc_smem, st>>>(map_att_q, map_att_kv, ap);
+      attention_tc_kernel<<<std::min(ap.n_units, (getenv("B200_ATT_CTAS") ? atoi(getenv("B200_ATT_CTAS")) : 2) * e->num_sms), ATT_THREADS, att_tc_smem, st>>>(map_att_q, map_att_kv, ap);
     } else {
       B200_PROF("attention", 4.0 * batch * (double)seq * seq * H, 2.0 * 4.0 * n_tok * H, st);
       if (dh == 32)
@@ -424,3 +424,13 @@ int b200_encoder_peek(b200_encoder_t* e, int which, float* out_host, int64_t num
 }
 
 }  // extern "C"
+
+#ifdef B200_ATT_TIMING
+extern "C" int b200_debug_att_timing(unsigned long long* out) {
+  cudaDeviceSynchronize();
+  cudaMemcpyFromSymbol(out, b200::g_att_timing, 8 * sizeof(unsigned long long));
+  unsigned long long z[8] = {0};
+  cudaMemcpyToSymbol(b200::g_att_timing, z, sizeof(z));
+  return 0;
+}
+#endif

@@ -15,3 +15,18 @@ for _ in range(3):
     out = prov.embed_tokens(ids, lens)
 torch.cuda.synchronize()
 print("ok", float(out.abs().sum()))
+# per-phase clocks of the attention softmax warps (library built with EXTRA=-DB200_ATT_TIMING)
+import ctypes
+nat = importlib.import_module(P + "._native")
+L = nat.lib()
+if hasattr(L, "b200_debug_att_timing"):
+    buf = (ctypes.c_ulonglong * 8)()
+    L.b200_debug_att_timing(buf)
+    out = prov.embed_tokens(ids, lens)
+    L.b200_debug_att_timing(buf)
+    n = max(1, buf[5])
+    names = ["wait_S", "pass1", "pass2", "wait_O", "output"]
+    tot = sum(buf[i] for i in range(5))
+    print("units(per sampling lane)", buf[5], "clk/unit", tot / n)
+    for i, nm in enumerate(names):
+        print(f"  {nm:8s} {buf[i]/n:9.1f} clk  {100.0*buf[i]/tot:5.1f}%")
