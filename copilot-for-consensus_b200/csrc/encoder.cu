@@ -204,9 +204,12 @@ static int run_encoder(b200_encoder* e, const int32_t* d_ids, const int32_t* d_l
   // other shapes use the mma.sync one.  B200_ATTENTION=legacy forces the latter (A/B timing).
   const char* att_env = getenv("B200_ATTENTION");
   const bool use_att_tc = dh == ATT_DH && seq <= ATT_MAX_S && seq % 32 == 0 && !(att_env && strcmp(att_env, "legacy") == 0);
-  const size_t att_tc_smem = 1024 + 2 * (size_t)ATT_STAGE_BYTES + 256;   // alignment slack, two stages, barriers
-  CUtensorMap map_att_q, map_att_kv;
+  const size_t att_tc_smem = ATT_SMEM_BYTES;   // alignment slack, two stages, barriers + exchange buffers
+  CUtensorMap map_att_q, map_att_kv, map_att_out, map_att_out_tail;
   if (use_att_tc) {
+    const int n_mt = (seq + 127) / 128;
+    B200_TRY(make_tma_2d_bf16_sw64(&map_att_out, e->ctx.p, (uint64_t)e->m_cap, (uint64_t)H, (uint32_t)std::min(seq, 128), ATT_DH));
+    B200_TRY(make_tma_2d_bf16_sw64(&map_att_out_tail, e->ctx.p, (uint64_t)e->m_cap, (uint64_t)H, (uint32_t)(seq - (n_mt - 1) * 128), ATT_DH));
     B200_TRY(make_tma_2d_bf16_sw64(&map_att_q, e->qkv.p, (uint64_t)e->m_cap, (uint64_t)(3 * H), (uint32_t)std::min(seq, 128), ATT_DH));
     B200_TRY(make_tma_2d_bf16_sw64(&map_att_kv, e->qkv.p, (uint64_t)e->m_cap, (uint64_t)(3 * H), (uint32_t)seq, ATT_DH));
     B200_CUDA(cudaFuncSetAttribute(attention_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)att_tc_smem));
@@ -223,7 +226,7 @@ static int run_encoder(b200_encoder* e, const int32_t* d_ids, const int32_t* d_l
       ap.S = seq; ap.H = H; ap.heads = heads; ap.n_mt = (seq + 127) / 128; ap.n_units = batch * heads * ap.n_mt;
       ap.lens = d_lens; ap.ctx = e->ctx.as<__nv_bfloat16>();
       B200_PROF("attention", 4.0 * batch * (double)seq * seq * H, 2.0 * 4.0 * n_tok * H, st);
-      attention_tc_kernel<<<std::min(ap.n_units, (getenv("B200_ATT_CTAS") ? atoi(getenv("B200_ATT_CTAS")) : 2) * e->num_sms), ATT_THREADS, att_tc_smem, st>>>(map_att_q, map_att_kv, ap);
+      attention_tc_kernel<<<std::min(ap.n_units, e->num_sms), ATT_THREADS, att_tc_smem, st>>>(map_att_q, map_att_kv, map_att_out, map_att_out_tail, ap);
     } else {
       B200_PROF("attention", 4.0 * batch * (double)seq * seq * H, 2.0 * 4.0 * n_tok * H, st);
       if (dh == 32)
@@ -428,8 +431,8 @@ int b200_encoder_peek(b200_encoder_t* e, int which, float* out_host, int64_t num
 #ifdef B200_ATT_TIMING
 extern "C" int b200_debug_att_timing(unsigned long long* out) {
   cudaDeviceSynchronize();
-  cudaMemcpyFromSymbol(out, b200::g_att_timing, 8 * sizeof(unsigned long long));
-  unsigned long long z[8] = {0};
+  cudaMemcpyFromSymbol(out, b200::g_att_timing, 16 * sizeof(unsigned long long));
+  unsigned long long z[16] = {0};
   cudaMemcpyToSymbol(b200::g_att_timing, z, sizeof(z));
   return 0;
 }
