@@ -205,11 +205,11 @@ static int run_encoder(b200_encoder* e, const int32_t* d_ids, const int32_t* d_l
   const char* att_env = getenv("B200_ATTENTION");
   const bool use_att_tc = dh == ATT_DH && seq <= ATT_MAX_S && seq % 32 == 0 && !(att_env && strcmp(att_env, "legacy") == 0);
   const size_t att_tc_smem = ATT_SMEM_BYTES;   // alignment slack, two stages, barriers + exchange buffers
-  CUtensorMap map_att_q, map_att_kv, map_att_out, map_att_out_tail;
+  const char* att_exact_env = getenv("B200_ATT_EXACT_MAX");
+  const int att_exact_max = att_exact_env && atoi(att_exact_env) != 0;
+  CUtensorMap map_att_q, map_att_kv, map_att_out;
   if (use_att_tc) {
-    const int n_mt = (seq + 127) / 128;
-    B200_TRY(make_tma_2d_bf16_sw64(&map_att_out, e->ctx.p, (uint64_t)e->m_cap, (uint64_t)H, (uint32_t)std::min(seq, 128), ATT_DH));
-    B200_TRY(make_tma_2d_bf16_sw64(&map_att_out_tail, e->ctx.p, (uint64_t)e->m_cap, (uint64_t)H, (uint32_t)(seq - (n_mt - 1) * 128), ATT_DH));
+    B200_TRY(make_tma_2d_bf16_plain(&map_att_out, e->ctx.p, (uint64_t)e->m_cap, (uint64_t)H, 32, ATT_DH / 2));   // one warp's rows x dims
     B200_TRY(make_tma_2d_bf16_sw64(&map_att_q, e->qkv.p, (uint64_t)e->m_cap, (uint64_t)(3 * H), (uint32_t)std::min(seq, 128), ATT_DH));
     B200_TRY(make_tma_2d_bf16_sw64(&map_att_kv, e->qkv.p, (uint64_t)e->m_cap, (uint64_t)(3 * H), (uint32_t)seq, ATT_DH));
     B200_CUDA(cudaFuncSetAttribute(attention_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)att_tc_smem));
@@ -224,9 +224,10 @@ static int run_encoder(b200_encoder* e, const int32_t* d_ids, const int32_t* d_l
     if (use_att_tc) {
       AttParams ap;
       ap.S = seq; ap.H = H; ap.heads = heads; ap.n_mt = (seq + 127) / 128; ap.n_units = batch * heads * ap.n_mt;
-      ap.lens = d_lens; ap.ctx = e->ctx.as<__nv_bfloat16>();
+      ap.lens = d_lens; ap.exact_max = att_exact_max;
+      ap.no_turns = getenv("B200_ATT_NO_TURNS") && atoi(getenv("B200_ATT_NO_TURNS")) != 0;
       B200_PROF("attention", 4.0 * batch * (double)seq * seq * H, 2.0 * 4.0 * n_tok * H, st);
-      attention_tc_kernel<<<std::min(ap.n_units, e->num_sms), ATT_THREADS, att_tc_smem, st>>>(map_att_q, map_att_kv, map_att_out, map_att_out_tail, ap);
+      attention_tc_kernel<<<std::min(ap.n_units, e->num_sms), ATT_THREADS, att_tc_smem, st>>>(map_att_q, map_att_kv, map_att_out, ap);
     } else {
       B200_PROF("attention", 4.0 * batch * (double)seq * seq * H, 2.0 * 4.0 * n_tok * H, st);
       if (dh == 32)
@@ -329,6 +330,13 @@ int b200_encoder_finalize(b200_encoder_t* e) {
       memcpy(wqkv.data() + (size_t)j * H * H, t->data(), H * H * 4);
       B200_TRY(take(e, p + "attention.self." + names[j] + ".bias", H, &t));
       memcpy(bqkv.data() + (size_t)j * H, t->data(), H * 4);
+    }
+    // The attention kernels take 2^x of their scores: fold log2(e) / sqrt(head dim) into the query
+    // projection here, in fp32 before the bf16 rounding, so that Q K^T needs no per-score multiply.
+    {
+      const float c = 1.4426950408889634f / sqrtf((float)(H / e->cfg.heads));
+      for (size_t i = 0; i < (size_t)H * H; ++i) wqkv[i] *= c;
+      for (size_t i = 0; i < (size_t)H; ++i) bqkv[i] *= c;
     }
     B200_TRY(upload_bf16(L->wqkv, wqkv.data(), wqkv.size()));
     B200_TRY(upload_f32(L->bqkv, bqkv.data(), bqkv.size()));

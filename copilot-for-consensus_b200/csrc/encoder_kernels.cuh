@@ -435,7 +435,7 @@ attention_kernel(const __nv_bfloat16* __restrict__ qkv, const int32_t* __restric
   }
   __syncthreads();
 
-  const float scale_log2 = rsqrtf((float)DH) * 1.4426950408889634f;
+  const float scale_log2 = 1.0f;   // log2(e) / sqrt(DH) is folded into the query projection (encoder.cu)
   const int r = lane >> 2, cq = (lane & 3) * 2;
   const int lm = lane >> 3, lr = lane & 7;   // ldmatrix: this lane addresses row lr of matrix lm
 

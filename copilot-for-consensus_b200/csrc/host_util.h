@@ -102,6 +102,10 @@ int make_tma_2d_bf16(CUtensorMap* out, const void* base, uint64_t rows, uint64_t
 int make_tma_2d_bf16_sw64(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint32_t box_rows,
                           uint32_t box_cols);
 
+// Unswizzled box (rows of box_cols bf16, a multiple of 16 bytes), e.g. a warp's slice of an output tile.
+int make_tma_2d_bf16_plain(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint32_t box_rows,
+                           uint32_t box_cols);
+
 int check_device_is_sm100(int device);
 
 // Optional per-kernel timing (off by default): when enabled through b200_profile_enable, each

@@ -82,6 +82,22 @@ int make_tma_2d_bf16_sw64(CUtensorMap* out, const void* base, uint64_t rows, uin
   return B200_OK;
 }
 
+int make_tma_2d_bf16_plain(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint32_t box_rows,
+                           uint32_t box_cols) {
+  EncodeTiledFn fn = encode_tiled_fn();
+  if (!fn) B200_FAIL(B200_ERR_CUDA, "cuTensorMapEncodeTiled is not available from the CUDA driver");
+  if ((box_cols * 2) % 16 != 0 || box_cols > 256 || box_rows > 256) B200_FAIL(B200_ERR_INVALID, "bad TMA box %u x %u", box_rows, box_cols);
+  cuuint64_t gdim[2] = {cols, rows};
+  cuuint64_t gstride[1] = {cols * 2};
+  cuuint32_t box[2] = {box_cols, box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), gdim, gstride, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) B200_FAIL(B200_ERR_CUDA, "cuTensorMapEncodeTiled (no swizzle) failed with CUresult %d", (int)r);
+  return B200_OK;
+}
+
 int check_device_is_sm100(int device) {
   int n = 0;
   if (cudaGetDeviceCount(&n) != cudaSuccess || n == 0) {

@@ -24,14 +24,11 @@ if hasattr(L, "b200_debug_att_timing"):
     L.b200_debug_att_timing(buf)
     out = prov.embed_tokens(ids, lens)
     L.b200_debug_att_timing(buf)
-    n = max(1, buf[5])
-    names = ["wait_S", "pass1", "pass2", "wait_O", "output", None, "wait_turn"]
-    tot = sum(buf[i] for i in range(7) if i != 5)
-    print("units(per sampling lane)", buf[5], "clk/unit", tot / n)
+    n = max(1, buf[7])
+    names = ["reference(next)", "wait scores", "exact max", "wait turn", "exp pass", "wait output", "output"]
+    tot = sum(buf[i] for i in range(7))
+    print("units(per sampling lane)", buf[7], "clk/unit", tot / n)
     for i, nm in enumerate(names):
-        if nm is None:
-            continue
-        print(f"  {nm:8s} {buf[i]/n:9.1f} clk  {100.0*buf[i]/tot:5.1f}%")
-    print("  pass 2 per unit: ld-wait %.1f  probs+st issue %.1f  tail (st wait, arrive) %.1f" % (buf[8]/n, buf[9]/n, buf[10]/n))
-    print("  output: O ld %.1f  pair barrier %.1f ; MMA warp PV issue %.1f" % (buf[11]/n, buf[12]/n, buf[13]/n))
-    print("  output: reciprocal %.1f" % (buf[14]/n))
+        print(f"  {nm:16s} {buf[i]/n:9.1f} clk  {100.0*buf[i]/tot:5.1f}%")
+    print("  MMA warp: P V issue %.1f clk per unit" % (buf[13] / max(1, 2 * n)))
+    print("  exp pass per warp of group 0:", " ".join("%.0f" % (buf[8 + w] / n) for w in range(8)))

@@ -132,6 +132,46 @@ __global__ void kt(float* out, const float* in, int iters, long long* clk) {
   if (warp == 0) tmem_dealloc(slot, 512);
 }
 
+// mode 6: tcgen05.ld only (two x32 loads in flight, maxima taken so the data is used)
+__global__ void kl(float* out, int iters, long long* clk) {
+  __shared__ uint32_t slot;
+  const int warp = threadIdx.x >> 5;
+  if (warp == 0) tmem_alloc(&slot, 512);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tb = slot + ((uint32_t)((warp & 3) * 32) << 16) + (warp >> 2) * 64;
+  uint32_t v[2][32];
+  float m = 0.f;
+  __syncthreads();
+  const long long t0 = clock64();
+#pragma unroll 1
+  for (int it = 0; it < iters; it += 2) {
+    tmem_ld32(tb, v[0]);
+    tmem_ld32(tb + 32, v[1]);
+    tmem_ld_wait_dep(v[0]);
+    tmem_ld_wait_dep(v[1]);
+    m = fmaxf(m, fmaxf(__uint_as_float(v[0][it & 31]), __uint_as_float(v[1][it & 31])));
+  }
+  const long long t1 = clock64();
+  out[blockIdx.x * blockDim.x + threadIdx.x] = m;
+  if (threadIdx.x == 0 && blockIdx.x == 0) *clk = t1 - t0;
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(slot, 512);
+}
+void runl(int warps_per_smsp, float* out, long long* clk) {
+  const int iters = 2000;
+  for (int rep = 0; rep < 2; ++rep) {
+    kl<<<148, warps_per_smsp * 128>>>(out, iters, clk);
+    cudaDeviceSynchronize();
+  }
+  long long c;
+  cudaMemcpy(&c, clk, 8, cudaMemcpyDeviceToHost);
+  printf("mode 6  warps/SMSP %d : %.1f clk per 4 KB chunk per warp -> %.1f B/clk per SMSP\n", warps_per_smsp, (double)c / iters,
+         4096.0 * warps_per_smsp * iters / (double)c);
+}
+
 template <int MODE>
 void runt(int warps_per_smsp, float* out, float* in, long long* clk) {
   const int iters = 2000;
@@ -176,6 +216,7 @@ int main() {
     run<3>(w, out, in, clk);
     runt<4>(w, out, in, clk);
     runt<5>(w, out, in, clk);
+    runl(w, out, clk);
   }
   printf("%s\n", cudaGetErrorString(cudaGetLastError()));
   return 0;

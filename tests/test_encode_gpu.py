@@ -88,6 +88,38 @@ def test_device_tensors_and_determinism(minilm, minilm_weights):
     np.testing.assert_allclose(solo[0], a[3].cpu().numpy(), atol=2e-3)
 
 
+def _scale_qk(weights: dict, scale: float) -> dict:
+    out = dict(weights)
+    for k in weights:
+        if ".attention.self.query." in k or ".attention.self.key." in k:
+            out[k] = weights[k] * scale
+    return out
+
+
+@pytest.mark.parametrize("qk_scale,exact_env", [(8.0, "0"), (8.0, "1"), (60.0, "0")])
+def test_sharp_attention_both_softmax_reference_paths(monkeypatch, qk_scale, exact_env):
+    """Random-init weights give near-uniform attention; real checkpoints do not.  Scaling the query / key
+    projections makes the logits 64x (moderately peaked rows: the Cauchy-Schwarz reference path of
+    attention_tc.cuh) and 3600x (one-hot rows whose bound exceeds ATT_BOUND_GAP: the exact maximum
+    pass); B200_ATT_EXACT_MAX=1 forces the exact pass on the moderate case, so both paths are checked
+    on the same input against the fp32 oracle."""
+    from safetensors.torch import load_file, save_file
+
+    monkeypatch.setenv("B200_ATT_EXACT_MAX", exact_env)
+    mio, prov = pkg("embedding.model_io"), pkg("embedding.provider")
+    with tempfile.TemporaryDirectory() as td:
+        mio.write_random_model(td, "all-MiniLM-L6-v2", seed=5)
+        path = td + "/model.safetensors"
+        save_file({k: v.contiguous() for k, v in _scale_qk(load_file(path), qk_scale).items()}, path)
+        p = prov.B200SentenceTransformerProvider(model_name=td, device="cuda:0")
+    w = _scale_qk(eo.make_weights(eo.MINILM_L6, seed=5), qk_scale)
+    for B, S in [(6, 256), (5, 96)]:
+        ids, mask, lens = eo.synthetic_tokens(B, S, 30522, seed=S, ragged=True)
+        got = p.embed_tokens(ids.numpy(), lens.numpy())
+        _check(got, eo.encode(eo.MINILM_L6, w, ids, mask).numpy())
+    p.close()
+
+
 def test_embed_contract(minilm):
     """sentence_transformer_provider.py:88-91 and the attributes its tests assert."""
     with pytest.raises(ValueError, match="Text cannot be None"):
