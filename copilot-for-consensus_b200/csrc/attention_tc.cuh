@@ -126,6 +126,9 @@ constexpr float ATT_NORM_SLACK = 1.04f;           // on |q| |k|: covers two sums
 // the row's leading keys is a normal fp32 / bf16 number and the softmax is unchanged.  Units over the
 // limit (decided per unit, uniformly for the group) take the exact maximum pass instead.
 constexpr float ATT_BOUND_GAP = 96.f;
+#ifndef ATT_HANDOVER
+#define ATT_HANDOVER 2   // chunks of its exponential pass a warp still has to do when it hands the turn over (measured: 0 -> 5042, 1 -> 4830, 2 -> 4538, 3 -> 4932, 4 -> 5379 clocks per pair of units)
+#endif
 
 // Maximum of one 32-key chunk of a row; FULL = every key valid, else only the first `valid` keys
 // (-inf when there are none).
@@ -189,9 +192,12 @@ B200_DEVINL float att_pass_max(uint32_t tS, int ncl, int lenh, uint32_t (&v)[2][
 
 // Exponential pass of a warp: probabilities written back in place (16 columns per chunk from tS on);
 // the tcgen05.ld of chunk c+1 is in flight while chunk c is processed (two register buffers).
+// `turn` is handed to the other group when this warp STARTS its last chunk: the overlap of one chunk
+// keeps the SFU queue full across the hand-over (warps of a group do not finish together).
 template <bool FULL, bool SUB>
-B200_DEVINL void att_pass_exp(uint32_t tS, int ncl, int lenh, float mx, uint32_t (&v)[2][32]) {
+B200_DEVINL void att_pass_exp(uint32_t tS, int ncl, int lenh, float mx, uint32_t (&v)[2][32], uint64_t* turn, int lane) {
   if (ncl > 0) tmem_ld32(tS, v[0]);
+  else if (lane == 0) mbar_arrive(turn);
 #pragma unroll 1
   for (int c = 0; c < ncl; c += 2) {
 #pragma unroll
@@ -200,6 +206,7 @@ B200_DEVINL void att_pass_exp(uint32_t tS, int ncl, int lenh, float mx, uint32_t
       if (cc < ncl) {
         tmem_ld_wait_dep(v[uu]);
         if (cc + 1 < ncl) tmem_ld32(tS + (cc + 1) * 32, v[uu ^ 1]);
+        if (cc == max(ncl - ATT_HANDOVER, 0) && lane == 0) mbar_arrive(turn);
         uint32_t pk[16];
         att_probs<FULL, SUB>(v[uu], lenh - cc * 32, mx, pk);
         tmem_st16(tS + cc * 16, pk);
@@ -244,7 +251,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_cons
   float* kmax2 = reinterpret_cast<float*>(tail + 272);   // [4] per stage: max_j |k_j|^2
   float* xch = reinterpret_cast<float*>(tail + ATT_TAIL_HDR);
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = uniform_warp_idx(), lane = threadIdx.x & 31;
   const int S = p.S;
   const int q_rows = min(S, 128);
   const int nch = S / 32, c0 = (nch + 1) / 2;
@@ -289,8 +296,8 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_cons
   const uint32_t kv_bytes = (uint32_t)S * ATT_DH * 2, q_bytes = (uint32_t)q_rows * ATT_DH * 2;
 
   if (warp == W_TMA) {
-    // ===== TMA producer =====
-    if (lane == 0) {
+    // ===== TMA producer: the warp runs the loop converged, one elected lane issues (see uniform_warp_idx) =====
+    {
       uint32_t it = 0;
       for (int u = blockIdx.x; u < p.n_units; u += gridDim.x, ++it) {
         const int st = it % ATT_STAGES, item = u / p.n_mt, mt = u - item * p.n_mt;
@@ -298,16 +305,20 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_cons
         const int len = p.lens[b];
         mbar_wait(&kv_empty[st], ((it / ATT_STAGES) & 1) ^ 1);
         uint8_t* base = smem + st * ATT_STAGE_BYTES;
-        meta[st] = make_int4(b * S, h, mt, max(1, min(len, S)));   // published by the arrive below
-        mbar_arrive_expect_tx(&full[st], q_bytes + 2 * kv_bytes);
-        tma_load_2d(base, &map_q, &full[st], h * ATT_DH, b * S + mt * 128);                                  // Q tile
-        tma_load_2d(base + ATT_Q_BYTES, &map_kv, &full[st], p.H + h * ATT_DH, b * S);                        // K
-        tma_load_2d(base + ATT_Q_BYTES + ATT_KV_BYTES, &map_kv, &full[st], 2 * p.H + h * ATT_DH, b * S);     // V
+        if (elect_one()) {
+          meta[st] = make_int4(b * S, h, mt, max(1, min(len, S)));   // published by the arrive below
+          mbar_arrive_expect_tx(&full[st], q_bytes + 2 * kv_bytes);
+          tma_load_2d(base, &map_q, &full[st], h * ATT_DH, b * S + mt * 128);                                  // Q tile
+          tma_load_2d(base + ATT_Q_BYTES, &map_kv, &full[st], p.H + h * ATT_DH, b * S);                        // K
+          tma_load_2d(base + ATT_Q_BYTES + ATT_KV_BYTES, &map_kv, &full[st], 2 * p.H + h * ATT_DH, b * S);     // V
+        }
+        __syncwarp();
       }
     }
   } else if (warp == W_MMA) {
-    // ===== MMA issuer: scores of unit j, then P V of unit j-1 (the other group's) =====
-    if (lane == 0) {
+    // ===== MMA issuer: scores of unit j, then P V of unit j-1 (the other group's).  The warp runs the
+    // loop converged and one elected lane issues, which keeps the operands in uniform registers =====
+    {
       const uint32_t idesc_s = umma_idesc_bf16_f32(128, (uint32_t)S);        // scores: N = S keys
       const uint32_t idesc_o = umma_idesc_bf16_f32_bmn(128, ATT_ON);         // output: N = 32 dims + 16 ones, V MN-major
       const uint64_t dkx = umma_smem_desc(smem_u32(kx), 4, 512, 0);
@@ -325,14 +336,17 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_cons
         uint64_t dv = umma_smem_desc(vbase, 4, 512, smem_u32(vx) - vbase);
         uint32_t tp = tb;
         const int k_half = 2 * c0;
-        for (int k = 0; k < ksteps; ++k) {
-          if (k == k_half) tp = tb + 32 * c0;        // probabilities of key half 1 start at its own score columns
-          umma_bf16_ts(tb + o_col, tp, dv, idesc_o, (uint32_t)(k != 0));
-          dv += 64ull - (64ull << 16);               // start address + 1024 bytes, leading offset - 1024 bytes
-          tp += 8;
+        if (elect_one()) {
+          for (int k = 0; k < ksteps; ++k) {
+            if (k == k_half) tp = tb + 32 * c0;      // probabilities of key half 1 start at its own score columns
+            umma_bf16_ts(tb + o_col, tp, dv, idesc_o, (uint32_t)(k != 0));
+            dv += 64ull - (64ull << 16);             // start address + 1024 bytes, leading offset - 1024 bytes
+            tp += 8;
+          }
+          umma_commit(&o_full[g]);
+          umma_commit(&kv_empty[st]);   // the stage is free once every MMA issued so far has finished
         }
-        umma_commit(&o_full[g]);
-        umma_commit(&kv_empty[st]);   // the stage is free once every MMA issued so far has finished
+        __syncwarp();
       };
       uint32_t it = 0;
       for (int u = blockIdx.x; u < p.n_units; u += gridDim.x, ++it) {
@@ -344,14 +358,17 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_cons
         mbar_wait(&qx_ready[g], (it >> 1) & 1);      // -m_r of this unit's rows is in the group's A slice
         tc_fence_after();
         // Q (A) and K (B) are K-major: rows of 64 bytes, 8-row swizzle atoms of 512 bytes
+        if (elect_one()) {
 #pragma unroll
-        for (int k = 0; k < ATT_DH / 16; ++k) {
-          const uint64_t dq = umma_smem_desc(sbase + k * 32, 4, 512, 0);
-          const uint64_t dk = umma_smem_desc(sbase + ATT_Q_BYTES + k * 32, 4, 512, 0);
-          umma_bf16(tmem_base + g * 256, dq, dk, idesc_s, (uint32_t)(k != 0));
+          for (int k = 0; k < ATT_DH / 16; ++k) {
+            const uint64_t dq = umma_smem_desc(sbase + k * 32, 4, 512, 0);
+            const uint64_t dk = umma_smem_desc(sbase + ATT_Q_BYTES + k * 32, 4, 512, 0);
+            umma_bf16(tmem_base + g * 256, dq, dk, idesc_s, (uint32_t)(k != 0));
+          }
+          umma_bf16(tmem_base + g * 256, umma_smem_desc(smem_u32(qx + g * ATT_Q_BYTES), 4, 512, 0), dkx, idesc_s, 1u);
+          umma_commit(&s_full[g]);
         }
-        umma_bf16(tmem_base + g * 256, umma_smem_desc(smem_u32(qx + g * ATT_Q_BYTES), 4, 512, 0), dkx, idesc_s, 1u);
-        umma_commit(&s_full[g]);
+        __syncwarp();
         if (it > 0) issue_pv(it - 1, len_prev);
         len_prev = len;
       }
@@ -463,14 +480,12 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_cons
       if (!p.no_turns) mbar_wait(&xu_turn[grp], grp == 0 ? ((k & 1) ^ 1) : (k & 1));
       ATT_STAMP(t4);
       if (use_bound) {
-        if (all_valid) att_pass_exp<true, false>(tS, ncl, lenh, 0.f, v);
-        else att_pass_exp<false, false>(tS, ncl, lenh, 0.f, v);
+        if (all_valid) att_pass_exp<true, false>(tS, ncl, lenh, 0.f, v, &xu_turn[grp ^ 1], lane);
+        else att_pass_exp<false, false>(tS, ncl, lenh, 0.f, v, &xu_turn[grp ^ 1], lane);
       } else {
-        if (all_valid) att_pass_exp<true, true>(tS, ncl, lenh, mx, v);
-        else att_pass_exp<false, true>(tS, ncl, lenh, mx, v);
+        if (all_valid) att_pass_exp<true, true>(tS, ncl, lenh, mx, v, &xu_turn[grp ^ 1], lane);
+        else att_pass_exp<false, true>(tS, ncl, lenh, mx, v, &xu_turn[grp ^ 1], lane);
       }
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&xu_turn[grp ^ 1]);           // hand the exponential pass over
       tmem_st_wait();
       tc_fence_before();
       __syncwarp();

@@ -172,6 +172,12 @@ B200_DEVINL void tmem_ld16(uint32_t taddr, uint32_t (&r)[16]) {
 B200_DEVINL void tmem_ld1(uint32_t taddr, uint32_t& r) {
   asm volatile("tcgen05.ld.sync.aligned.32x32b.x1.b32 {%0}, [%1];" : "=r"(r) : "r"(taddr) : "memory");
 }
+// The warp index as a value the compiler can prove warp-uniform.  A warp that runs its loop CONVERGED
+// and issues single-thread instructions (tcgen05.mma, TMA) under `if (elect_one())` keeps their operands
+// in uniform registers; issuing them from an `if (lane == 0)` region makes ptxas wrap each one in an
+// elect / broadcast / branch sequence of ~20 instructions.
+B200_DEVINL int uniform_warp_idx() { return __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0); }
+
 // Explicit shared-space accesses by 32-bit shared address.  Pointers into the dynamic shared array that
 // went through integer alignment arithmetic compile to GENERIC loads/stores with 64-bit address math;
 // these keep hot paths on LDS/STS.

@@ -127,11 +127,53 @@ static int launch_gemm_t(const b200_encoder* e, const GemmIO& io, GemmParams p, 
   return B200_OK;
 }
 
+// A-stationary CTA-pair GEMM (gemm_bf16_ast_kernel): K <= 384, whole 256-row blocks.
+template <int BLOCK_N, int EPI>
+static int launch_gemm_ast(const b200_encoder* e, const GemmIO& io, GemmParams p, cudaStream_t st) {
+  constexpr int NEPI = gemm_epi_warps(BLOCK_N);
+  const size_t slab = (size_t)GEMM_AST_MAX_KB * GEMM_A_STAGE_BYTES;
+  const size_t stage = (size_t)(BLOCK_N / 2) * GEMM_BLOCK_K * 2;
+  const size_t max_smem = 232448;
+  // staging boxes, barriers (2*nstage + 2*MAX_KB + 4 + NEPI, at most 8 stages), TMEM slot, per-warp bias slices
+  const size_t tail = (size_t)NEPI * GEMM_STAGING_BYTES + 8 * (2 * 8 + 2 * GEMM_AST_MAX_KB + 4 + NEPI) + 16 +
+                      (size_t)NEPI * GEMM_OUT_CHUNK * 4;
+  const int nstage = (int)std::min<size_t>(8, (max_smem - 1024 - slab - tail) / stage);
+  if (nstage < 2) B200_FAIL(B200_ERR_UNSUPPORTED, "A-stationary GEMM tile does not fit in shared memory");
+  p.nstage = nstage;
+  const size_t smem = 1024 + slab + (size_t)nstage * stage + tail;
+  auto kern = gemm_bf16_ast_kernel<BLOCK_N, EPI>;
+  B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  const int m_blocks = p.M / (2 * GEMM_BLOCK_M);
+  const int grid = std::min(m_blocks, e->num_sms / 2) * 2;
+  {
+    B200_PROF(EPI == EPI_BIAS ? "gemm_bias" : (EPI == EPI_BIAS_GELU ? "gemm_bias_gelu" : "gemm_bias_resid"),
+              2.0 * p.M * (double)p.N * p.K,
+              2.0 * ((double)p.M * p.K + (double)p.N * p.K + (double)p.M * p.N * (EPI == EPI_BIAS_RESID ? 2 : 1)), st);
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(gemm_threads(BLOCK_N));
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    B200_CUDA(cudaLaunchKernelEx(&cfg, kern, *io.a, *io.w2, *io.out, *io.resid, p));
+  }
+  B200_CUDA(cudaGetLastError());
+  return B200_OK;
+}
+
 template <int EPI>
 static int launch_gemm(const b200_encoder* e, const GemmIO& io, const GemmParams& p, cudaStream_t st) {
   // CTA pairs need whole 256-row tiles; B200_GEMM_CG=1 forces single-CTA tiles (A/B timing)
   const char* cg_env = getenv("B200_GEMM_CG");
   const bool pair = (p.M % (2 * GEMM_BLOCK_M) == 0) && io.w2 != nullptr && !(cg_env && atoi(cg_env) == 1);
+  // K <= 384: keep the activation slab in shared memory across column tiles (B200_GEMM_AST=0 disables)
+  const char* ast_env = getenv("B200_GEMM_AST");
+  if (pair && pick_block_n(p.N) == 192 && p.K <= GEMM_AST_MAX_KB * GEMM_BLOCK_K && p.N / 192 >= 2 &&
+      !(ast_env && atoi(ast_env) == 0))
+    return launch_gemm_ast<192, EPI>(e, io, p, st);
   switch (pick_block_n(p.N)) {
     case 192: return pair ? launch_gemm_t<192, EPI, 2>(e, io, p, st) : launch_gemm_t<192, EPI, 1>(e, io, p, st);
     case 128: return pair ? launch_gemm_t<128, EPI, 2>(e, io, p, st) : launch_gemm_t<128, EPI, 1>(e, io, p, st);
@@ -442,6 +484,17 @@ extern "C" int b200_debug_att_timing(unsigned long long* out) {
   cudaMemcpyFromSymbol(out, b200::g_att_timing, 16 * sizeof(unsigned long long));
   unsigned long long z[16] = {0};
   cudaMemcpyToSymbol(b200::g_att_timing, z, sizeof(z));
+  return 0;
+}
+#endif
+
+#ifdef B200_GEMM_TIMING
+extern "C" int b200_debug_gemm_timing(unsigned long long* out) {
+  cudaDeviceSynchronize();
+  cudaMemcpyFromSymbol(out, b200::g_gemm_timing, 8 * sizeof(unsigned long long));
+  unsigned long long z[8] = {0};
+  z[7] = getenv("B200_GEMM_NOEPI") ? (unsigned long long)atoi(getenv("B200_GEMM_NOEPI")) : 0;
+  cudaMemcpyToSymbol(b200::g_gemm_timing, z, sizeof(z));
   return 0;
 }
 #endif

@@ -155,6 +155,91 @@ B200_DEVINL float gelu_erf(float x) {
   return fmaf(hx, th, hx);
 }
 
+#ifdef B200_GEMM_TIMING
+// Development aid (not compiled into the shipped library): where the MMA issuer of CTA pair 0 spends its
+// clocks.  [0] waiting for a free accumulator, [1] waiting for operands, [2] issuing, [3] tiles, [4] total.
+__device__ unsigned long long g_gemm_timing[8];
+#endif
+
+// One epilogue warp's share of one output tile: 32 rows (TMEM lanes) x 64 columns.  Accumulator ->
+// registers (one tcgen05.ld.x64), bias (+ GELU | + residual, which arrives by TMA in the staging box),
+// bf16, 128-byte-swizzled staging box, TMA store.
+template <int EPI, int CG>
+B200_DEVINL void gemm_epi_tile(const CUtensorMap& map_out, const CUtensorMap& map_resid, const float* bias, int m0, int n0,
+                               uint8_t* stg, float* sbias, uint64_t* rbar, uint8_t* my_row, int sw, int lane, uint32_t tacc,
+                               uint64_t* acc_full_bar, uint32_t aph, uint64_t* acc_empty_bar, uint32_t it) {
+  __syncwarp();
+  sbias[lane] = __ldg(bias + n0 + lane);
+  sbias[lane + 32] = __ldg(bias + n0 + 32 + lane);
+  if (lane == 0) {
+    tma_store_wait_read();   // the previous tile's store has finished reading this warp's box
+    if (EPI == EPI_BIAS_RESID) {
+      mbar_arrive_expect_tx(rbar, GEMM_STAGING_BYTES);
+      tma_load_2d(stg, &map_resid, rbar, n0, m0);
+    }
+  }
+  __syncwarp();
+  mbar_wait(acc_full_bar, aph);
+  tc_fence_after();
+  uint32_t v[64];
+  tmem_ld64(tacc, v);
+  tmem_ld_wait();
+  tc_fence_before();         // this warp's share of the accumulator stage is in registers
+  __syncwarp();
+  if (lane == 0) {
+    if (CG == 2) mbar_arrive_leader(acc_empty_bar); else mbar_arrive(acc_empty_bar);
+  }
+  if (EPI == EPI_BIAS_RESID) mbar_wait(rbar, it & 1);
+#ifdef B200_GEMM_TIMING
+  const unsigned long long dbg = g_gemm_timing[7];
+  if (dbg == 1) return;   // experiment: accumulators drained, nothing computed or stored
+#endif
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {   // 8 columns = one 16-byte piece of this thread's row
+    const float4 b0 = *reinterpret_cast<const float4*>(sbias + j * 8);
+    const float4 b1 = *reinterpret_cast<const float4*>(sbias + j * 8 + 4);
+    float f[8];
+    f[0] = __uint_as_float(v[j * 8 + 0]) + b0.x; f[1] = __uint_as_float(v[j * 8 + 1]) + b0.y;
+    f[2] = __uint_as_float(v[j * 8 + 2]) + b0.z; f[3] = __uint_as_float(v[j * 8 + 3]) + b0.w;
+    f[4] = __uint_as_float(v[j * 8 + 4]) + b1.x; f[5] = __uint_as_float(v[j * 8 + 5]) + b1.y;
+    f[6] = __uint_as_float(v[j * 8 + 6]) + b1.z; f[7] = __uint_as_float(v[j * 8 + 7]) + b1.w;
+    if (EPI == EPI_BIAS_GELU) {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) f[i] = gelu_erf(f[i]);
+    }
+    uint4* slot = reinterpret_cast<uint4*>(my_row + ((j ^ sw) << 4));
+    if (EPI == EPI_BIAS_RESID) {
+      const uint4 r = *slot;
+      const __nv_bfloat162* r2 = reinterpret_cast<const __nv_bfloat162*>(&r);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        f[2 * i] += __low2float(r2[i]);
+        f[2 * i + 1] += __high2float(r2[i]);
+      }
+    }
+    uint4 o;
+    __nv_bfloat162 t0 = __floats2bfloat162_rn(f[0], f[1]);
+    __nv_bfloat162 t1 = __floats2bfloat162_rn(f[2], f[3]);
+    __nv_bfloat162 t2 = __floats2bfloat162_rn(f[4], f[5]);
+    __nv_bfloat162 t3 = __floats2bfloat162_rn(f[6], f[7]);
+    o.x = *reinterpret_cast<uint32_t*>(&t0); o.y = *reinterpret_cast<uint32_t*>(&t1);
+    o.z = *reinterpret_cast<uint32_t*>(&t2); o.w = *reinterpret_cast<uint32_t*>(&t3);
+    *slot = o;
+  }
+#ifdef B200_GEMM_TIMING
+  if (dbg == 3) return;      // experiment: no fence, no store
+#endif
+  fence_proxy_async();       // generic-proxy writes -> visible to the TMA (async proxy)
+  __syncwarp();
+#ifdef B200_GEMM_TIMING
+  if (dbg == 2) return;      // experiment: no store
+#endif
+  if (lane == 0) {
+    tma_store_2d(&map_out, stg, n0, m0);
+    tma_store_commit();
+  }
+}
+
 // CG = 1: one CTA per 128 x BLOCK_N tile.  CG = 2: a CTA pair (cluster of 2, cta_group::2) per
 // 256 x BLOCK_N tile -- each CTA loads its own 128 rows of A but only HALF of the weight tile, and the
 // leader's single MMA drives both SMs' tensor cores.  That halves the weight bytes every SM pulls
@@ -187,7 +272,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(resid_bar + NEPI);
   float* bias_smem = reinterpret_cast<float*>(tmem_slot + 4);               // [NEPI][64]
 
-  const int warp = threadIdx.x >> 5;
+  const int warp = uniform_warp_idx();
   const int lane = threadIdx.x & 31;
   const int rank = (CG == 2) ? (int)cluster_ctarank() : 0;
   const bool leader = rank == 0;
@@ -225,8 +310,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
-    // ===== TMA producer (every CTA loads its own A rows and its share of the weight tile) =====
-    if (lane == 0) {
+    // ===== TMA producer (every CTA loads its own A rows and its share of the weight tile); the warp runs
+    // the loop converged, one elected lane issues =====
+    {
       int s = 0;
       uint32_t ph = 0;
       for (int tile = group; tile < total_tiles; tile += n_groups) {
@@ -235,46 +321,77 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
         for (int kb = 0; kb < num_k; ++kb) {
           mbar_wait(&empty[s], ph ^ 1);
           uint8_t* sa = smem + (size_t)s * STAGE_BYTES;
-          if (CG == 2) {
-            if (leader) mbar_arrive_expect_tx(&full[s], STAGE_BYTES * CG);
-            else mbar_arrive_leader(&full[s]);
-            tma_load_2d_2sm(sa, &map_a, &full[s], kb * GEMM_BLOCK_K, m0);
-            tma_load_2d_2sm(sa + GEMM_A_STAGE_BYTES, &map_b, &full[s], kb * GEMM_BLOCK_K, n0);
-          } else {
-            mbar_arrive_expect_tx(&full[s], STAGE_BYTES);
-            tma_load_2d(sa, &map_a, &full[s], kb * GEMM_BLOCK_K, m0);
-            tma_load_2d(sa + GEMM_A_STAGE_BYTES, &map_b, &full[s], kb * GEMM_BLOCK_K, n0);
+          if (elect_one()) {
+            if (CG == 2) {
+              if (leader) mbar_arrive_expect_tx(&full[s], STAGE_BYTES * CG);
+              else mbar_arrive_leader(&full[s]);
+              tma_load_2d_2sm(sa, &map_a, &full[s], kb * GEMM_BLOCK_K, m0);
+              tma_load_2d_2sm(sa + GEMM_A_STAGE_BYTES, &map_b, &full[s], kb * GEMM_BLOCK_K, n0);
+            } else {
+              mbar_arrive_expect_tx(&full[s], STAGE_BYTES);
+              tma_load_2d(sa, &map_a, &full[s], kb * GEMM_BLOCK_K, m0);
+              tma_load_2d(sa + GEMM_A_STAGE_BYTES, &map_b, &full[s], kb * GEMM_BLOCK_K, n0);
+            }
           }
+          __syncwarp();
           if (++s == p.nstage) { s = 0; ph ^= 1; }
         }
       }
     }
   } else if (warp == 1) {
-    // ===== MMA issuer (one thread of the leader CTA) =====
-    if (lane == 0 && leader) {
+    // ===== MMA issuer: the leader CTA's warp 1 runs the loop converged, one elected lane issues =====
+    if (leader) {
       int s = 0;
       uint32_t ph = 0, it = 0;
       const uint32_t smem_addr = smem_u32(smem);
       for (int tile = group; tile < total_tiles; tile += n_groups, ++it) {
         const uint32_t as = it & 1, aph = (it >> 1) & 1;
+#ifdef B200_GEMM_TIMING
+        const long long g0 = clock64();
+#endif
         mbar_wait(&acc_empty[as], aph ^ 1);
         tc_fence_after();
+#ifdef B200_GEMM_TIMING
+        long long g1 = clock64(), gw = 0;
+        if (blockIdx.x == 0 && lane == 0) atomicAdd(&g_gemm_timing[0], (unsigned long long)(g1 - g0));
+#endif
         const uint32_t tacc = tmem_base + as * BLOCK_N;
         for (int kb = 0; kb < num_k; ++kb) {
+#ifdef B200_GEMM_TIMING
+          const long long w0 = clock64();
+#endif
           mbar_wait(&full[s], ph);
           tc_fence_after();
+#ifdef B200_GEMM_TIMING
+          gw += clock64() - w0;
+#endif
           const uint32_t a_addr = smem_addr + (uint32_t)s * STAGE_BYTES;
           const uint64_t da = umma_smem_desc_sw128(a_addr);
           const uint64_t db = umma_smem_desc_sw128(a_addr + GEMM_A_STAGE_BYTES);
+          if (elect_one()) {
 #pragma unroll
-          for (int k = 0; k < GEMM_BLOCK_K / 16; ++k) {
-            if (CG == 2) umma_bf16_2sm(tacc, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), IDESC, (uint32_t)((kb | k) != 0));
-            else umma_bf16(tacc, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), IDESC, (uint32_t)((kb | k) != 0));
+            for (int k = 0; k < GEMM_BLOCK_K / 16; ++k) {
+              if (CG == 2) umma_bf16_2sm(tacc, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), IDESC, (uint32_t)((kb | k) != 0));
+              else umma_bf16(tacc, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), IDESC, (uint32_t)((kb | k) != 0));
+            }
+            if (CG == 2) umma_commit_2sm(&empty[s]); else umma_commit(&empty[s]);
           }
-          if (CG == 2) umma_commit_2sm(&empty[s]); else umma_commit(&empty[s]);
+          __syncwarp();
           if (++s == p.nstage) { s = 0; ph ^= 1; }
         }
-        if (CG == 2) umma_commit_2sm(&acc_full[as]); else umma_commit(&acc_full[as]);
+        if (elect_one()) {
+          if (CG == 2) umma_commit_2sm(&acc_full[as]); else umma_commit(&acc_full[as]);
+        }
+        __syncwarp();
+#ifdef B200_GEMM_TIMING
+        if (blockIdx.x == 0 && lane == 0) {
+          const long long g2 = clock64();
+          atomicAdd(&g_gemm_timing[1], (unsigned long long)gw);
+          atomicAdd(&g_gemm_timing[2], (unsigned long long)(g2 - g1 - gw));
+          atomicAdd(&g_gemm_timing[3], 1ull);
+          atomicAdd(&g_gemm_timing[4], (unsigned long long)(g2 - g0));
+        }
+#endif
       }
     }
   } else if (warp >= 4) {
@@ -292,66 +409,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
       const uint32_t as = it & 1, aph = (it >> 1) & 1;
       const int m0 = (tile / n_tiles) * (GEMM_BLOCK_M * CG) + rank * GEMM_BLOCK_M + wq * 32;
       const int n0 = (tile % n_tiles) * BLOCK_N + chunk * GEMM_OUT_CHUNK;
-      __syncwarp();
-      sbias[lane] = __ldg(p.bias + n0 + lane);
-      sbias[lane + 32] = __ldg(p.bias + n0 + 32 + lane);
-      if (lane == 0) {
-        tma_store_wait_read();   // the previous tile's store has finished reading this warp's box
-        if (EPI == EPI_BIAS_RESID) {
-          mbar_arrive_expect_tx(rbar, GEMM_STAGING_BYTES);
-          tma_load_2d(stg, &map_resid, rbar, n0, m0);
-        }
-      }
-      __syncwarp();
-      mbar_wait(&acc_full[as], aph);
-      tc_fence_after();
-      uint32_t v[64];
-      tmem_ld64(tmem_base + ((uint32_t)(wq * 32) << 16) + as * BLOCK_N + chunk * GEMM_OUT_CHUNK, v);
-      tmem_ld_wait();
-      tc_fence_before();         // this warp's share of the accumulator stage is in registers
-      __syncwarp();
-      if (lane == 0) {
-        if (CG == 2) mbar_arrive_leader(&acc_empty[as]); else mbar_arrive(&acc_empty[as]);
-      }
-      if (EPI == EPI_BIAS_RESID) mbar_wait(rbar, it & 1);
-#pragma unroll
-      for (int j = 0; j < 8; ++j) {   // 8 columns = one 16-byte piece of this thread's row
-        const float4 b0 = *reinterpret_cast<const float4*>(sbias + j * 8);
-        const float4 b1 = *reinterpret_cast<const float4*>(sbias + j * 8 + 4);
-        float f[8];
-        f[0] = __uint_as_float(v[j * 8 + 0]) + b0.x; f[1] = __uint_as_float(v[j * 8 + 1]) + b0.y;
-        f[2] = __uint_as_float(v[j * 8 + 2]) + b0.z; f[3] = __uint_as_float(v[j * 8 + 3]) + b0.w;
-        f[4] = __uint_as_float(v[j * 8 + 4]) + b1.x; f[5] = __uint_as_float(v[j * 8 + 5]) + b1.y;
-        f[6] = __uint_as_float(v[j * 8 + 6]) + b1.z; f[7] = __uint_as_float(v[j * 8 + 7]) + b1.w;
-        if (EPI == EPI_BIAS_GELU) {
-#pragma unroll
-          for (int i = 0; i < 8; ++i) f[i] = gelu_erf(f[i]);
-        }
-        uint4* slot = reinterpret_cast<uint4*>(my_row + ((j ^ sw) << 4));
-        if (EPI == EPI_BIAS_RESID) {
-          const uint4 r = *slot;
-          const __nv_bfloat162* r2 = reinterpret_cast<const __nv_bfloat162*>(&r);
-#pragma unroll
-          for (int i = 0; i < 4; ++i) {
-            f[2 * i] += __low2float(r2[i]);
-            f[2 * i + 1] += __high2float(r2[i]);
-          }
-        }
-        uint4 o;
-        __nv_bfloat162 t0 = __floats2bfloat162_rn(f[0], f[1]);
-        __nv_bfloat162 t1 = __floats2bfloat162_rn(f[2], f[3]);
-        __nv_bfloat162 t2 = __floats2bfloat162_rn(f[4], f[5]);
-        __nv_bfloat162 t3 = __floats2bfloat162_rn(f[6], f[7]);
-        o.x = *reinterpret_cast<uint32_t*>(&t0); o.y = *reinterpret_cast<uint32_t*>(&t1);
-        o.z = *reinterpret_cast<uint32_t*>(&t2); o.w = *reinterpret_cast<uint32_t*>(&t3);
-        *slot = o;
-      }
-      fence_proxy_async();       // generic-proxy writes -> visible to the TMA (async proxy)
-      __syncwarp();
-      if (lane == 0) {
-        tma_store_2d(&map_out, stg, n0, m0);
-        tma_store_commit();
-      }
+      gemm_epi_tile<EPI, CG>(map_out, map_resid, p.bias, m0, n0, stg, sbias, rbar, my_row, sw, lane,
+                             tmem_base + ((uint32_t)(wq * 32) << 16) + as * BLOCK_N + chunk * GEMM_OUT_CHUNK,
+                             &acc_full[as], aph, &acc_empty[as], it);
     }
     if (lane == 0) tma_store_wait_all();
   }
@@ -363,6 +423,202 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     tc_fence_after();
     if (CG == 2) tmem_dealloc_2sm(tmem_base, TMEM_COLS);
     else tmem_dealloc(tmem_base, TMEM_COLS);
+  }
+}
+
+// A-stationary variant for K <= GEMM_AST_MAX_KB * 64 (the encoder's K = hidden GEMMs), CTA pairs only.
+// The generic kernel re-reads the activation tile once per column tile (N / BLOCK_N times: 6 for the
+// QKV projection, 8 for FFN1) and at ~10 TB/s of L2 -> SM traffic that, not the tensor pipe, is what
+// holds it at 60 % MMA duty.  Here a CTA keeps its 128 x K slab of A in shared memory for ALL column
+// tiles of its row block and streams only the weight half-tiles through a ring:
+//   L2 -> SM bytes, QKV projection: 1.06 GB -> 0.55 GB;  FFN1: 1.41 GB -> 0.70 GB.
+// Each 64-wide k-block of the slab has its own full / empty barrier, so the producer refills the
+// slab with the next row block k-block by k-block while the last column tile is still being issued.
+constexpr int GEMM_AST_MAX_KB = 6;
+
+template <int BLOCK_N, int EPI>
+__global__ void __launch_bounds__(gemm_threads(BLOCK_N), 1)
+gemm_bf16_ast_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
+                     const __grid_constant__ CUtensorMap map_out, const __grid_constant__ CUtensorMap map_resid,
+                     const GemmParams p) {
+  constexpr int CG = 2;
+  constexpr uint32_t B_ROWS = BLOCK_N / CG;                      // weight rows this CTA loads per stage
+  constexpr uint32_t B_STAGE_BYTES = B_ROWS * GEMM_BLOCK_K * 2;
+  constexpr uint32_t SLAB_BYTES = GEMM_AST_MAX_KB * GEMM_A_STAGE_BYTES;
+  constexpr uint32_t IDESC = umma_idesc_bf16_f32(GEMM_BLOCK_M * CG, BLOCK_N);
+  constexpr uint32_t TMEM_COLS = (2 * BLOCK_N <= 128) ? 128 : ((2 * BLOCK_N <= 256) ? 256 : 512);
+  constexpr int NEPI = gemm_epi_warps(BLOCK_N);
+  static_assert(BLOCK_N % 64 == 0 && BLOCK_N <= 256, "BLOCK_N must be 64..256 in steps of 64");
+  static_assert(B_STAGE_BYTES % 1024 == 0, "weight stages must keep the 1024-byte swizzle alignment");
+
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* ring = smem + SLAB_BYTES;                                        // [nstage] weight half-tiles
+  uint8_t* staging = ring + (size_t)p.nstage * B_STAGE_BYTES;               // [NEPI][4 KB], 1024-aligned
+  uint64_t* bars = reinterpret_cast<uint64_t*>(staging + (size_t)NEPI * GEMM_STAGING_BYTES);
+  uint64_t* b_full = bars;                                 // [nstage]  TMA -> MMA   (leader's copy is the one used)
+  uint64_t* b_empty = bars + p.nstage;                     // [nstage]  MMA -> TMA   (one per CTA)
+  uint64_t* a_full = bars + 2 * p.nstage;                  // [MAX_KB]  TMA -> MMA   (leader's copy)
+  uint64_t* a_empty = a_full + GEMM_AST_MAX_KB;            // [MAX_KB]  MMA -> TMA   (one per CTA)
+  uint64_t* acc_full = a_empty + GEMM_AST_MAX_KB;          // [2]       MMA -> epilogue     (one per CTA)
+  uint64_t* acc_empty = acc_full + 2;                      // [2]       epilogue -> MMA     (leader's copy)
+  uint64_t* resid_bar = acc_empty + 2;                     // [NEPI]    residual box landed (one per epilogue warp)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(resid_bar + NEPI);
+  float* bias_smem = reinterpret_cast<float*>(tmem_slot + 4);               // [NEPI][64]
+
+  const int warp = uniform_warp_idx();
+  const int lane = threadIdx.x & 31;
+  const int rank = (int)cluster_ctarank();
+  const bool leader = rank == 0;
+  const int n_tiles = p.N / BLOCK_N;
+  const int m_blocks = p.M / (GEMM_BLOCK_M * CG);
+  const int group = blockIdx.x / CG, n_groups = gridDim.x / CG;
+  const int num_k = p.K / GEMM_BLOCK_K;                    // <= GEMM_AST_MAX_KB (checked by the host)
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&map_a);
+    tma_prefetch_desc(&map_b);
+    tma_prefetch_desc(&map_out);
+    if (EPI == EPI_BIAS_RESID) tma_prefetch_desc(&map_resid);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < p.nstage; ++i) {
+      mbar_init(&b_full[i], CG);               // one arrival per CTA of the pair
+      mbar_init(&b_empty[i], 1);
+    }
+    for (int i = 0; i < GEMM_AST_MAX_KB; ++i) {
+      mbar_init(&a_full[i], CG);
+      mbar_init(&a_empty[i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&acc_full[i], 1);
+      mbar_init(&acc_empty[i], NEPI * CG);
+    }
+    for (int i = 0; i < NEPI; ++i) mbar_init(&resid_bar[i], 1);
+    fence_mbar_init();
+  }
+  if (warp == 2) tmem_alloc_2sm(tmem_slot, TMEM_COLS);
+  tc_fence_before();
+  cluster_sync_all();                          // the peer's barriers are initialised before anyone signals them
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===== TMA producer: this CTA's 128 rows of A once per row block, its half of every weight tile; the
+    // warp runs the loop converged, one elected lane issues =====
+    {
+      int s = 0;
+      uint32_t ph = 0, mbi = 0;
+      for (int mb = group; mb < m_blocks; mb += n_groups, ++mbi) {
+        const int m0 = mb * (GEMM_BLOCK_M * CG) + rank * GEMM_BLOCK_M;
+        for (int nt = 0; nt < n_tiles; ++nt) {
+          const int n0 = nt * BLOCK_N + rank * (int)B_ROWS;
+          for (int kb = 0; kb < num_k; ++kb) {
+            if (nt == 0) {
+              mbar_wait(&a_empty[kb], (mbi & 1) ^ 1);      // the previous row block is done with this k-block
+              if (elect_one()) {
+                if (leader) mbar_arrive_expect_tx(&a_full[kb], GEMM_A_STAGE_BYTES * CG);
+                else mbar_arrive_leader(&a_full[kb]);
+                tma_load_2d_2sm(smem + (size_t)kb * GEMM_A_STAGE_BYTES, &map_a, &a_full[kb], kb * GEMM_BLOCK_K, m0);
+              }
+              __syncwarp();
+            }
+            mbar_wait(&b_empty[s], ph ^ 1);
+            if (elect_one()) {
+              if (leader) mbar_arrive_expect_tx(&b_full[s], B_STAGE_BYTES * CG);
+              else mbar_arrive_leader(&b_full[s]);
+              tma_load_2d_2sm(ring + (size_t)s * B_STAGE_BYTES, &map_b, &b_full[s], kb * GEMM_BLOCK_K, n0);
+            }
+            __syncwarp();
+            if (++s == p.nstage) { s = 0; ph ^= 1; }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer: the leader CTA's warp 1 runs the loop converged, one elected lane issues =====
+    if (leader) {
+      int s = 0;
+      uint32_t ph = 0, it = 0, mbi = 0;
+      const uint32_t slab_addr = smem_u32(smem), ring_addr = smem_u32(ring);
+      for (int mb = group; mb < m_blocks; mb += n_groups, ++mbi) {
+        for (int nt = 0; nt < n_tiles; ++nt, ++it) {
+          const uint32_t as = it & 1, aph = (it >> 1) & 1;
+#ifdef B200_GEMM_TIMING
+          const long long g0 = clock64();
+#endif
+          mbar_wait(&acc_empty[as], aph ^ 1);
+          tc_fence_after();
+#ifdef B200_GEMM_TIMING
+          long long g1 = clock64(), gw = 0;
+          if (blockIdx.x == 0 && lane == 0) atomicAdd(&g_gemm_timing[0], (unsigned long long)(g1 - g0));
+#endif
+          const uint32_t tacc = tmem_base + as * BLOCK_N;
+          for (int kb = 0; kb < num_k; ++kb) {
+#ifdef B200_GEMM_TIMING
+            const long long w0 = clock64();
+#endif
+            if (nt == 0) mbar_wait(&a_full[kb], mbi & 1);
+            mbar_wait(&b_full[s], ph);
+            tc_fence_after();
+#ifdef B200_GEMM_TIMING
+            gw += clock64() - w0;
+#endif
+            const uint64_t da = umma_smem_desc_sw128(slab_addr + (uint32_t)kb * GEMM_A_STAGE_BYTES);
+            const uint64_t db = umma_smem_desc_sw128(ring_addr + (uint32_t)s * B_STAGE_BYTES);
+            if (elect_one()) {
+#pragma unroll
+              for (int k = 0; k < GEMM_BLOCK_K / 16; ++k)
+                umma_bf16_2sm(tacc, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), IDESC, (uint32_t)((kb | k) != 0));
+              umma_commit_2sm(&b_empty[s]);
+              if (nt == n_tiles - 1) umma_commit_2sm(&a_empty[kb]);   // last use of this k-block of the slab
+            }
+            __syncwarp();
+            if (++s == p.nstage) { s = 0; ph ^= 1; }
+          }
+          if (elect_one()) umma_commit_2sm(&acc_full[as]);
+          __syncwarp();
+#ifdef B200_GEMM_TIMING
+          if (blockIdx.x == 0 && lane == 0) {
+            const long long g2 = clock64();
+            atomicAdd(&g_gemm_timing[1], (unsigned long long)gw);
+            atomicAdd(&g_gemm_timing[2], (unsigned long long)(g2 - g1 - gw));
+            atomicAdd(&g_gemm_timing[3], 1ull);
+            atomicAdd(&g_gemm_timing[4], (unsigned long long)(g2 - g0));
+          }
+#endif
+        }
+      }
+    }
+  } else if (warp >= 4) {
+    // ===== epilogue warp: TMEM lanes [32 wq, +32) x columns [64 chunk, +64) of this CTA's 128 rows =====
+    const int e = warp - 4;
+    const int wq = e & 3;         // == warp % 4: the TMEM lane group this warp may read
+    const int chunk = e >> 2;
+    uint8_t* stg = staging + (size_t)e * GEMM_STAGING_BYTES;
+    float* sbias = bias_smem + e * GEMM_OUT_CHUNK;
+    uint64_t* rbar = &resid_bar[e];
+    uint8_t* my_row = stg + lane * 128;
+    const int sw = lane & 7;       // 128-byte swizzle: 16-byte chunk j of row r lives at chunk j ^ (r % 8)
+    uint32_t it = 0;
+    for (int mb = group; mb < m_blocks; mb += n_groups) {
+      for (int nt = 0; nt < n_tiles; ++nt, ++it) {
+        const uint32_t as = it & 1, aph = (it >> 1) & 1;
+        const int m0 = mb * (GEMM_BLOCK_M * CG) + rank * GEMM_BLOCK_M + wq * 32;
+        const int n0 = nt * BLOCK_N + chunk * GEMM_OUT_CHUNK;
+        gemm_epi_tile<EPI, CG>(map_out, map_resid, p.bias, m0, n0, stg, sbias, rbar, my_row, sw, lane,
+                               tmem_base + ((uint32_t)(wq * 32) << 16) + as * BLOCK_N + chunk * GEMM_OUT_CHUNK,
+                               &acc_full[as], aph, &acc_empty[as], it);
+      }
+    }
+    if (lane == 0) tma_store_wait_all();
+  }
+
+  tc_fence_before();
+  cluster_sync_all();                          // no CTA leaves while its peer may still signal its barriers
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc_2sm(tmem_base, TMEM_COLS);
   }
 }
 

@@ -79,5 +79,9 @@ int main() {
   run<64, 1, false>(d);
   run<128, 1, false>(d);
   run<256, 1, false>(d);
+  run<192, 1, false>(d);
+  run<160, 1, false>(d);
+  run<96, 1, false>(d);
+  run<224, 1, false>(d);
   return 0;
 }
