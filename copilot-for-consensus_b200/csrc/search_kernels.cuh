@@ -188,7 +188,7 @@ sim_topk_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant
   uint64_t* a_full = acc_empty + 2;            // [1]       query tile landed
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(a_full + 1);
 
-  const int warp = threadIdx.x >> 5;
+  const int warp = uniform_warp_idx();
   const int lane = threadIdx.x & 31;
   const int qtile = (CG == 1 && p.split_major) ? blockIdx.y : blockIdx.x;   // CTA pair = query tiles (2i, 2i+1)
   const int split = (CG == 1 && p.split_major) ? blockIdx.x : blockIdx.y;
@@ -228,39 +228,45 @@ sim_topk_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
-    // ===== TMA producer =====
-    if (lane == 0 && ntiles > 0) {
-      if (CG == 2) {
-        if (leader) mbar_arrive_expect_tx(a_full, (uint32_t)p.kc * SIM_A_CHUNK_BYTES * CG);
-        else mbar_arrive_leader(a_full);
-        for (int c = 0; c < p.kc; ++c)
-          tma_load_2d_2sm(sA + (size_t)c * SIM_A_CHUNK_BYTES, &map_q, a_full, c * SIM_BLOCK_K, qtile * SIM_BLOCK_M);
-      } else {
-        mbar_arrive_expect_tx(a_full, (uint32_t)p.kc * SIM_A_CHUNK_BYTES);
-        for (int c = 0; c < p.kc; ++c)
-          tma_load_2d(sA + (size_t)c * SIM_A_CHUNK_BYTES, &map_q, a_full, c * SIM_BLOCK_K, qtile * SIM_BLOCK_M);
+    // ===== TMA producer: the warp runs the loop converged, one elected lane issues (see uniform_warp_idx) =====
+    if (ntiles > 0) {
+      if (elect_one()) {
+        if (CG == 2) {
+          if (leader) mbar_arrive_expect_tx(a_full, (uint32_t)p.kc * SIM_A_CHUNK_BYTES * CG);
+          else mbar_arrive_leader(a_full);
+          for (int c = 0; c < p.kc; ++c)
+            tma_load_2d_2sm(sA + (size_t)c * SIM_A_CHUNK_BYTES, &map_q, a_full, c * SIM_BLOCK_K, qtile * SIM_BLOCK_M);
+        } else {
+          mbar_arrive_expect_tx(a_full, (uint32_t)p.kc * SIM_A_CHUNK_BYTES);
+          for (int c = 0; c < p.kc; ++c)
+            tma_load_2d(sA + (size_t)c * SIM_A_CHUNK_BYTES, &map_q, a_full, c * SIM_BLOCK_K, qtile * SIM_BLOCK_M);
+        }
       }
+      __syncwarp();
       int s = 0;
       uint32_t ph = 0;
       for (uint32_t t = 0; t < ntiles; ++t) {
         const int32_t row = (int32_t)((tile0 + t) * BLOCK_N + rank * B_ROWS);
         for (int c = 0; c < p.kc; ++c) {
           mbar_wait(&empty[s], ph ^ 1);
-          if (CG == 2) {
-            if (leader) mbar_arrive_expect_tx(&full[s], B_STAGE_BYTES * CG);
-            else mbar_arrive_leader(&full[s]);
-            tma_load_2d_2sm(sB + (size_t)s * B_STAGE_BYTES, &map_c, &full[s], c * SIM_BLOCK_K, row);
-          } else {
-            mbar_arrive_expect_tx(&full[s], B_STAGE_BYTES);
-            tma_load_2d(sB + (size_t)s * B_STAGE_BYTES, &map_c, &full[s], c * SIM_BLOCK_K, row);
+          if (elect_one()) {
+            if (CG == 2) {
+              if (leader) mbar_arrive_expect_tx(&full[s], B_STAGE_BYTES * CG);
+              else mbar_arrive_leader(&full[s]);
+              tma_load_2d_2sm(sB + (size_t)s * B_STAGE_BYTES, &map_c, &full[s], c * SIM_BLOCK_K, row);
+            } else {
+              mbar_arrive_expect_tx(&full[s], B_STAGE_BYTES);
+              tma_load_2d(sB + (size_t)s * B_STAGE_BYTES, &map_c, &full[s], c * SIM_BLOCK_K, row);
+            }
           }
+          __syncwarp();
           if (++s == p.nstage) { s = 0; ph ^= 1; }
         }
       }
     }
   } else if (warp == 1) {
-    // ===== MMA issuer (one thread of the leader CTA) =====
-    if (lane == 0 && ntiles > 0 && leader) {
+    // ===== MMA issuer: the leader CTA's warp 1 runs the loop converged, one elected lane issues =====
+    if (ntiles > 0 && leader) {
       mbar_wait(a_full, 0);
       tc_fence_after();
       const uint32_t a_addr = smem_u32(sA);
@@ -277,16 +283,22 @@ sim_topk_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant
           tc_fence_after();
           const uint64_t da = umma_smem_desc_sw128(a_addr + (uint32_t)c * SIM_A_CHUNK_BYTES);
           const uint64_t db = umma_smem_desc_sw128(b_addr + (uint32_t)s * B_STAGE_BYTES);
+          if (elect_one()) {
 #pragma unroll
-          for (int k = 0; k < SIM_BLOCK_K / 16; ++k) {
-            // +32 bytes per K=16 step inside the 128-byte swizzle row: +2 in the >>4 address field
-            if (CG == 2) umma_bf16_2sm(tacc, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), IDESC, (uint32_t)((c | k) != 0));
-            else umma_bf16(tacc, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), IDESC, (uint32_t)((c | k) != 0));
+            for (int k = 0; k < SIM_BLOCK_K / 16; ++k) {
+              // +32 bytes per K=16 step inside the 128-byte swizzle row: +2 in the >>4 address field
+              if (CG == 2) umma_bf16_2sm(tacc, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), IDESC, (uint32_t)((c | k) != 0));
+              else umma_bf16(tacc, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), IDESC, (uint32_t)((c | k) != 0));
+            }
+            if (CG == 2) umma_commit_2sm(&empty[s]); else umma_commit(&empty[s]);   // stage reusable once read
           }
-          if (CG == 2) umma_commit_2sm(&empty[s]); else umma_commit(&empty[s]);   // stage reusable once read
+          __syncwarp();
           if (++s == p.nstage) { s = 0; ph ^= 1; }
         }
-        if (CG == 2) umma_commit_2sm(&acc_full[as]); else umma_commit(&acc_full[as]);   // accumulator tile complete
+        if (elect_one()) {
+          if (CG == 2) umma_commit_2sm(&acc_full[as]); else umma_commit(&acc_full[as]);   // accumulator tile complete
+        }
+        __syncwarp();
       }
     }
   } else if (warp >= 4) {
