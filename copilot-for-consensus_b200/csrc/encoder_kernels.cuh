@@ -169,8 +169,8 @@ B200_DEVINL void gemm_epi_tile(const CUtensorMap& map_out, const CUtensorMap& ma
                                uint8_t* stg, float* sbias, uint64_t* rbar, uint8_t* my_row, int sw, int lane, uint32_t tacc,
                                uint64_t* acc_full_bar, uint32_t aph, uint64_t* acc_empty_bar, uint32_t it) {
   __syncwarp();
-  sbias[lane] = __ldg(bias + n0 + lane);
-  sbias[lane + 32] = __ldg(bias + n0 + 32 + lane);
+  sts32(smem_u32(sbias) + lane * 4, __float_as_uint(__ldg(bias + n0 + lane)));
+  sts32(smem_u32(sbias) + (lane + 32) * 4, __float_as_uint(__ldg(bias + n0 + 32 + lane)));
   if (lane == 0) {
     tma_store_wait_read();   // the previous tile's store has finished reading this warp's box
     if (EPI == EPI_BIAS_RESID) {
@@ -194,22 +194,22 @@ B200_DEVINL void gemm_epi_tile(const CUtensorMap& map_out, const CUtensorMap& ma
   const unsigned long long dbg = g_gemm_timing[7];
   if (dbg == 1) return;   // experiment: accumulators drained, nothing computed or stored
 #endif
+  const uint32_t s_bias = smem_u32(sbias), s_row = smem_u32(my_row);   // shared-space accesses (see lds128)
 #pragma unroll
   for (int j = 0; j < 8; ++j) {   // 8 columns = one 16-byte piece of this thread's row
-    const float4 b0 = *reinterpret_cast<const float4*>(sbias + j * 8);
-    const float4 b1 = *reinterpret_cast<const float4*>(sbias + j * 8 + 4);
+    const uint4 b0 = lds128(s_bias + j * 32), b1 = lds128(s_bias + j * 32 + 16);
     float f[8];
-    f[0] = __uint_as_float(v[j * 8 + 0]) + b0.x; f[1] = __uint_as_float(v[j * 8 + 1]) + b0.y;
-    f[2] = __uint_as_float(v[j * 8 + 2]) + b0.z; f[3] = __uint_as_float(v[j * 8 + 3]) + b0.w;
-    f[4] = __uint_as_float(v[j * 8 + 4]) + b1.x; f[5] = __uint_as_float(v[j * 8 + 5]) + b1.y;
-    f[6] = __uint_as_float(v[j * 8 + 6]) + b1.z; f[7] = __uint_as_float(v[j * 8 + 7]) + b1.w;
+    f[0] = __uint_as_float(v[j * 8 + 0]) + __uint_as_float(b0.x); f[1] = __uint_as_float(v[j * 8 + 1]) + __uint_as_float(b0.y);
+    f[2] = __uint_as_float(v[j * 8 + 2]) + __uint_as_float(b0.z); f[3] = __uint_as_float(v[j * 8 + 3]) + __uint_as_float(b0.w);
+    f[4] = __uint_as_float(v[j * 8 + 4]) + __uint_as_float(b1.x); f[5] = __uint_as_float(v[j * 8 + 5]) + __uint_as_float(b1.y);
+    f[6] = __uint_as_float(v[j * 8 + 6]) + __uint_as_float(b1.z); f[7] = __uint_as_float(v[j * 8 + 7]) + __uint_as_float(b1.w);
     if (EPI == EPI_BIAS_GELU) {
 #pragma unroll
       for (int i = 0; i < 8; ++i) f[i] = gelu_erf(f[i]);
     }
-    uint4* slot = reinterpret_cast<uint4*>(my_row + ((j ^ sw) << 4));
+    const uint32_t slot = s_row + ((j ^ sw) << 4);
     if (EPI == EPI_BIAS_RESID) {
-      const uint4 r = *slot;
+      const uint4 r = lds128(slot);
       const __nv_bfloat162* r2 = reinterpret_cast<const __nv_bfloat162*>(&r);
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
@@ -224,7 +224,7 @@ B200_DEVINL void gemm_epi_tile(const CUtensorMap& map_out, const CUtensorMap& ma
     __nv_bfloat162 t3 = __floats2bfloat162_rn(f[6], f[7]);
     o.x = *reinterpret_cast<uint32_t*>(&t0); o.y = *reinterpret_cast<uint32_t*>(&t1);
     o.z = *reinterpret_cast<uint32_t*>(&t2); o.w = *reinterpret_cast<uint32_t*>(&t3);
-    *slot = o;
+    sts128(slot, o);
   }
 #ifdef B200_GEMM_TIMING
   if (dbg == 3) return;      // experiment: no fence, no store
