@@ -299,7 +299,7 @@ def run_b200(a) -> None:
         roofline = {"bound": "tensor", "kernel": "gemm_bf16_kernel (all four linear shapes of the encoder layer)",
                     "achieved": ach, "peak": pk["tf_sustained"], "unit": "TFLOP/s", "frac": ach / pk["tf_sustained"],
                     "peak_source": pk["source"] + " (sustained bf16 GEMM: kernel timed inside a long step)",
-                    "flop_per_launch": g_fl / g_n, "ms_per_launch": g_ms / g_n, "traffic": None}
+                    "flop_per_launch": g_fl / g_n, "ms_per_launch": g_ms / g_n, "traffic": gemm_traffic_per_launch()}
     sim = prof.get("sim_topk")
     search_roof = None
     if sim and sim["ms"] > 0:
@@ -370,6 +370,19 @@ def run_b200(a) -> None:
         }))
     if world > 1:
         dist.destroy_process_group()
+
+
+def gemm_traffic_per_launch():
+    """dram__bytes_read.sum + dram__bytes_write.sum per GEMM launch (mean over the four linear shapes of a
+    layer, weighted like the roofline's flops: one launch each), from the committed `ncu --set full`
+    capture summarised by scripts/summarize_ncu_full.py; None when the capture is not there."""
+    try:
+        with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "traffic.json")) as f:
+            t = json.load(f)["dram_bytes_per_launch"]
+        g = [v for k, v in t.items() if k.startswith("gemm_bf16")]
+        return sum(g) / len(g) if g else None
+    except Exception:  # noqa: BLE001
+        return None
 
 
 def main():
