@@ -296,7 +296,7 @@ def run_b200(a) -> None:
     roofline = None
     if g_ms > 0:
         ach = g_fl / (g_ms * 1e9)
-        roofline = {"bound": "tensor", "kernel": "gemm_bf16_kernel (all four linear shapes of the encoder layer)",
+        roofline = {"bound": "tensor", "kernel": "gemm_bf16_ast_kernel / gemm_ln_kernel (all four linear shapes of the encoder layer)",
                     "achieved": ach, "peak": pk["tf_sustained"], "unit": "TFLOP/s", "frac": ach / pk["tf_sustained"],
                     "peak_source": pk["source"] + " (sustained bf16 GEMM: kernel timed inside a long step)",
                     "flop_per_launch": g_fl / g_n, "ms_per_launch": g_ms / g_n, "traffic": gemm_traffic_per_launch()}
@@ -310,8 +310,9 @@ def run_b200(a) -> None:
                        "tflops": tf, "frac_tensor": tf / pk["tf_sustained"], "gbs": gbs, "frac_hbm": gbs / pk["hbm_gbs"],
                        "bound": "tensor" if q_per_pass > 212 else "hbm"}
 
-    # launches of OUR kernels per step: embed+LN, 6 x (4 GEMM + attention + 2 LN), pool, prep_queries, sim, merge
-    launches_step = 1 + 6 * 7 + 1 + 3 + (1 if world > 1 else 0)
+    # launches of OUR kernels per step: embed+LN, 6 x (4 GEMM + attention; the two LayerNorms are fused into the
+    # out-proj / FFN2 GEMMs for hidden 384), pool, prep_queries, sim, merge
+    launches_step = 1 + 6 * 5 + 1 + 3 + (1 if world > 1 else 0)
     gpu_launches = launches_step * a.steps
 
     # --- extra: BASELINE.json configs[2] shape at one GPU, search only (4096 queries x 10M rows bf16) ---

@@ -164,6 +164,42 @@ static int launch_gemm_ast(const b200_encoder* e, const GemmIO& io, GemmParams p
   return B200_OK;
 }
 
+// GEMM + bias + residual + LayerNorm (gemm_ln_kernel): N == 384, whole 256-row blocks.  `io.out` is the
+// store map of the normalised output (it may be the residual's own tensor: updated in place).
+static int launch_gemm_ln(const b200_encoder* e, const GemmIO& io, GemmParams p, cudaStream_t st) {
+  constexpr int BLOCK_N = 192;
+  constexpr int NEPI = gemm_epi_warps(BLOCK_N);
+  const size_t stage = (size_t)GEMM_A_STAGE_BYTES + (size_t)(BLOCK_N / 2) * GEMM_BLOCK_K * 2;
+  const size_t max_smem = 232448;
+  // staging boxes, barriers (2*nstage + 4 + NEPI, at most 8 stages), TMEM slot, bias/gamma/beta, row statistics
+  const size_t tail = (size_t)NEPI * GEMM_STAGING_BYTES + 8 * (2 * 8 + 4 + NEPI) + 16 + 3 * 2 * BLOCK_N * 4 +
+                      2 * (BLOCK_N / GEMM_OUT_CHUNK) * 128 * 8;
+  const int nstage = (int)std::min<size_t>(8, (max_smem - 1024 - tail) / stage);
+  if (nstage < 2) B200_FAIL(B200_ERR_UNSUPPORTED, "fused GEMM + LayerNorm tile does not fit in shared memory");
+  p.nstage = nstage;
+  const size_t smem = 1024 + (size_t)nstage * stage + tail;
+  auto kern = gemm_ln_kernel<BLOCK_N>;
+  B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  const int m_blocks = p.M / (2 * GEMM_BLOCK_M);
+  const int grid = std::min(m_blocks, e->num_sms / 2) * 2;
+  {
+    B200_PROF("gemm_bias_resid_ln", 2.0 * p.M * (double)p.N * p.K,
+              2.0 * ((double)p.M * p.K + (double)p.N * p.K + (double)p.M * p.N * 2), st);
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(gemm_threads(BLOCK_N));
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    B200_CUDA(cudaLaunchKernelEx(&cfg, kern, *io.a, *io.w2, *io.out, *io.resid, p));
+  }
+  B200_CUDA(cudaGetLastError());
+  return B200_OK;
+}
+
 template <int EPI>
 static int launch_gemm(const b200_encoder* e, const GemmIO& io, const GemmParams& p, cudaStream_t st) {
   // CTA pairs need whole 256-row tiles; B200_GEMM_CG=1 forces single-CTA tiles (A/B timing)
@@ -257,6 +293,10 @@ static int run_encoder(b200_encoder* e, const int32_t* d_ids, const int32_t* d_l
     B200_CUDA(cudaFuncSetAttribute(attention_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)att_tc_smem));
   }
 
+  // hidden 384 = two 192-column tiles: residual + LayerNorm fused into the producing GEMM (B200_FUSE_LN=0 disables)
+  const char* fuse_env = getenv("B200_FUSE_LN");
+  const char* cg_env2 = getenv("B200_GEMM_CG");
+  const bool fuse_ln = H == 384 && M % 256 == 0 && !(fuse_env && atoi(fuse_env) == 0) && !(cg_env2 && atoi(cg_env2) == 1);
   for (int l = 0; l < e->cfg.layers; ++l) {
     LayerWeights* L = e->layers[l];
     GemmParams p{};
@@ -282,18 +322,28 @@ static int run_encoder(b200_encoder* e, const int32_t* d_ids, const int32_t* d_l
     B200_CUDA(cudaGetLastError());
     // y = ctx Wo^T + bo + x ; x = LN(y)
     p.N = H; p.K = H; p.bias = L->bo.as<float>();
-    B200_TRY(launch_gemm<EPI_BIAS_RESID>(e, GemmIO{&e->map_ctx, &L->map_wo, &L->map_wo_h, &e->map_y_st, &e->map_x_res}, p, st));
-    layernorm_kernel<NV><<<(n_tok + wpb - 1) / wpb, wpb * 32, 0, st>>>(y, n_tok, L->ln1_g.as<float>(), L->ln1_b.as<float>(),
-                                                                      e->cfg.ln_eps, x);
-    B200_CUDA(cudaGetLastError());
+    if (fuse_ln) {
+      p.gamma = L->ln1_g.as<float>(); p.beta = L->ln1_b.as<float>(); p.eps = e->cfg.ln_eps;
+      B200_TRY(launch_gemm_ln(e, GemmIO{&e->map_ctx, &L->map_wo, &L->map_wo_h, &e->map_x_res, &e->map_x_res}, p, st));
+    } else {
+      B200_TRY(launch_gemm<EPI_BIAS_RESID>(e, GemmIO{&e->map_ctx, &L->map_wo, &L->map_wo_h, &e->map_y_st, &e->map_x_res}, p, st));
+      layernorm_kernel<NV><<<(n_tok + wpb - 1) / wpb, wpb * 32, 0, st>>>(y, n_tok, L->ln1_g.as<float>(), L->ln1_b.as<float>(),
+                                                                        e->cfg.ln_eps, x);
+      B200_CUDA(cudaGetLastError());
+    }
     // ffn = gelu(x W1^T + b1) ; y = ffn W2^T + b2 + x ; x = LN(y)
     p.N = I; p.K = H; p.bias = L->b1.as<float>();
     B200_TRY(launch_gemm<EPI_BIAS_GELU>(e, GemmIO{&e->map_x, &L->map_w1, &L->map_w1_h, &e->map_ffn_st, &e->map_ffn_st}, p, st));
     p.N = H; p.K = I; p.bias = L->b2.as<float>();
-    B200_TRY(launch_gemm<EPI_BIAS_RESID>(e, GemmIO{&e->map_ffn, &L->map_w2, &L->map_w2_h, &e->map_y_st, &e->map_x_res}, p, st));
-    layernorm_kernel<NV><<<(n_tok + wpb - 1) / wpb, wpb * 32, 0, st>>>(y, n_tok, L->ln2_g.as<float>(), L->ln2_b.as<float>(),
-                                                                      e->cfg.ln_eps, x);
-    B200_CUDA(cudaGetLastError());
+    if (fuse_ln) {
+      p.gamma = L->ln2_g.as<float>(); p.beta = L->ln2_b.as<float>(); p.eps = e->cfg.ln_eps;
+      B200_TRY(launch_gemm_ln(e, GemmIO{&e->map_ffn, &L->map_w2, &L->map_w2_h, &e->map_x_res, &e->map_x_res}, p, st));
+    } else {
+      B200_TRY(launch_gemm<EPI_BIAS_RESID>(e, GemmIO{&e->map_ffn, &L->map_w2, &L->map_w2_h, &e->map_y_st, &e->map_x_res}, p, st));
+      layernorm_kernel<NV><<<(n_tok + wpb - 1) / wpb, wpb * 32, 0, st>>>(y, n_tok, L->ln2_g.as<float>(), L->ln2_b.as<float>(),
+                                                                        e->cfg.ln_eps, x);
+      B200_CUDA(cudaGetLastError());
+    }
   }
   pool_normalize_kernel<<<batch, 256, 0, st>>>(x, d_lens, seq, H, d_out);
   B200_CUDA(cudaGetLastError());

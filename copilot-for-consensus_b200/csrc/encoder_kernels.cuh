@@ -138,6 +138,9 @@ struct GemmParams {
   int M, N, K;         // M multiple of 128, N multiple of BLOCK_N, K multiple of 64
   int nstage;
   const float* bias;   // [N]
+  const float* gamma;  // [N]  LayerNorm weight (gemm_ln_kernel only)
+  const float* beta;   // [N]  LayerNorm bias   (gemm_ln_kernel only)
+  float eps;
 };
 
 // GELU(x) = x * Phi(x) (the exact-erf form BERT uses).  Phi is evaluated as
@@ -616,6 +619,265 @@ gemm_bf16_ast_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
 
   tc_fence_before();
   cluster_sync_all();                          // no CTA leaves while its peer may still signal its barriers
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc_2sm(tmem_base, TMEM_COLS);
+  }
+}
+
+// GEMM + bias + residual + LayerNorm in one kernel, for N == 2 * BLOCK_N (hidden 384: out-proj and FFN2 of
+// the MiniLM layer), CTA pairs.  The two TMEM accumulator stages hold the two column tiles of the SAME
+// 256-row block, so after the second tile's MMAs a CTA has whole rows on chip:
+//   pass 1  (per column tile, as soon as its MMAs are done -- the first overlaps the second tile's MMAs)
+//           y = acc + bias + residual, written back to TMEM as fp32; per-row sum and sum of squares
+//   stats   the three chunk warps of a TMEM lane group exchange their partials through shared memory
+//   pass 2  y re-read from TMEM, the accumulator stage handed back, (y - mean) * rstd * gamma + beta -> bf16
+//           -> swizzled staging box -> TMA store
+// The separate LayerNorm kernel (read + write of the hidden state, 37 us per call at M = 131072) and the bf16
+// round trip of y disappear; statistics are taken on the fp32 values.  Output rows may alias the residual
+// rows (x is updated in place): a pair reads all residual tiles of its row block before it stores any.
+template <int BLOCK_N>
+__global__ void __launch_bounds__(gemm_threads(BLOCK_N), 1)
+gemm_ln_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
+               const __grid_constant__ CUtensorMap map_out, const __grid_constant__ CUtensorMap map_resid,
+               const GemmParams p) {
+  constexpr int CG = 2;
+  constexpr int N_TOTAL = 2 * BLOCK_N;
+  constexpr uint32_t B_ROWS = BLOCK_N / CG;
+  constexpr uint32_t B_STAGE_BYTES = B_ROWS * GEMM_BLOCK_K * 2;
+  constexpr uint32_t STAGE_BYTES = GEMM_A_STAGE_BYTES + B_STAGE_BYTES;
+  constexpr uint32_t IDESC = umma_idesc_bf16_f32(GEMM_BLOCK_M * CG, BLOCK_N);
+  constexpr uint32_t TMEM_COLS = 512;
+  constexpr int NEPI = gemm_epi_warps(BLOCK_N);
+  constexpr int NCHUNK = BLOCK_N / GEMM_OUT_CHUNK;       // chunk warps per TMEM lane group
+  static_assert(BLOCK_N == 192, "written for 192-column tiles (two accumulator stages in 512 TMEM columns)");
+  static_assert(STAGE_BYTES % 1024 == 0, "stages must keep the 1024-byte swizzle alignment");
+
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* staging = smem + (size_t)p.nstage * STAGE_BYTES;                 // [NEPI][4 KB], 1024-aligned
+  uint64_t* bars = reinterpret_cast<uint64_t*>(staging + (size_t)NEPI * GEMM_STAGING_BYTES);
+  uint64_t* full = bars;                       // [nstage]  TMA -> MMA          (leader's copy is the one used)
+  uint64_t* empty = bars + p.nstage;           // [nstage]  MMA -> TMA          (one per CTA)
+  uint64_t* acc_full = bars + 2 * p.nstage;    // [2]       MMA -> epilogue     (one per CTA)
+  uint64_t* acc_empty = acc_full + 2;          // [2]       epilogue -> MMA     (leader's copy is the one used)
+  uint64_t* resid_bar = acc_empty + 2;         // [NEPI]    residual box landed (one per epilogue warp)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(resid_bar + NEPI);
+  float* vecs = reinterpret_cast<float*>(tmem_slot + 4);                    // bias, gamma, beta: [3][N_TOTAL]
+  float* xs = vecs + 3 * N_TOTAL;                                           // [2 parities][NCHUNK][128] {sum, sumsq}
+
+  const int warp = uniform_warp_idx();
+  const int lane = threadIdx.x & 31;
+  const int rank = (int)cluster_ctarank();
+  const bool leader = rank == 0;
+  const int m_blocks = p.M / (GEMM_BLOCK_M * CG);
+  const int group = blockIdx.x / CG, n_groups = gridDim.x / CG;
+  const int num_k = p.K / GEMM_BLOCK_K;
+
+  for (int i = threadIdx.x; i < N_TOTAL; i += blockDim.x) {
+    vecs[i] = __ldg(p.bias + i);
+    vecs[N_TOTAL + i] = __ldg(p.gamma + i);
+    vecs[2 * N_TOTAL + i] = __ldg(p.beta + i);
+  }
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&map_a);
+    tma_prefetch_desc(&map_b);
+    tma_prefetch_desc(&map_out);
+    tma_prefetch_desc(&map_resid);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < p.nstage; ++i) {
+      mbar_init(&full[i], CG);
+      mbar_init(&empty[i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&acc_full[i], 1);
+      mbar_init(&acc_empty[i], NEPI * CG);
+    }
+    for (int i = 0; i < NEPI; ++i) mbar_init(&resid_bar[i], 1);
+    fence_mbar_init();
+  }
+  if (warp == 2) tmem_alloc_2sm(tmem_slot, TMEM_COLS);
+  tc_fence_before();
+  cluster_sync_all();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===== TMA producer (converged loop, one elected lane issues) =====
+    int s = 0;
+    uint32_t ph = 0;
+    for (int mb = group; mb < m_blocks; mb += n_groups) {
+      const int m0 = mb * (GEMM_BLOCK_M * CG) + rank * GEMM_BLOCK_M;
+      for (int nt = 0; nt < 2; ++nt) {
+        const int n0 = nt * BLOCK_N + rank * (int)B_ROWS;
+        for (int kb = 0; kb < num_k; ++kb) {
+          mbar_wait(&empty[s], ph ^ 1);
+          uint8_t* sa = smem + (size_t)s * STAGE_BYTES;
+          if (elect_one()) {
+            if (leader) mbar_arrive_expect_tx(&full[s], STAGE_BYTES * CG);
+            else mbar_arrive_leader(&full[s]);
+            tma_load_2d_2sm(sa, &map_a, &full[s], kb * GEMM_BLOCK_K, m0);
+            tma_load_2d_2sm(sa + GEMM_A_STAGE_BYTES, &map_b, &full[s], kb * GEMM_BLOCK_K, n0);
+          }
+          __syncwarp();
+          if (++s == p.nstage) { s = 0; ph ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer (leader CTA; converged loop, one elected lane issues): tile nt -> accumulator stage nt =====
+    if (leader) {
+      int s = 0;
+      uint32_t ph = 0, mbi = 0;
+      const uint32_t smem_addr = smem_u32(smem);
+      for (int mb = group; mb < m_blocks; mb += n_groups, ++mbi) {
+        for (int nt = 0; nt < 2; ++nt) {
+          mbar_wait(&acc_empty[nt], (mbi & 1) ^ 1);
+          tc_fence_after();
+          const uint32_t tacc = tmem_base + nt * BLOCK_N;
+          for (int kb = 0; kb < num_k; ++kb) {
+            mbar_wait(&full[s], ph);
+            tc_fence_after();
+            const uint32_t a_addr = smem_addr + (uint32_t)s * STAGE_BYTES;
+            const uint64_t da = umma_smem_desc_sw128(a_addr);
+            const uint64_t db = umma_smem_desc_sw128(a_addr + GEMM_A_STAGE_BYTES);
+            if (elect_one()) {
+#pragma unroll
+              for (int k = 0; k < GEMM_BLOCK_K / 16; ++k)
+                umma_bf16_2sm(tacc, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), IDESC, (uint32_t)((kb | k) != 0));
+              umma_commit_2sm(&empty[s]);
+            }
+            __syncwarp();
+            if (++s == p.nstage) { s = 0; ph ^= 1; }
+          }
+          if (elect_one()) umma_commit_2sm(&acc_full[nt]);
+          __syncwarp();
+        }
+      }
+    }
+  } else if (warp >= 4) {
+    // ===== epilogue warp: TMEM lanes [32 wq, +32) x columns [64 chunk, +64) of BOTH column tiles =====
+    const int e = warp - 4;
+    const int wq = e & 3;
+    const int chunk = e >> 2;
+    uint8_t* stg = staging + (size_t)e * GEMM_STAGING_BYTES;
+    uint64_t* rbar = &resid_bar[e];
+    const uint32_t s_row = smem_u32(stg) + lane * 128;
+    const uint32_t s_vecs = smem_u32(vecs), s_xs = smem_u32(xs);
+    const int sw = lane & 7;       // 128-byte swizzle: 16-byte chunk j of row r lives at chunk j ^ (r % 8)
+    const int row = wq * 32 + lane;
+    const uint32_t tlane = tmem_base + ((uint32_t)(wq * 32) << 16) + chunk * GEMM_OUT_CHUNK;
+    const float inv_n = 1.0f / (float)N_TOTAL;
+    uint32_t mbi = 0, rcount = 0;
+    for (int mb = group; mb < m_blocks; mb += n_groups, ++mbi) {
+      const int m0 = mb * (GEMM_BLOCK_M * CG) + rank * GEMM_BLOCK_M + wq * 32;
+      float sum = 0.f, sumsq = 0.f;
+      // ---- pass 1: y = acc + bias + residual back into TMEM, row statistics ----
+#pragma unroll 1
+      for (int nt = 0; nt < 2; ++nt, ++rcount) {
+        const int n0 = nt * BLOCK_N + chunk * GEMM_OUT_CHUNK;
+        __syncwarp();                          // every lane is done reading the box (previous residual tile)
+        if (lane == 0) {
+          tma_store_wait_read();               // the box is no longer being read by an earlier store
+          mbar_arrive_expect_tx(rbar, GEMM_STAGING_BYTES);
+          tma_load_2d(stg, &map_resid, rbar, n0, m0);
+        }
+        __syncwarp();
+        mbar_wait(&acc_full[nt], mbi & 1);
+        tc_fence_after();
+        uint32_t v[64];
+        tmem_ld64(tlane + nt * BLOCK_N, v);
+        tmem_ld_wait();
+        mbar_wait(rbar, rcount & 1);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const uint4 b0 = lds128(s_vecs + (n0 + j * 8) * 4), b1 = lds128(s_vecs + (n0 + j * 8 + 4) * 4);
+          const uint4 r = lds128(s_row + ((j ^ sw) << 4));
+          const __nv_bfloat162* r2 = reinterpret_cast<const __nv_bfloat162*>(&r);
+          const float bb[8] = {__uint_as_float(b0.x), __uint_as_float(b0.y), __uint_as_float(b0.z), __uint_as_float(b0.w),
+                               __uint_as_float(b1.x), __uint_as_float(b1.y), __uint_as_float(b1.z), __uint_as_float(b1.w)};
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const float y0 = __uint_as_float(v[j * 8 + 2 * i]) + bb[2 * i] + __low2float(r2[i]);
+            const float y1 = __uint_as_float(v[j * 8 + 2 * i + 1]) + bb[2 * i + 1] + __high2float(r2[i]);
+            sum += y0 + y1;
+            sumsq = fmaf(y0, y0, sumsq);
+            sumsq = fmaf(y1, y1, sumsq);
+            v[j * 8 + 2 * i] = __float_as_uint(y0);
+            v[j * 8 + 2 * i + 1] = __float_as_uint(y1);
+          }
+        }
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          uint32_t w[16];
+#pragma unroll
+          for (int i = 0; i < 16; ++i) w[i] = v[q * 16 + i];
+          tmem_st16(tlane + nt * BLOCK_N + q * 16, w);
+        }
+      }
+      tmem_st_wait();
+      // ---- row statistics across the chunk warps of this lane group ----
+      const uint32_t xs_par = s_xs + (mbi & 1) * (NCHUNK * 128 * 8);
+      sts32(xs_par + (chunk * 128 + row) * 8, __float_as_uint(sum));
+      sts32(xs_par + (chunk * 128 + row) * 8 + 4, __float_as_uint(sumsq));
+      named_bar_sync(1 + wq, NCHUNK * 32);
+      float tot = 0.f, totsq = 0.f;
+#pragma unroll
+      for (int c = 0; c < NCHUNK; ++c) {
+        tot += __uint_as_float(lds32(xs_par + (c * 128 + row) * 8));
+        totsq += __uint_as_float(lds32(xs_par + (c * 128 + row) * 8 + 4));
+      }
+      const float mean = tot * inv_n;
+      const float rstd = rsqrtf(fmaxf(totsq * inv_n - mean * mean, 0.f) + p.eps);
+      const float shift = -mean * rstd;
+      // ---- pass 2: normalise, affine, bf16, TMA store ----
+#pragma unroll 1
+      for (int nt = 0; nt < 2; ++nt) {
+        const int n0 = nt * BLOCK_N + chunk * GEMM_OUT_CHUNK;
+        uint32_t v[64];
+        tmem_ld64(tlane + nt * BLOCK_N, v);
+        tmem_ld_wait();
+        tc_fence_before();         // this warp's share of the accumulator stage is in registers
+        __syncwarp();
+        if (lane == 0) {
+          mbar_arrive_leader(&acc_empty[nt]);
+          tma_store_wait_read();   // the previous store has finished reading this warp's box
+        }
+        __syncwarp();
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const uint4 g0 = lds128(s_vecs + (N_TOTAL + n0 + j * 8) * 4), g1 = lds128(s_vecs + (N_TOTAL + n0 + j * 8 + 4) * 4);
+          const uint4 e0 = lds128(s_vecs + (2 * N_TOTAL + n0 + j * 8) * 4), e1 = lds128(s_vecs + (2 * N_TOTAL + n0 + j * 8 + 4) * 4);
+          const float gg[8] = {__uint_as_float(g0.x), __uint_as_float(g0.y), __uint_as_float(g0.z), __uint_as_float(g0.w),
+                               __uint_as_float(g1.x), __uint_as_float(g1.y), __uint_as_float(g1.z), __uint_as_float(g1.w)};
+          const float ee[8] = {__uint_as_float(e0.x), __uint_as_float(e0.y), __uint_as_float(e0.z), __uint_as_float(e0.w),
+                               __uint_as_float(e1.x), __uint_as_float(e1.y), __uint_as_float(e1.z), __uint_as_float(e1.w)};
+          float f[8];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) f[i] = fmaf(fmaf(__uint_as_float(v[j * 8 + i]), rstd, shift), gg[i], ee[i]);
+          uint4 o;
+          __nv_bfloat162 t0 = __floats2bfloat162_rn(f[0], f[1]);
+          __nv_bfloat162 t1 = __floats2bfloat162_rn(f[2], f[3]);
+          __nv_bfloat162 t2 = __floats2bfloat162_rn(f[4], f[5]);
+          __nv_bfloat162 t3 = __floats2bfloat162_rn(f[6], f[7]);
+          o.x = *reinterpret_cast<uint32_t*>(&t0); o.y = *reinterpret_cast<uint32_t*>(&t1);
+          o.z = *reinterpret_cast<uint32_t*>(&t2); o.w = *reinterpret_cast<uint32_t*>(&t3);
+          sts128(s_row + ((j ^ sw) << 4), o);
+        }
+        fence_proxy_async();       // generic-proxy writes -> visible to the TMA (async proxy)
+        __syncwarp();
+        if (lane == 0) {
+          tma_store_2d(&map_out, stg, n0, m0);
+          tma_store_commit();
+        }
+      }
+    }
+    if (lane == 0) tma_store_wait_all();
+  }
+
+  tc_fence_before();
+  cluster_sync_all();
   if (warp == 2) {
     tc_fence_after();
     tmem_dealloc_2sm(tmem_base, TMEM_COLS);
