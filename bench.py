@@ -339,6 +339,26 @@ def run_b200(a) -> None:
             big.close()
         except Exception as exc:  # noqa: BLE001 - the extra block must never sink the headline line
             extra = {"error": str(exc)[:200]}
+        # BASELINE.json configs[3] architecture at one GPU: 768-d, 12 layers, 12 heads x 64, seq 384
+        try:
+            with tempfile.TemporaryDirectory() as td:
+                mio.write_random_model(td, "all-mpnet-base-v2", seed=0)
+                big_prov = prov_mod.B200SentenceTransformerProvider(model_name=td, device=f"cuda:{local}")
+            bb, ss = 128, 384
+            ids_b = torch.randint(1000, 30522, (bb, ss), generator=g, device=dev, dtype=torch.int32)
+            lens_b = torch.full((bb,), ss, device=dev, dtype=torch.int32)
+            f = lambda: big_prov.embed_tokens(ids_b, lens_b)
+            ms, _ = timed(f, 5, 3)
+            ms /= 5
+            gflop_chunk = 70.67           # 768-d, 12 layers, seq 384
+            extra = extra or {}
+            extra["encode_mpnet_class_b128_s384"] = {"ms_per_batch": ms, "chunks_per_s": bb / (ms * 1e-3),
+                                                     "tflops_algorithmic": bb * gflop_chunk / ms,
+                                                     "frac_of_sustained_peak": bb * gflop_chunk / ms / pk["tf_sustained"]}
+            big_prov.close()
+        except Exception as exc:  # noqa: BLE001
+            extra = extra or {}
+            extra["encode_mpnet_class_b128_s384"] = {"error": str(exc)[:200]}
 
     cpu = None
     if rank == 0 and world == 1 and not a.no_cpu_baseline:

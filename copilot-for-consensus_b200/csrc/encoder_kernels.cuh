@@ -238,6 +238,9 @@ B200_DEVINL void gemm_epi_tile(const CUtensorMap& map_out, const CUtensorMap& ma
   if (dbg == 2) return;      // experiment: no store
 #endif
   if (lane == 0) {
+#ifdef B200_GEMM_TIMING
+    if (dbg == 4) m0 &= 255;   // experiment: every store lands in the first 256 rows (stays in L2)
+#endif
     tma_store_2d(&map_out, stg, n0, m0);
     tma_store_commit();
   }
@@ -527,10 +530,15 @@ gemm_bf16_ast_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
               __syncwarp();
             }
             mbar_wait(&b_empty[s], ph ^ 1);
+#ifdef B200_GEMM_TIMING
+            const bool skip_b = g_gemm_timing[7] == 5 && (kb & 1);   // experiment: half of the weight loads dropped
+#else
+            const bool skip_b = false;
+#endif
             if (elect_one()) {
-              if (leader) mbar_arrive_expect_tx(&b_full[s], B_STAGE_BYTES * CG);
+              if (leader) mbar_arrive_expect_tx(&b_full[s], skip_b ? 0u : B_STAGE_BYTES * CG);
               else mbar_arrive_leader(&b_full[s]);
-              tma_load_2d_2sm(ring + (size_t)s * B_STAGE_BYTES, &map_b, &b_full[s], kb * GEMM_BLOCK_K, n0);
+              if (!skip_b) tma_load_2d_2sm(ring + (size_t)s * B_STAGE_BYTES, &map_b, &b_full[s], kb * GEMM_BLOCK_K, n0);
             }
             __syncwarp();
             if (++s == p.nstage) { s = 0; ph ^= 1; }
