@@ -294,6 +294,8 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_cons
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   const uint32_t kv_bytes = (uint32_t)S * ATT_DH * 2, q_bytes = (uint32_t)q_rows * ATT_DH * 2;
+  pdl_wait();                                  // the QKV projection has finished
+  pdl_launch_dependents();
 
   if (warp == W_TMA) {
     // ===== TMA producer: the warp runs the loop converged, one elected lane issues (see uniform_warp_idx) =====

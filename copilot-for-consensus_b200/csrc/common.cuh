@@ -178,6 +178,16 @@ B200_DEVINL void tmem_ld1(uint32_t taddr, uint32_t& r) {
 // elect / broadcast / branch sequence of ~20 instructions.
 B200_DEVINL int uniform_warp_idx() { return __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0); }
 
+// Programmatic dependent launch.  A kernel launched with cudaLaunchAttributeProgrammaticStreamSerialization may
+// become resident while its predecessor in the stream is still running (its CTAs take the SMs the
+// predecessor's CTAs leave): barrier initialisation, TMEM allocation and descriptor prefetch then overlap the
+// predecessor's tail.  pdl_wait() blocks until the predecessor grid has completed and its writes are
+// visible -- nothing it produced may be read, and nothing it reads may be written, before this point;
+// pdl_launch_dependents() lets the NEXT kernel in the stream start arriving.  Both are no-ops for a
+// kernel launched without the attribute.
+B200_DEVINL void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+B200_DEVINL void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 // Explicit shared-space accesses by 32-bit shared address.  Pointers into the dynamic shared array that
 // went through integer alignment arithmetic compile to GENERIC loads/stores with 64-bit address math;
 // these keep hot paths on LDS/STS.

@@ -89,6 +89,26 @@ struct GemmIO {
   const CUtensorMap* resid;  // residual [M, N], box {64, 32} (TMA load) or the same as out when unused
 };
 
+// Launch attributes of the hot-path kernels: cluster of two (CTA pairs) and, with B200_PDL=1, programmatic
+// stream serialisation (see pdl_wait in common.cuh).  Off by default: measured +0.3 % on the 512 x 256
+// batch (3.975 -> 3.960 ms per step) -- the kernels are long and persistent, so their boundaries cost
+// little -- which is not worth relaxing the stream order for.  Returns the attribute count.
+static int hot_launch_attrs(cudaLaunchAttribute* attr, bool pair) {
+  int n = 0;
+  if (pair) {
+    attr[n].id = cudaLaunchAttributeClusterDimension;
+    attr[n].val.clusterDim.x = 2; attr[n].val.clusterDim.y = 1; attr[n].val.clusterDim.z = 1;
+    ++n;
+  }
+  static const bool pdl = [] { const char* v = getenv("B200_PDL"); return v && atoi(v) != 0; }();
+  if (pdl && !prof_enabled()) {     // per-kernel timing records events between launches: keep those runs serial
+    attr[n].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[n].val.programmaticStreamSerializationAllowed = 1;
+    ++n;
+  }
+  return n;
+}
+
 template <int BLOCK_N, int EPI, int CG>
 static int launch_gemm_t(const b200_encoder* e, const GemmIO& io, GemmParams p, cudaStream_t st) {
   constexpr int NEPI = gemm_epi_warps(BLOCK_N);
@@ -116,10 +136,8 @@ static int launch_gemm_t(const b200_encoder* e, const GemmIO& io, GemmParams p, 
       cfg.blockDim = dim3(gemm_threads(BLOCK_N));
       cfg.dynamicSmemBytes = smem;
       cfg.stream = st;
-      cudaLaunchAttribute attr[1];
-      attr[0].id = cudaLaunchAttributeClusterDimension;
-      attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
-      cfg.attrs = attr; cfg.numAttrs = 1;
+      cudaLaunchAttribute attr[2];
+      cfg.attrs = attr; cfg.numAttrs = hot_launch_attrs(attr, true);
       B200_CUDA(cudaLaunchKernelEx(&cfg, kern, *io.a, *io.w2, *io.out, *io.resid, p));
     }
   }
@@ -154,10 +172,8 @@ static int launch_gemm_ast(const b200_encoder* e, const GemmIO& io, GemmParams p
     cfg.blockDim = dim3(gemm_threads(BLOCK_N));
     cfg.dynamicSmemBytes = smem;
     cfg.stream = st;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
-    cfg.attrs = attr; cfg.numAttrs = 1;
+    cudaLaunchAttribute attr[2];
+    cfg.attrs = attr; cfg.numAttrs = hot_launch_attrs(attr, true);
     B200_CUDA(cudaLaunchKernelEx(&cfg, kern, *io.a, *io.w2, *io.out, *io.resid, p));
   }
   B200_CUDA(cudaGetLastError());
@@ -190,10 +206,8 @@ static int launch_gemm_ln(const b200_encoder* e, const GemmIO& io, GemmParams p,
     cfg.blockDim = dim3(gemm_threads(BLOCK_N));
     cfg.dynamicSmemBytes = smem;
     cfg.stream = st;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
-    cfg.attrs = attr; cfg.numAttrs = 1;
+    cudaLaunchAttribute attr[2];
+    cfg.attrs = attr; cfg.numAttrs = hot_launch_attrs(attr, true);
     B200_CUDA(cudaLaunchKernelEx(&cfg, kern, *io.a, *io.w2, *io.out, *io.resid, p));
   }
   B200_CUDA(cudaGetLastError());
@@ -309,7 +323,14 @@ static int run_encoder(b200_encoder* e, const int32_t* d_ids, const int32_t* d_l
       ap.lens = d_lens; ap.exact_max = att_exact_max;
       ap.no_turns = getenv("B200_ATT_NO_TURNS") && atoi(getenv("B200_ATT_NO_TURNS")) != 0;
       B200_PROF("attention", 4.0 * batch * (double)seq * seq * H, 2.0 * 4.0 * n_tok * H, st);
-      attention_tc_kernel<<<std::min(ap.n_units, e->num_sms), ATT_THREADS, att_tc_smem, st>>>(map_att_q, map_att_kv, map_att_out, ap);
+      cudaLaunchConfig_t cfg{};
+      cfg.gridDim = dim3(std::min(ap.n_units, e->num_sms));
+      cfg.blockDim = dim3(ATT_THREADS);
+      cfg.dynamicSmemBytes = att_tc_smem;
+      cfg.stream = st;
+      cudaLaunchAttribute attr[2];
+      cfg.attrs = attr; cfg.numAttrs = hot_launch_attrs(attr, false);
+      B200_CUDA(cudaLaunchKernelEx(&cfg, attention_tc_kernel, map_att_q, map_att_kv, map_att_out, ap));
     } else {
       B200_PROF("attention", 4.0 * batch * (double)seq * seq * H, 2.0 * 4.0 * n_tok * H, st);
       if (dh == 32)

@@ -314,6 +314,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
   else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();                                  // the producer of A / the residual has finished
+  pdl_launch_dependents();
 
   if (warp == 0) {
     // ===== TMA producer (every CTA loads its own A rows and its share of the weight tile); the warp runs
@@ -508,6 +510,8 @@ gemm_bf16_ast_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
   cluster_sync_all();                          // the peer's barriers are initialised before anyone signals them
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();                                  // the producer of A has finished
+  pdl_launch_dependents();
 
   if (warp == 0) {
     // ===== TMA producer: this CTA's 128 rows of A once per row block, its half of every weight tile; the
@@ -710,6 +714,8 @@ gemm_ln_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
   cluster_sync_all();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();                                  // the producers of A and of the residual have finished
+  pdl_launch_dependents();
 
   if (warp == 0) {
     // ===== TMA producer (converged loop, one elected lane issues) =====
