@@ -64,6 +64,7 @@ struct AttParams {
   int n_units;      // batch * heads * n_mt
   const int32_t* lens;
   int exact_max;    // 1: always take the exact row-maximum pass (B200_ATT_EXACT_MAX=1), for A/B checks
+  int reverse;      // 1: walk the units from the last to the first (see GemmParams::reverse)
   int no_turns;     // 1: the groups do not take turns in the exponential pass (B200_ATT_NO_TURNS=1), for A/B timing
 };
 
@@ -302,7 +303,8 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_cons
     {
       uint32_t it = 0;
       for (int u = blockIdx.x; u < p.n_units; u += gridDim.x, ++it) {
-        const int st = it % ATT_STAGES, item = u / p.n_mt, mt = u - item * p.n_mt;
+        const int ur = p.reverse ? p.n_units - 1 - u : u;
+        const int st = it % ATT_STAGES, item = ur / p.n_mt, mt = ur - item * p.n_mt;
         const int b = item / p.heads, h = item - b * p.heads;
         const int len = p.lens[b];
         mbar_wait(&kv_empty[st], ((it / ATT_STAGES) & 1) ^ 1);

@@ -311,16 +311,21 @@ static int run_encoder(b200_encoder* e, const int32_t* d_ids, const int32_t* d_l
   const char* fuse_env = getenv("B200_FUSE_LN");
   const char* cg_env2 = getenv("B200_GEMM_CG");
   const bool fuse_ln = H == 384 && M % 256 == 0 && !(fuse_env && atoi(fuse_env) == 0) && !(cg_env2 && atoi(cg_env2) == 1);
+  // serpentine row order: every kernel walks the rows in the opposite direction of the one before it
+  // (B200_SERPENTINE=0 disables)
+  const char* serp_env = getenv("B200_SERPENTINE");
+  const bool serp = !(serp_env && atoi(serp_env) == 0);
+  int kcount = 0;
   for (int l = 0; l < e->cfg.layers; ++l) {
     LayerWeights* L = e->layers[l];
     GemmParams p{};
     // Q,K,V projections in one GEMM: qkv = x Wqkv^T + bqkv
-    p.M = M; p.N = 3 * H; p.K = H; p.bias = L->bqkv.as<float>();
+    p.M = M; p.N = 3 * H; p.K = H; p.bias = L->bqkv.as<float>(); p.reverse = serp ? (kcount++ & 1) : 0;
     B200_TRY(launch_gemm<EPI_BIAS>(e, GemmIO{&e->map_x, &L->map_wqkv, &L->map_wqkv_h, &e->map_qkv_st, &e->map_qkv_st}, p, st));
     if (use_att_tc) {
       AttParams ap;
       ap.S = seq; ap.H = H; ap.heads = heads; ap.n_mt = (seq + 127) / 128; ap.n_units = batch * heads * ap.n_mt;
-      ap.lens = d_lens; ap.exact_max = att_exact_max;
+      ap.lens = d_lens; ap.exact_max = att_exact_max; ap.reverse = serp ? (kcount++ & 1) : 0;
       ap.no_turns = getenv("B200_ATT_NO_TURNS") && atoi(getenv("B200_ATT_NO_TURNS")) != 0;
       B200_PROF("attention", 4.0 * batch * (double)seq * seq * H, 2.0 * 4.0 * n_tok * H, st);
       cudaLaunchConfig_t cfg{};
@@ -342,7 +347,7 @@ static int run_encoder(b200_encoder* e, const int32_t* d_ids, const int32_t* d_l
     }
     B200_CUDA(cudaGetLastError());
     // y = ctx Wo^T + bo + x ; x = LN(y)
-    p.N = H; p.K = H; p.bias = L->bo.as<float>();
+    p.N = H; p.K = H; p.bias = L->bo.as<float>(); p.reverse = serp ? (kcount++ & 1) : 0;
     if (fuse_ln) {
       p.gamma = L->ln1_g.as<float>(); p.beta = L->ln1_b.as<float>(); p.eps = e->cfg.ln_eps;
       B200_TRY(launch_gemm_ln(e, GemmIO{&e->map_ctx, &L->map_wo, &L->map_wo_h, &e->map_x_res, &e->map_x_res}, p, st));
@@ -353,9 +358,9 @@ static int run_encoder(b200_encoder* e, const int32_t* d_ids, const int32_t* d_l
       B200_CUDA(cudaGetLastError());
     }
     // ffn = gelu(x W1^T + b1) ; y = ffn W2^T + b2 + x ; x = LN(y)
-    p.N = I; p.K = H; p.bias = L->b1.as<float>();
+    p.N = I; p.K = H; p.bias = L->b1.as<float>(); p.reverse = serp ? (kcount++ & 1) : 0;
     B200_TRY(launch_gemm<EPI_BIAS_GELU>(e, GemmIO{&e->map_x, &L->map_w1, &L->map_w1_h, &e->map_ffn_st, &e->map_ffn_st}, p, st));
-    p.N = H; p.K = I; p.bias = L->b2.as<float>();
+    p.N = H; p.K = I; p.bias = L->b2.as<float>(); p.reverse = serp ? (kcount++ & 1) : 0;
     if (fuse_ln) {
       p.gamma = L->ln2_g.as<float>(); p.beta = L->ln2_b.as<float>(); p.eps = e->cfg.ln_eps;
       B200_TRY(launch_gemm_ln(e, GemmIO{&e->map_ffn, &L->map_w2, &L->map_w2_h, &e->map_x_res, &e->map_x_res}, p, st));

@@ -141,6 +141,9 @@ struct GemmParams {
   const float* gamma;  // [N]  LayerNorm weight (gemm_ln_kernel only)
   const float* beta;   // [N]  LayerNorm bias   (gemm_ln_kernel only)
   float eps;
+  int reverse;         // 1: walk the row blocks from the last to the first.  Consecutive kernels of a layer
+                       // alternate, so each starts with the rows its producer wrote LAST -- the part of a
+                       // 300-400 MB activation that is still in the 126 MB L2.
 };
 
 // GELU(x) = x * Phi(x) (the exact-erf form BERT uses).  Phi is evaluated as
@@ -324,7 +327,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
       int s = 0;
       uint32_t ph = 0;
       for (int tile = group; tile < total_tiles; tile += n_groups) {
-        const int m0 = (tile / n_tiles) * (GEMM_BLOCK_M * CG) + rank * GEMM_BLOCK_M;
+        const int mt = tile / n_tiles, mtr = p.reverse ? total_tiles / n_tiles - 1 - mt : mt;
+        const int m0 = mtr * (GEMM_BLOCK_M * CG) + rank * GEMM_BLOCK_M;
         const int n0 = (tile % n_tiles) * BLOCK_N + rank * (int)B_ROWS;
         for (int kb = 0; kb < num_k; ++kb) {
           mbar_wait(&empty[s], ph ^ 1);
@@ -415,7 +419,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     uint32_t it = 0;
     for (int tile = group; tile < total_tiles; tile += n_groups, ++it) {
       const uint32_t as = it & 1, aph = (it >> 1) & 1;
-      const int m0 = (tile / n_tiles) * (GEMM_BLOCK_M * CG) + rank * GEMM_BLOCK_M + wq * 32;
+      const int mt = tile / n_tiles, mtr = p.reverse ? total_tiles / n_tiles - 1 - mt : mt;
+      const int m0 = mtr * (GEMM_BLOCK_M * CG) + rank * GEMM_BLOCK_M + wq * 32;
       const int n0 = (tile % n_tiles) * BLOCK_N + chunk * GEMM_OUT_CHUNK;
       gemm_epi_tile<EPI, CG>(map_out, map_resid, p.bias, m0, n0, stg, sbias, rbar, my_row, sw, lane,
                              tmem_base + ((uint32_t)(wq * 32) << 16) + as * BLOCK_N + chunk * GEMM_OUT_CHUNK,
@@ -520,7 +525,7 @@ gemm_bf16_ast_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
       int s = 0;
       uint32_t ph = 0, mbi = 0;
       for (int mb = group; mb < m_blocks; mb += n_groups, ++mbi) {
-        const int m0 = mb * (GEMM_BLOCK_M * CG) + rank * GEMM_BLOCK_M;
+        const int m0 = (p.reverse ? m_blocks - 1 - mb : mb) * (GEMM_BLOCK_M * CG) + rank * GEMM_BLOCK_M;
         for (int nt = 0; nt < n_tiles; ++nt) {
           const int n0 = nt * BLOCK_N + rank * (int)B_ROWS;
           for (int kb = 0; kb < num_k; ++kb) {
@@ -619,7 +624,7 @@ gemm_bf16_ast_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
     for (int mb = group; mb < m_blocks; mb += n_groups) {
       for (int nt = 0; nt < n_tiles; ++nt, ++it) {
         const uint32_t as = it & 1, aph = (it >> 1) & 1;
-        const int m0 = mb * (GEMM_BLOCK_M * CG) + rank * GEMM_BLOCK_M + wq * 32;
+        const int m0 = (p.reverse ? m_blocks - 1 - mb : mb) * (GEMM_BLOCK_M * CG) + rank * GEMM_BLOCK_M + wq * 32;
         const int n0 = nt * BLOCK_N + chunk * GEMM_OUT_CHUNK;
         gemm_epi_tile<EPI, CG>(map_out, map_resid, p.bias, m0, n0, stg, sbias, rbar, my_row, sw, lane,
                                tmem_base + ((uint32_t)(wq * 32) << 16) + as * BLOCK_N + chunk * GEMM_OUT_CHUNK,
@@ -722,7 +727,7 @@ gemm_ln_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
     int s = 0;
     uint32_t ph = 0;
     for (int mb = group; mb < m_blocks; mb += n_groups) {
-      const int m0 = mb * (GEMM_BLOCK_M * CG) + rank * GEMM_BLOCK_M;
+      const int m0 = (p.reverse ? m_blocks - 1 - mb : mb) * (GEMM_BLOCK_M * CG) + rank * GEMM_BLOCK_M;
       for (int nt = 0; nt < 2; ++nt) {
         const int n0 = nt * BLOCK_N + rank * (int)B_ROWS;
         for (int kb = 0; kb < num_k; ++kb) {
@@ -785,7 +790,7 @@ gemm_ln_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
     const float inv_n = 1.0f / (float)N_TOTAL;
     uint32_t mbi = 0, rcount = 0;
     for (int mb = group; mb < m_blocks; mb += n_groups, ++mbi) {
-      const int m0 = mb * (GEMM_BLOCK_M * CG) + rank * GEMM_BLOCK_M + wq * 32;
+      const int m0 = (p.reverse ? m_blocks - 1 - mb : mb) * (GEMM_BLOCK_M * CG) + rank * GEMM_BLOCK_M + wq * 32;
       float sum = 0.f, sumsq = 0.f;
       // ---- pass 1: y = acc + bias + residual back into TMEM, row statistics ----
 #pragma unroll 1
