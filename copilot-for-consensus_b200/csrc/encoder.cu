@@ -16,6 +16,7 @@
 #include <vector>
 
 #include "attention_tc.cuh"
+#include "ffn_fused.cuh"
 #include "encoder_kernels.cuh"
 #include "host_util.h"
 
@@ -29,6 +30,7 @@ struct LayerWeights {
   DevBuf ln1_g, ln1_b, ln2_g, ln2_b;    // fp32
   CUtensorMap map_wqkv, map_wo, map_w1, map_w2;           // box rows = BLOCK_N
   CUtensorMap map_wqkv_h, map_wo_h, map_w1_h, map_w2_h;   // box rows = BLOCK_N / 2 (one CTA's share in a CTA pair)
+  CUtensorMap map_w1_f;                                   // box rows = 64: one CTA's share of a 128-column FFN slice (ffn_fused_kernel)
 };
 
 uint16_t f32_to_bf16_host(float f) {
@@ -214,6 +216,33 @@ static int launch_gemm_ln(const b200_encoder* e, const GemmIO& io, GemmParams p,
   return B200_OK;
 }
 
+// The whole feed-forward block of a layer in one kernel (ffn_fused_kernel): hidden 384, whole 256-row blocks.
+static int launch_ffn_fused(const b200_encoder* e, const LayerWeights* L, int M, int I, int reverse, cudaStream_t st) {
+  auto kern = ffn_fused_kernel;
+  B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FFN_SMEM_BYTES));
+  FfnParams p{};
+  p.M = M; p.I = I;
+  p.b1 = L->b1.as<float>(); p.b2 = L->b2.as<float>();
+  p.gamma = L->ln2_g.as<float>(); p.beta = L->ln2_b.as<float>(); p.eps = e->cfg.ln_eps;
+  p.reverse = reverse;
+  const int m_blocks = M / (2 * GEMM_BLOCK_M);
+  const int grid = std::min(m_blocks, e->num_sms / 2) * 2;
+  {
+    const double H = FFN_H;
+    B200_PROF("ffn_fused", 4.0 * M * H * I, 2.0 * (2.0 * M * H + 2.0 * H * I), st);
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(FFN_THREADS);
+    cfg.dynamicSmemBytes = FFN_SMEM_BYTES;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[2];
+    cfg.attrs = attr; cfg.numAttrs = hot_launch_attrs(attr, true);
+    B200_CUDA(cudaLaunchKernelEx(&cfg, kern, e->map_x, L->map_w1_f, L->map_w2_h, e->map_x_res, p));
+  }
+  B200_CUDA(cudaGetLastError());
+  return B200_OK;
+}
+
 template <int EPI>
 static int launch_gemm(const b200_encoder* e, const GemmIO& io, const GemmParams& p, cudaStream_t st) {
   // CTA pairs need whole 256-row tiles; B200_GEMM_CG=1 forces single-CTA tiles (A/B timing)
@@ -310,6 +339,9 @@ static int run_encoder(b200_encoder* e, const int32_t* d_ids, const int32_t* d_l
   // hidden 384 = two 192-column tiles: residual + LayerNorm fused into the producing GEMM (B200_FUSE_LN=0 disables)
   const char* fuse_env = getenv("B200_FUSE_LN");
   const char* cg_env2 = getenv("B200_GEMM_CG");
+  const char* ffn_env = getenv("B200_FUSE_FFN");
+  const bool fuse_ffn = H == FFN_H && M % 256 == 0 && I % FFN_SLICE == 0 && !(ffn_env && atoi(ffn_env) == 0) &&
+                        !(cg_env2 && atoi(cg_env2) == 1);
   const bool fuse_ln = H == 384 && M % 256 == 0 && !(fuse_env && atoi(fuse_env) == 0) && !(cg_env2 && atoi(cg_env2) == 1);
   // serpentine row order: every kernel walks the rows in the opposite direction of the one before it
   // (B200_SERPENTINE=0 disables)
@@ -358,6 +390,10 @@ static int run_encoder(b200_encoder* e, const int32_t* d_ids, const int32_t* d_l
       B200_CUDA(cudaGetLastError());
     }
     // ffn = gelu(x W1^T + b1) ; y = ffn W2^T + b2 + x ; x = LN(y)
+    if (fuse_ffn) {
+      B200_TRY(launch_ffn_fused(e, L, M, I, serp ? (kcount++ & 1) : 0, st));
+      continue;
+    }
     p.N = I; p.K = H; p.bias = L->b1.as<float>(); p.reverse = serp ? (kcount++ & 1) : 0;
     B200_TRY(launch_gemm<EPI_BIAS_GELU>(e, GemmIO{&e->map_x, &L->map_w1, &L->map_w1_h, &e->map_ffn_st, &e->map_ffn_st}, p, st));
     p.N = H; p.K = I; p.bias = L->b2.as<float>(); p.reverse = serp ? (kcount++ & 1) : 0;
@@ -486,6 +522,7 @@ int b200_encoder_finalize(b200_encoder_t* e) {
     B200_TRY(weight_map(&L->map_wo_h, L->wo, (int)H, (int)H, 2));
     B200_TRY(weight_map(&L->map_w1_h, L->w1, (int)I, (int)H, 2));
     B200_TRY(weight_map(&L->map_w2_h, L->w2, (int)H, (int)I, 2));
+    B200_TRY(make_tma_2d_bf16(&L->map_w1_f, L->w1.p, (uint64_t)I, (uint64_t)H, FFN_SLICE / 2, GEMM_BLOCK_K));
   }
   e->pending.clear();
   e->finalized = true;
