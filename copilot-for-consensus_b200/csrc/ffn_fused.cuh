@@ -26,7 +26,10 @@ constexpr int FFN_H = 384;                                // hidden size this ke
 constexpr int FFN_SLICE = 128;                            // intermediate columns per slice
 constexpr int FFN_KB1 = FFN_H / GEMM_BLOCK_K;             // 6 k-blocks of G1
 constexpr int FFN_KB2 = FFN_SLICE / GEMM_BLOCK_K;         // 2 k-blocks of G2 per slice
-constexpr int FFN_W1_STAGES = 3;
+#ifndef FFN_W1_NSTAGE
+#define FFN_W1_NSTAGE 5
+#endif
+constexpr int FFN_W1_STAGES = FFN_W1_NSTAGE;
 constexpr int FFN_W2_STAGES = 2;
 constexpr int FFN_EPI_WARPS = 8;
 constexpr int FFN_THREADS = (4 + FFN_EPI_WARPS) * 32;
@@ -73,8 +76,8 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap map_x,      // x as A opera
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + FFN_OFF_TAIL);
   uint64_t* x_full = bars;                    // [6]  TMA -> MMA   (leader's copy)     slab k-block landed
   uint64_t* x_empty = bars + 6;               // [6]  MMA -> TMA   (one per CTA)       last G1 of the row block read it
-  uint64_t* w1_full = bars + 12;              // [3]  TMA -> MMA   (leader's copy)
-  uint64_t* w1_empty = bars + 15;             // [3]  MMA -> TMA   (one per CTA)
+  uint64_t* w1_full = bars + 32;              // [FFN_W1_STAGES <= 8]  TMA -> MMA   (leader's copy)
+  uint64_t* w1_empty = bars + 40;             // [FFN_W1_STAGES <= 8]  MMA -> TMA   (one per CTA)
   uint64_t* w2_full = bars + 18;              // [2]  TMA -> MMA   (leader's copy)
   uint64_t* w2_empty = bars + 20;             // [2]  MMA -> TMA   (one per CTA)
   uint64_t* h_full = bars + 22;               // MMA -> epilogue   (one per CTA)       G1(j) complete
@@ -83,7 +86,7 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap map_x,      // x as A opera
   uint64_t* hs_free = bars + 25;              // MMA -> epilogue   (one per CTA)       G2(j) has read Hs
   uint64_t* y_full = bars + 26;               // MMA -> epilogue   (one per CTA)       row block's Y complete
   uint64_t* y_free = bars + 27;               // epilogue -> MMA   (leader's copy)     Y drained
-  uint64_t* resid_bar = bars + 28;            // [8]  residual box landed (one per epilogue warp)
+  uint64_t* resid_bar = bars + 48;            // [8]  residual box landed (one per epilogue warp)
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 64);
   float* vecs = reinterpret_cast<float*>(tmem_slot + 4);                   // b2, gamma, beta: [3][384]
   float* xs = vecs + 3 * FFN_H;                                            // [2 parities][2][128] {sum, sumsq}
