@@ -1086,24 +1086,55 @@ attention_kernel(const __nv_bfloat16* __restrict__ qkv, const int32_t* __restric
 }
 
 // =============================================================================================
-// K7: masked mean over the valid tokens, then x / max(||x||, 1e-12).  One CTA per sequence,
-// thread t owns features t, t+blockDim, ...
+// K7: masked mean over the valid tokens, then x / max(||x||, 1e-12).  One CTA per sequence.  A thread
+// owns 8 consecutive features (one 16-byte load per token row) of every ng-th token, ng = 256 / (H / 8)
+// token rows in flight per pass; the ng partial sums per feature meet in shared memory and are added
+// in a fixed order (run-to-run bit-reproducible).  H % 8 == 0, H <= 1024.
 // =============================================================================================
 __global__ void __launch_bounds__(256) pool_normalize_kernel(const __nv_bfloat16* __restrict__ x,
                                                              const int32_t* __restrict__ lens, int S, int H,
                                                              float* __restrict__ out) {
+  __shared__ float part[2048];                 // [ng][H], ng * H <= 256 * 8
   __shared__ float red[8];
   const int b = blockIdx.x;
   const int len = max(0, min(lens[b], S));
   const float denom = fmaxf((float)len, 1e-9f);
-  float acc[4] = {0.f, 0.f, 0.f, 0.f};  // H <= 1024 with 256 threads
+  const int nf = H >> 3, ng = max(1, (int)blockDim.x / nf);
+  const int g = threadIdx.x / nf, f = threadIdx.x - g * nf;
+  if (g < ng) {
+    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    const uint4* base = reinterpret_cast<const uint4*>(x + (size_t)b * S * H) + f;
+    const int row_stride = H >> 3;               // uint4 per token row
+    int t = g;
+    for (; t + ng < len; t += 2 * ng) {          // two independent loads in flight
+      const uint4 u0 = __ldg(base + (size_t)t * row_stride), u1 = __ldg(base + (size_t)(t + ng) * row_stride);
+      const uint32_t w0[4] = {u0.x, u0.y, u0.z, u0.w}, w1[4] = {u1.x, u1.y, u1.z, u1.w};
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        acc[2 * i] += __uint_as_float(w0[i] << 16) + __uint_as_float(w1[i] << 16);
+        acc[2 * i + 1] += __uint_as_float(w0[i] & 0xffff0000u) + __uint_as_float(w1[i] & 0xffff0000u);
+      }
+    }
+    if (t < len) {
+      const uint4 u0 = __ldg(base + (size_t)t * row_stride);
+      const uint32_t w0[4] = {u0.x, u0.y, u0.z, u0.w};
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        acc[2 * i] += __uint_as_float(w0[i] << 16);
+        acc[2 * i + 1] += __uint_as_float(w0[i] & 0xffff0000u);
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) part[g * H + f * 8 + i] = acc[i];
+  }
+  __syncthreads();
+  float v[4] = {0.f, 0.f, 0.f, 0.f};           // H <= 1024 with 256 threads
   float ss = 0.f;
   for (int k = 0, c = threadIdx.x; c < H; c += blockDim.x, ++k) {
     float a = 0.f;
-    const __nv_bfloat16* col = x + (size_t)b * S * H + c;
-    for (int t = 0; t < len; ++t) a += __bfloat162float(col[(size_t)t * H]);
+    for (int gg = 0; gg < ng; ++gg) a += part[gg * H + c];
     a /= denom;
-    acc[k] = a;
+    v[k] = a;
     ss = fmaf(a, a, ss);
   }
   ss = warp_sum(ss);
@@ -1112,7 +1143,7 @@ __global__ void __launch_bounds__(256) pool_normalize_kernel(const __nv_bfloat16
   float tot = 0.f;
   for (int i = 0; i < (int)(blockDim.x >> 5); ++i) tot += red[i];
   const float inv = 1.0f / fmaxf(sqrtf(tot), 1e-12f);
-  for (int k = 0, c = threadIdx.x; c < H; c += blockDim.x, ++k) out[(size_t)b * H + c] = acc[k] * inv;
+  for (int k = 0, c = threadIdx.x; c < H; c += blockDim.x, ++k) out[(size_t)b * H + c] = v[k] * inv;
 }
 
 }  // namespace b200
