@@ -115,6 +115,8 @@ __global__ void __launch_bounds__(256) prep_queries_kernel(const TIn* __restrict
 // K8: similarity tiles with fused top-KP selection.
 // ---------------------------------------------------------------------------------------------
 struct SimParams {
+  int a_stream;      // 1: the query tile does not fit in shared memory (dim > 384): its 64-wide chunks travel with
+                     //    the corpus chunks through the ring (re-read from L2 per corpus tile) instead of staying resident
   int nq;                 // valid queries
   int kc;                 // 64-wide K chunks per row (dpad / 64), 1..6 with the query tile resident
   int nstage;             // corpus-tile pipeline stages
@@ -177,9 +179,13 @@ sim_topk_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant
 
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  // resident mode: [query tile: kc chunks][ring: nstage corpus chunks]; streamed mode: [ring: nstage x (query
+  // chunk + corpus chunk)]
+  const uint32_t a_in_stage = p.a_stream ? SIM_A_CHUNK_BYTES : 0u;
+  const uint32_t stage_stride = a_in_stage + B_STAGE_BYTES;
   uint8_t* sA = smem;
-  uint8_t* sB = sA + (size_t)p.kc * SIM_A_CHUNK_BYTES;
-  uint64_t* ckeys = reinterpret_cast<uint64_t*>(sB + (size_t)p.nstage * B_STAGE_BYTES);   // [128][KP+1]
+  uint8_t* sB = p.a_stream ? smem : sA + (size_t)p.kc * SIM_A_CHUNK_BYTES;
+  uint64_t* ckeys = reinterpret_cast<uint64_t*>(sB + (size_t)p.nstage * stage_stride);   // [128][KP+1]
   uint64_t* bars = ckeys + SIM_BLOCK_M * (KP + 1);
   uint64_t* full = bars;                       // [nstage]  TMA -> MMA
   uint64_t* empty = bars + p.nstage;           // [nstage]  MMA -> TMA
@@ -230,7 +236,7 @@ sim_topk_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant
   if (warp == 0) {
     // ===== TMA producer: the warp runs the loop converged, one elected lane issues (see uniform_warp_idx) =====
     if (ntiles > 0) {
-      if (elect_one()) {
+      if (!p.a_stream && elect_one()) {
         if (CG == 2) {
           if (leader) mbar_arrive_expect_tx(a_full, (uint32_t)p.kc * SIM_A_CHUNK_BYTES * CG);
           else mbar_arrive_leader(a_full);
@@ -250,13 +256,16 @@ sim_topk_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant
         for (int c = 0; c < p.kc; ++c) {
           mbar_wait(&empty[s], ph ^ 1);
           if (elect_one()) {
+            uint8_t* stg = sB + (size_t)s * stage_stride;
             if (CG == 2) {
-              if (leader) mbar_arrive_expect_tx(&full[s], B_STAGE_BYTES * CG);
+              if (leader) mbar_arrive_expect_tx(&full[s], stage_stride * CG);
               else mbar_arrive_leader(&full[s]);
-              tma_load_2d_2sm(sB + (size_t)s * B_STAGE_BYTES, &map_c, &full[s], c * SIM_BLOCK_K, row);
+              if (p.a_stream) tma_load_2d_2sm(stg, &map_q, &full[s], c * SIM_BLOCK_K, qtile * SIM_BLOCK_M);
+              tma_load_2d_2sm(stg + a_in_stage, &map_c, &full[s], c * SIM_BLOCK_K, row);
             } else {
-              mbar_arrive_expect_tx(&full[s], B_STAGE_BYTES);
-              tma_load_2d(sB + (size_t)s * B_STAGE_BYTES, &map_c, &full[s], c * SIM_BLOCK_K, row);
+              mbar_arrive_expect_tx(&full[s], stage_stride);
+              if (p.a_stream) tma_load_2d(stg, &map_q, &full[s], c * SIM_BLOCK_K, qtile * SIM_BLOCK_M);
+              tma_load_2d(stg + a_in_stage, &map_c, &full[s], c * SIM_BLOCK_K, row);
             }
           }
           __syncwarp();
@@ -267,7 +276,7 @@ sim_topk_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant
   } else if (warp == 1) {
     // ===== MMA issuer: the leader CTA's warp 1 runs the loop converged, one elected lane issues =====
     if (ntiles > 0 && leader) {
-      mbar_wait(a_full, 0);
+      if (!p.a_stream) mbar_wait(a_full, 0);
       tc_fence_after();
       const uint32_t a_addr = smem_u32(sA);
       const uint32_t b_addr = smem_u32(sB);
@@ -281,8 +290,9 @@ sim_topk_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant
         for (int c = 0; c < p.kc; ++c) {
           mbar_wait(&full[s], ph);
           tc_fence_after();
-          const uint64_t da = umma_smem_desc_sw128(a_addr + (uint32_t)c * SIM_A_CHUNK_BYTES);
-          const uint64_t db = umma_smem_desc_sw128(b_addr + (uint32_t)s * B_STAGE_BYTES);
+          const uint64_t da = umma_smem_desc_sw128(p.a_stream ? b_addr + (uint32_t)s * stage_stride
+                                                              : a_addr + (uint32_t)c * SIM_A_CHUNK_BYTES);
+          const uint64_t db = umma_smem_desc_sw128(b_addr + (uint32_t)s * stage_stride + a_in_stage);
           if (elect_one()) {
 #pragma unroll
             for (int k = 0; k < SIM_BLOCK_K / 16; ++k) {

@@ -60,7 +60,8 @@ enum {
   B200_INDEX_MASTER_BF16 = 1  /* rows are given as bf16 and kept as bf16 (BASELINE.json "bf16 corpus") */
 };
 
-/* dim: vector dimension (1..384 in this round); capacity: initial row capacity, grows on demand. */
+/* dim: vector dimension (1..4096; up to 384 the query tile stays resident in shared memory, beyond that it is
+ * streamed); capacity: initial row capacity, grows on demand. */
 int b200_index_create(int dim, int64_t capacity, int device, int master_dtype, b200_index_t** out);
 int b200_index_destroy(b200_index_t* idx);
 /* inmemory.py:145-148 clear() */

@@ -75,7 +75,10 @@ def test_ties_resolve_to_insertion_order(vs, search_golden):
 
 
 @pytest.mark.parametrize("n,d,nq,k", [(20000, 384, 300, 10), (5000, 384, 129, 24), (3000, 384, 5, 48),
-                                      (777, 200, 64, 10), (1, 384, 3, 10), (7, 64, 2, 10), (4097, 96, 130, 10)])
+                                      (777, 200, 64, 10), (1, 384, 3, 10), (7, 64, 2, 10), (4097, 96, 130, 10),
+                                      # dimensions beyond the resident query tile (streamed mode): mpnet-class 768,
+                                      # OpenAI-class 1536, an odd one, the largest accepted
+                                      (6000, 768, 200, 10), (3000, 1536, 129, 10), (900, 1000, 5, 48), (600, 4096, 3, 10)])
 def test_random_corpora_match_oracle_bit_exact(vs, n, d, nq, k):
     rng = np.random.default_rng(n + d)
     rows = so.round_bf16(rng.standard_normal((n, d), dtype=np.float32))
