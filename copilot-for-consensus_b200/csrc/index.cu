@@ -527,6 +527,53 @@ int b200_index_get_rows(b200_index_t* ix, const int64_t* rows, int64_t n, float*
   return B200_OK;
 }
 
+}  // extern "C"
+
+// top_k in (48, EXH_KEEP]: exhaustive exact scoring, one query at a time (see search_kernels.cuh).
+static int search_exhaustive(b200_index* ix, const uint8_t* q_dev, int q_dtype, int64_t nq, int k, int64_t id_base,
+                             int64_t* d_ids, float* d_sc, cudaStream_t st) {
+  const uint32_t n_rows = (uint32_t)ix->count;
+  const uint64_t chunks0 = ((uint64_t)n_rows + EXH_CHUNK - 1) / EXH_CHUNK;
+  // scratch: fp32 copy of one query, keys of every row, two ping-pong survivor buffers
+  const size_t q_bytes = ((size_t)ix->dim * 4 + 255) / 256 * 256;
+  const size_t keys_bytes = (size_t)n_rows * 8;
+  const size_t surv_bytes = (size_t)chunks0 * EXH_KEEP * 8;
+  B200_TRY(ix->tmp.grow(q_bytes + keys_bytes + 2 * surv_bytes + 512, 0, st));
+  float* q_f32 = ix->tmp.as<float>();
+  uint64_t* keys = reinterpret_cast<uint64_t*>(ix->tmp.as<uint8_t>() + q_bytes);
+  uint64_t* surv[2] = {keys + n_rows, keys + n_rows + chunks0 * EXH_KEEP};
+  B200_CUDA(cudaFuncSetAttribute(exh_reduce_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, EXH_CHUNK * 8));
+  const int score_grid = (int)std::min<uint64_t>((n_rows + 7) / 8, (uint64_t)ix->num_sms * 8);
+  for (int64_t q = 0; q < nq; ++q) {
+    if (q_dtype == 0) {
+      B200_CUDA(cudaMemcpyAsync(q_f32, q_dev + (size_t)q * ix->dim * 4, (size_t)ix->dim * 4, cudaMemcpyDeviceToDevice, st));
+    } else {
+      exh_query_f32_kernel<<<1, 256, 0, st>>>(reinterpret_cast<const __nv_bfloat16*>(q_dev) + (size_t)q * ix->dim, ix->dim, q_f32);
+    }
+    if (ix->master_dtype == B200_INDEX_MASTER_F32)
+      exh_score_kernel<float><<<score_grid, 256, (size_t)ix->dim * 4, st>>>(q_f32, ix->master.as<float>(), n_rows, ix->dim, keys);
+    else
+      exh_score_kernel<__nv_bfloat16><<<score_grid, 256, (size_t)ix->dim * 4, st>>>(q_f32, ix->master.as<__nv_bfloat16>(), n_rows,
+                                                                                     ix->dim, keys);
+    const uint64_t* in = keys;
+    uint64_t n_in = n_rows;
+    int pp = 0;
+    for (;;) {
+      const uint64_t chunks = (n_in + EXH_CHUNK - 1) / EXH_CHUNK;
+      exh_reduce_kernel<<<(unsigned)chunks, 512, EXH_CHUNK * 8, st>>>(in, n_in, surv[pp]);
+      in = surv[pp];
+      n_in = chunks * EXH_KEEP;
+      pp ^= 1;
+      if (chunks == 1) break;
+    }
+    exh_write_kernel<<<1, 256, 0, st>>>(in, EXH_KEEP, k, id_base, d_ids + q * k, d_sc + q * k);
+    B200_CUDA(cudaGetLastError());
+  }
+  return B200_OK;
+}
+
+extern "C" {
+
 int b200_index_search(b200_index_t* ix, const void* queries, int q_dtype, int queries_on_device, int64_t nq, int k,
                       int64_t id_base, int64_t* ids, float* scores, int out_on_device, void* stream) {
   if (!ix) B200_FAIL(B200_ERR_INVALID, "index is NULL");
@@ -534,7 +581,7 @@ int b200_index_search(b200_index_t* ix, const void* queries, int q_dtype, int qu
   if (nq == 0 || k == 0) return B200_OK;
   if (!queries || !ids || !scores) B200_FAIL(B200_ERR_INVALID, "NULL buffer");
   if (q_dtype != 0 && q_dtype != 1) B200_FAIL(B200_ERR_INVALID, "q_dtype must be 0 (fp32) or 1 (bf16)");
-  if (k > 48) B200_FAIL(B200_ERR_UNSUPPORTED, "k=%d: the fused select keeps at most 64 candidates per query (k <= 48)", k);
+  if (k > EXH_KEEP) B200_FAIL(B200_ERR_UNSUPPORTED, "k=%d: top_k above %d is not supported", k, EXH_KEEP);
   const int kp = k <= 10 ? 16 : (k <= 24 ? 32 : 64);
   std::lock_guard<std::mutex> lk(ix->mu);
   DeviceGuard g(ix->device);
@@ -559,10 +606,14 @@ int b200_index_search(b200_index_t* ix, const void* queries, int q_dtype, int qu
       B200_CUDA(cudaMemcpyAsync(ix->stage.p, queries, (size_t)nq * ix->dim * qelt, cudaMemcpyHostToDevice, st));
       q_dev = ix->stage.as<uint8_t>();
     }
-    for (int64_t q0 = 0; q0 < nq; q0 += kMaxQueryChunk) {
-      const int n = (int)std::min<int64_t>(kMaxQueryChunk, nq - q0);
-      B200_TRY(search_chunk(ix, q_dev + (size_t)q0 * ix->dim * qelt, q_dtype, n, k, kp, id_base, d_ids + q0 * k,
-                            d_sc + q0 * k, st));
+    if (k > 48) {
+      B200_TRY(search_exhaustive(ix, q_dev, q_dtype, nq, k, id_base, d_ids, d_sc, st));
+    } else {
+      for (int64_t q0 = 0; q0 < nq; q0 += kMaxQueryChunk) {
+        const int n = (int)std::min<int64_t>(kMaxQueryChunk, nq - q0);
+        B200_TRY(search_chunk(ix, q_dev + (size_t)q0 * ix->dim * qelt, q_dtype, n, k, kp, id_base, d_ids + q0 * k,
+                              d_sc + q0 * k, st));
+      }
     }
   }
   if (!out_on_device) {

@@ -565,6 +565,68 @@ __global__ void __launch_bounds__(256) merge_rescore_kernel(const MergeParams p)
 }
 
 // ---------------------------------------------------------------------------------------------
+// Exhaustive path for top_k > 48 (the fused select keeps at most 64 candidates per query and corpus
+// slice).  The reference slices its sorted list at any top_k (inmemory.py:119) and one of its callers
+// asks for 50 by default (orchestrator/app/context_sources.py:66), so large k must work -- it need not
+// be fast: exact canonical fp32 score of EVERY row against one query (the arithmetic of the rescoring
+// pass, so the scores are bit-identical to the oracle's), packed into the usual 64-bit keys, then
+// repeated "sort 4096 keys in shared memory, keep the best 1024" passes until one list is left.
+// HBM-bound on the master copy: ~0.3 ms per query per million 384-d fp32 rows.
+// ---------------------------------------------------------------------------------------------
+constexpr int EXH_CHUNK = 4096;      // keys sorted per CTA
+constexpr int EXH_KEEP = 1024;       // survivors per CTA = the largest supported top_k
+
+template <typename TV>
+__global__ void __launch_bounds__(256) exh_score_kernel(const float* __restrict__ q_raw, const TV* __restrict__ master,
+                                                        uint32_t n_rows, int d, uint64_t* __restrict__ keys) {
+  extern __shared__ float exh_qh[];            // [d] normalised query
+  __shared__ float s_den;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
+  if (warp == 0) {
+    const float den = __fadd_rn(__fsqrt_rn(canon_dot_self(q_raw, d, lane)), 1e-8f);
+    if (lane == 0) s_den = den;
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < d; i += blockDim.x) exh_qh[i] = __fdiv_rn(q_raw[i], s_den);
+  __syncthreads();
+  for (uint32_t row = blockIdx.x * nwarp + warp; row < n_rows; row += gridDim.x * nwarp) {
+    const float s = canon_score(exh_qh, master + (size_t)row * d, d, lane);
+    if (lane == 0) keys[row] = pack_key(s, row);
+  }
+}
+
+// keys_in[n_in] -> keys_out[gridDim.x * EXH_KEEP]: CTA b sorts keys [b * EXH_CHUNK, +EXH_CHUNK) (0 = none)
+// in descending order and keeps the first EXH_KEEP.
+__global__ void __launch_bounds__(512) exh_reduce_kernel(const uint64_t* __restrict__ keys_in, uint64_t n_in,
+                                                         uint64_t* __restrict__ keys_out) {
+  extern __shared__ uint64_t exh_keys[];       // [EXH_CHUNK]
+  const uint64_t base = (uint64_t)blockIdx.x * EXH_CHUNK;
+  for (int i = threadIdx.x; i < EXH_CHUNK; i += blockDim.x) exh_keys[i] = base + i < n_in ? keys_in[base + i] : 0ull;
+  __syncthreads();
+  bitonic_sort_desc(exh_keys, EXH_CHUNK);
+  for (int i = threadIdx.x; i < EXH_KEEP; i += blockDim.x) keys_out[(uint64_t)blockIdx.x * EXH_KEEP + i] = exh_keys[i];
+}
+
+__global__ void exh_query_f32_kernel(const __nv_bfloat16* __restrict__ q, int d, float* __restrict__ out) {
+  for (int i = threadIdx.x; i < d; i += blockDim.x) out[i] = __bfloat162float(q[i]);
+}
+
+// the single surviving sorted list -> ids / scores of one query
+__global__ void exh_write_kernel(const uint64_t* __restrict__ keys, int n_keys, int k, int64_t id_base,
+                                 int64_t* __restrict__ ids, float* __restrict__ scores) {
+  for (int j = threadIdx.x; j < k; j += blockDim.x) {
+    const uint64_t key = j < n_keys ? keys[j] : 0ull;
+    if (key) {
+      ids[j] = id_base + (int64_t)(~(uint32_t)(key & 0xFFFFFFFFu));
+      scores[j] = orderable_f32((uint32_t)(key >> 32));
+    } else {
+      ids[j] = -1;
+      scores[j] = 0.f;
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
 // K10: merge nlists sorted (score, id) lists of k_in per query into the best k_out, global ids,
 // (score desc, id asc).  Used after the all-gather of per-GPU results: lists arrive as
 // [nlists][nq][k_in].  One warp per query; nlists*k_in <= 1024.

@@ -9,7 +9,8 @@ and the metadata dicts stay here, as SURVEY.md section 8b lays out.
 Deliberate differences, all documented in DESIGN.md:
   * a store has ONE dimension, fixed by the first insert; a later insert of another length raises
     ``ValueError("... dimension ...")`` (the reference accepts it and then fails inside ``query``);
-  * ``top_k`` above 48 and negative ``top_k`` raise instead of being served;
+  * ``top_k`` above 1024 and negative ``top_k`` raise instead of being served (up to 48 the fused
+    select serves it; 49..1024 -- the orchestrator asks for 50 by default -- takes the exhaustive path);
   * ``delete`` is lazy: rows are compacted (order-preserving) before the next read.
 
 Extensions (array in / array out, no per-element Python): ``add_embeddings_array``,
@@ -26,7 +27,7 @@ import numpy as np
 from .. import _native as nat
 from .interface import SearchResult, VectorStore
 
-MAX_TOP_K = 48
+MAX_TOP_K = 1024
 
 
 def _as_ptr(a: np.ndarray) -> ctypes.c_void_p:
@@ -239,7 +240,7 @@ class B200VectorStore(VectorStore):
 
     def _check_k(self, k: int) -> None:
         if k > MAX_TOP_K:
-            raise RuntimeError(f"top_k={k} is above the fused kernel's limit of {MAX_TOP_K}")
+            raise RuntimeError(f"top_k={k} is above the supported maximum of {MAX_TOP_K}")
 
     def _search_host(self, q: np.ndarray, k: int) -> tuple[np.ndarray, np.ndarray]:
         self._check_k(k)

@@ -86,7 +86,9 @@ int b200_index_get_rows(b200_index_t* idx, const int64_t* rows_host, int64_t n, 
 /* inmemory.py:78-128 query(), batched: for each of nq raw query vectors return the k best rows by
  * cosine similarity, scores computed as the reference does (fp32, eps 1e-8), ordered by
  * (score descending, row ascending).  ids[nq*k] = id_base + row, -1 where fewer than k rows exist;
- * scores[nq*k].  q_dtype: 0 = fp32, 1 = bf16.  k <= 48 in this round. */
+ * scores[nq*k].  q_dtype: 0 = fp32, 1 = bf16.  k <= 1024: up to 48 the fused
+ * select serves it; 49..1024 (orchestrator/app/context_sources.py:66 asks for 50) scores every row exactly, one
+ * query at a time -- same ids, order and scores, HBM-bound on the master copy. */
 int b200_index_search(b200_index_t* idx, const void* queries, int q_dtype, int queries_on_device, int64_t nq,
                       int k, int64_t id_base, int64_t* ids, float* scores, int out_on_device, void* stream);
 

@@ -89,6 +89,27 @@ def test_random_corpora_match_oracle_bit_exact(vs, n, d, nq, k):
     _assert_matches_oracle(ids, sc, qs, rows, k)
 
 
+@pytest.mark.parametrize("n,d,nq,k,master", [(20000, 384, 7, 50, "float32"), (9000, 384, 3, 200, "float32"),
+                                             (5000, 96, 2, 1024, "float32"), (30, 384, 2, 50, "float32"),
+                                             (6000, 768, 4, 64, "bfloat16")])
+def test_large_top_k_exhaustive_path_matches_oracle_bit_exact(vs, n, d, nq, k, master):
+    """top_k above the fused select's 48 (orchestrator/app/context_sources.py:66 asks for 50): every row is
+    scored exactly; ids, order and fp32 scores equal the oracle's, short lists are padded with -1."""
+    rng = np.random.default_rng(n + k)
+    rows = so.round_bf16(rng.standard_normal((n, d), dtype=np.float32))
+    rows[11] = rows[3]                      # exact duplicates: the lower row wins the tie
+    rows[n - 1] = rows[3]
+    qs = so.round_bf16(rng.standard_normal((nq, d), dtype=np.float32))
+    qs[0] = rows[3]
+    st = vs.B200VectorStore(device="cuda:0", master_dtype=master)
+    st.add_embeddings_array([f"r{i}" for i in range(n)], rows)
+    ids, sc = st.query_batch(qs, top_k=k)
+    _assert_matches_oracle(ids, sc, qs, rows, k)
+    assert list(ids[0, :3]) == [3, 11, n - 1]
+    res = st.query(qs[1].tolist(), top_k=k)             # the reference-shaped call
+    assert len(res) == min(k, n) and [r.id for r in res] == [f"r{i}" for i in ids[1, :min(k, n)]]
+
+
 def test_fp32_inputs_drop_in_mode(vs):
     """Raw fp32 vectors (not bf16-representable): candidates come from the bf16 search copy, the
     final order and scores from the fp32 master copy, so the result still equals the oracle."""
@@ -174,8 +195,8 @@ def test_error_contract_and_edge_cases(vs):
     assert st.count() == 0 and st.query([1.0, 0.0, 0.0]) == []
     st.add_embedding("z", [1.0, 2.0], {})              # a cleared store accepts a new dimension
     assert st.query([1.0, 2.0])[0].id == "z"
-    with pytest.raises(RuntimeError, match="limit"):
-        st.query_batch(np.ones((1, 2), np.float32), top_k=49)
+    with pytest.raises(RuntimeError, match="maximum"):
+        st.query_batch(np.ones((1, 2), np.float32), top_k=1025)
 
 
 def test_factory_dispatch(vs):
