@@ -102,7 +102,8 @@ static int hot_launch_attrs(cudaLaunchAttribute* attr, bool pair) {
     attr[n].val.clusterDim.x = 2; attr[n].val.clusterDim.y = 1; attr[n].val.clusterDim.z = 1;
     ++n;
   }
-  static const bool pdl = [] { const char* v = getenv("B200_PDL"); return v && atoi(v) != 0; }();
+  const char* pdl_env = getenv("B200_PDL");
+  const bool pdl = pdl_env && atoi(pdl_env) != 0;
   if (pdl && !prof_enabled()) {     // per-kernel timing records events between launches: keep those runs serial
     attr[n].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[n].val.programmaticStreamSerializationAllowed = 1;

@@ -120,6 +120,21 @@ def test_sharp_attention_both_softmax_reference_paths(monkeypatch, qk_scale, exa
     p.close()
 
 
+@pytest.mark.parametrize("env", [{"B200_FUSE_FFN": "0"}, {"B200_FUSE_FFN": "0", "B200_FUSE_LN": "0"},
+                                 {"B200_FUSE_FFN": "0", "B200_FUSE_LN": "0", "B200_GEMM_AST": "0"},
+                                 {"B200_GEMM_CG": "1"}, {"B200_SERPENTINE": "0"}, {"B200_PDL": "1"},
+                                 {"B200_ATTENTION": "legacy"}])
+def test_alternative_kernel_paths_stay_correct(monkeypatch, minilm, minilm_weights, env):
+    """The kernels the default MiniLM path no longer takes (separate FFN GEMMs, separate LayerNorm, the
+    non-A-stationary and single-CTA GEMMs, the mma.sync attention) still serve other shapes; the
+    switches are read per call, so the same provider can be driven through each of them."""
+    for k, v in env.items():
+        monkeypatch.setenv(k, v)
+    ids, mask, lens = eo.synthetic_tokens(9, 256, 30522, seed=21, ragged=True)
+    got = minilm.embed_tokens(ids.numpy(), lens.numpy())
+    _check(got, eo.encode(eo.MINILM_L6, minilm_weights, ids, mask).numpy())
+
+
 def test_embed_contract(minilm):
     """sentence_transformer_provider.py:88-91 and the attributes its tests assert."""
     with pytest.raises(ValueError, match="Text cannot be None"):
