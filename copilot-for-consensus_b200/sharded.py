@@ -73,11 +73,21 @@ class ShardedSearch:
             return ids, sc
         nq = ids.shape[0]
         # gathered along dim 0 ([world*nq, k]); viewed as [world, nq, k], the layout b200_merge_topk takes
-        all_ids = torch.empty((self.world * nq, k), dtype=ids.dtype, device=ids.device)
-        all_sc = torch.empty((self.world * nq, k), dtype=sc.dtype, device=sc.device)
-        self._dist.all_gather_into_tensor(all_ids, ids.contiguous(), group=self._group)
-        self._dist.all_gather_into_tensor(all_sc, sc.contiguous(), group=self._group)
+        all_ids, all_sc = self._gather_candidates(ids, sc)
         return self._merge(all_ids.view(self.world, nq, k), all_sc.view(self.world, nq, k), k)
+
+    def _gather_candidates(self, ids: Any, sc: Any):
+        """ONE all-gather for both halves of the candidates (the exchange is latency-bound: 0.49 MB per rank
+        at 4096 queries): ids and the scores' bit patterns travel as one ``[n, 2k]`` int64 tensor."""
+        import torch
+
+        n, k = ids.shape
+        packed = torch.cat((ids, sc.contiguous().view(torch.int32).to(torch.int64)), dim=1).contiguous()
+        gathered = torch.empty((self.world * n, 2 * k), dtype=torch.int64, device=ids.device)
+        self._dist.all_gather_into_tensor(gathered, packed, group=self._group)
+        all_ids = gathered[:, :k].contiguous()
+        all_sc = gathered[:, k:].to(torch.int32).view(torch.float32).contiguous()
+        return all_ids, all_sc
 
     def search_local_queries(self, queries: Any, k: int = 10):
         """Each rank passes its OWN ``[nq_local, dim]`` queries (same count on every rank, e.g. the
@@ -90,10 +100,7 @@ class ShardedSearch:
         q_all = torch.empty((self.world * nq, queries.shape[1]), dtype=queries.dtype, device=queries.device)
         self._dist.all_gather_into_tensor(q_all, queries.contiguous(), group=self._group)
         ids, sc = self._search(q_all, k, self.row_offset)               # [world*nq, k] on this shard
-        all_ids = torch.empty((self.world * self.world * nq, k), dtype=ids.dtype, device=ids.device)
-        all_sc = torch.empty((self.world * self.world * nq, k), dtype=sc.dtype, device=sc.device)
-        self._dist.all_gather_into_tensor(all_ids, ids.contiguous(), group=self._group)
-        self._dist.all_gather_into_tensor(all_sc, sc.contiguous(), group=self._group)
+        all_ids, all_sc = self._gather_candidates(ids, sc)
         mine = slice(self.rank * nq, (self.rank + 1) * nq)
         all_ids = all_ids.view(self.world, self.world * nq, k)
         all_sc = all_sc.view(self.world, self.world * nq, k)
