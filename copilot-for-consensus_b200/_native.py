@@ -48,6 +48,9 @@ SYMBOLS = {
     "b200_encoder_hidden": (_i, [_vp]),
     "b200_encode": (_i, [_vp, _vp, _vp, _i, _i, _i, _vp, _i, _vp]),
     "b200_encoder_peek": (_i, [_vp, _i, _vp, _i64]),
+    "b200_wordpiece_create": (_i, [_vp, _vp, ctypes.c_int32, _i, ctypes.POINTER(_vp)]),
+    "b200_wordpiece_destroy": (_i, [_vp]),
+    "b200_wordpiece_encode": (_i, [_vp, _vp, _vp, _i64, ctypes.c_int32, _vp, _vp, ctypes.c_int32]),
     "b200_profile_enable": (_i, [_i]),
     "b200_profile_reset": (_i, []),
     "b200_profile_read": (_i64, [_vp, _i64]),

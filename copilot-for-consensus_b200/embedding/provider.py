@@ -113,24 +113,25 @@ class B200SentenceTransformerProvider(EmbeddingProvider):
         out = np.empty((n, self.dimension), dtype=np.float32)
         if n == 0:
             return out
-        rows = [self.tokenizer.encode(t, self.max_seq_length) for t in texts]
-        order = sorted(range(n), key=lambda i: len(rows[i]))
+        all_ids, all_lens = self.tokenizer.encode_arrays(texts, self.max_seq_length)
+        order = np.argsort(all_lens, kind="stable")
+        sorted_lens = all_lens[order]
+        s_cap = -(-self.config.max_pos // 16) * 16
         i = 0
         while i < n:
             # grow the bucket while (padded length x rows) stays inside the per-call token budget
             j = i
             while j < n:
-                S = -(-len(rows[order[j]]) // 64) * 64
+                S = -(-int(sorted_lens[j]) // 64) * 64
                 if (j - i + 1) * S > self._max_tokens and j > i:
                     break
                 j += 1
             sel = order[i:j]
-            S = min(-(-len(rows[sel[-1]]) // 64) * 64, -(-self.config.max_pos // 16) * 16)
+            S = min(-(-int(sorted_lens[j - 1]) // 64) * 64, s_cap)
             ids = np.zeros((len(sel), S), dtype=np.int32)
-            lens = np.empty(len(sel), dtype=np.int32)
-            for k, r in enumerate(sel):
-                ids[k, : len(rows[r])] = rows[r]
-                lens[k] = len(rows[r])
+            w = min(S, all_ids.shape[1])
+            ids[:, :w] = all_ids[sel, :w]
+            lens = np.ascontiguousarray(all_lens[sel])
             out[sel] = self._encode_host(ids, lens)
             i = j
         return out

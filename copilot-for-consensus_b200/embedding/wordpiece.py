@@ -148,15 +148,96 @@ class WordPieceTokenizer:
         body = self.tokenize_to_ids(text)[: max(0, max_length - 2)]
         return [self.cls_id, *body, self.sep_id]
 
+    # -- many texts at once: native ASCII fast path + this implementation for the rest -------------
+    def _native_handle(self):
+        """Handle of the C++ tokenizer over the same vocabulary (csrc/wordpiece.cu), or None when the
+        shared library cannot be loaded.  Built lazily, once."""
+        if getattr(self, "_native_tried", False):
+            return self._native
+        self._native_tried, self._native = True, None
+        try:
+            import ctypes
+
+            from .. import _native as nat
+
+            lib = nat.lib()
+            by_id = sorted(self.vocab.items(), key=lambda kv: kv[1])
+            if [i for _, i in by_id] != list(range(len(by_id))):
+                return None                                  # ids are not 0..n-1: keep the Python path
+            enc = [t.encode("utf-8") for t, _ in by_id]
+            offs = np.zeros(len(enc) + 1, dtype=np.int64)
+            np.cumsum([len(b) for b in enc], out=offs[1:])
+            blob = b"".join(enc)
+            h = ctypes.c_void_p()
+            nat.check(lib.b200_wordpiece_create(ctypes.c_char_p(blob), ctypes.c_void_p(offs.ctypes.data), len(enc),
+                                                1 if self.do_lower_case else 0, ctypes.byref(h)))
+            self._native = (lib, h)
+        except Exception:                                    # no library on this machine: Python only
+            self._native = None
+        return self._native
+
+    def encode_arrays(self, texts: Sequence[str], max_length: int, n_threads: int = 0) -> tuple[np.ndarray, np.ndarray]:
+        """``(ids[n, max_length] int32 padded with [PAD], lengths[n] int32)`` -- :meth:`encode` for every text
+        without a Python object per token.  ASCII texts go through the multi-threaded C++ tokenizer
+        (``b200_wordpiece_encode``), texts with any non-ASCII character through :meth:`encode`; the result is
+        the same either way (tests/test_wordpiece.py compares the two on the same inputs)."""
+        n = len(texts)
+        ids = np.full((n, max_length), self.pad_id, dtype=np.int32)
+        lens = np.zeros(n, dtype=np.int32)
+        nat_h = self._native_handle() if n >= 4 and max_length >= 2 and self.max_chars_per_word == 100 else None
+        if nat_h is None:
+            todo = range(n)
+        else:
+            import ctypes
+
+            from .. import _native as nat
+
+            lib, h = nat_h
+            enc = [t.encode("utf-8", "surrogatepass") for t in texts]
+            offs = np.zeros(n + 1, dtype=np.int64)
+            np.cumsum([len(b) for b in enc], out=offs[1:])
+            blob = b"".join(enc)
+            nat.check(lib.b200_wordpiece_encode(h, ctypes.c_char_p(blob), ctypes.c_void_p(offs.ctypes.data), n, max_length,
+                                                ctypes.c_void_p(ids.ctypes.data), ctypes.c_void_p(lens.ctypes.data),
+                                                n_threads))
+            todo = np.flatnonzero(lens < 0).tolist()          # texts with non-ASCII characters
+        for i in todo:
+            row = self.encode(texts[i], max_length)
+            ids[i, : len(row)] = row
+            ids[i, len(row):] = self.pad_id
+            lens[i] = len(row)
+        return ids, lens
+
+    def encode_many(self, texts: Sequence[str], max_length: int, n_threads: int = 0) -> list[list[int]]:
+        """:meth:`encode` for every text, as lists (see :meth:`encode_arrays`)."""
+        if max_length < 2:
+            return [self.encode(t, max_length) for t in texts]
+        ids, lens = self.encode_arrays(texts, max_length, n_threads)
+        return [ids[i, : int(lens[i])].tolist() for i in range(len(texts))]
+
+    def __del__(self):
+        nat_h = getattr(self, "_native", None)
+        if nat_h:
+            try:
+                nat_h[0].b200_wordpiece_destroy(nat_h[1])
+            except Exception:
+                pass
+
     def encode_batch(self, texts: Iterable[str], max_length: int, pad_to_multiple: int = 1
                      ) -> tuple[np.ndarray, np.ndarray]:
         """Padded ``(input_ids[B,S] int32, lengths[B] int32)``; S = longest row rounded up."""
-        rows = [self.encode(t, max_length) for t in texts]
-        longest = max((len(r) for r in rows), default=1)
+        texts = list(texts)
+        if max_length < 2:
+            rows = [self.encode(t, max_length) for t in texts]
+            full = np.full((len(rows), max(2, max_length)), self.pad_id, dtype=np.int32)
+            lens = np.array([len(r) for r in rows], dtype=np.int32)
+            for i, r in enumerate(rows):
+                full[i, : len(r)] = r
+        else:
+            full, lens = self.encode_arrays(texts, max_length)
+        longest = int(lens.max()) if len(texts) else 1
         S = -(-longest // pad_to_multiple) * pad_to_multiple
-        ids = np.full((len(rows), S), self.pad_id, dtype=np.int32)
-        lens = np.zeros(len(rows), dtype=np.int32)
-        for i, r in enumerate(rows):
-            ids[i, : len(r)] = r
-            lens[i] = len(r)
+        ids = np.full((len(texts), S), self.pad_id, dtype=np.int32)
+        w = min(S, full.shape[1])
+        ids[:, :w] = full[:, :w]
         return ids, lens

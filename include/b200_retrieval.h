@@ -43,6 +43,7 @@ typedef enum b200_status {
 
 typedef struct b200_index b200_index_t;
 typedef struct b200_encoder b200_encoder_t;
+typedef struct b200_wordpiece b200_wordpiece_t;
 
 /* ---- library ------------------------------------------------------------------------------ */
 const char* b200_last_error(void);
@@ -149,6 +150,21 @@ int b200_encode(b200_encoder_t* enc, const int32_t* input_ids, const int32_t* le
  * activation buffer, as left by the last b200_encode call, to a host fp32 buffer.
  * which: 0 = x (hidden state), 1 = qkv, 2 = ctx (attention output), 3 = y (pre-LayerNorm), 4 = ffn. */
 int b200_encoder_peek(b200_encoder_t* enc, int which, float* out_host, int64_t numel);
+
+/* ---- host-side WordPiece (ASCII fast path) ---------------------------------------------------------
+ * Replaces, for text made of ASCII bytes only, the tokenisation `SentenceTransformer.encode` performs
+ * inside sentence_transformer_provider.py:93 (uncased BERT recipe: clean, lower-case, split on whitespace
+ * and punctuation, greedy longest-match WordPiece, [CLS] ... [SEP], truncation).  No CUDA involved.
+ *   vocab_blob / offsets[n_vocab + 1]: the pieces of vocab.txt concatenated (UTF-8), id = line number.
+ *   texts_blob / offsets[n_texts + 1]: the texts concatenated (UTF-8).
+ *   ids[n_texts * max_length] (padded with [PAD]), lengths[n_texts]; lengths[i] = -1 marks a text with
+ *   non-ASCII bytes, which the caller must tokenise with the full Unicode implementation
+ *   (copilot-for-consensus_b200/embedding/wordpiece.py).  n_threads <= 0: one per hardware thread. */
+int b200_wordpiece_create(const char* vocab_blob, const int64_t* offsets, int32_t n_vocab, int do_lower_case,
+                          b200_wordpiece_t** out);
+int b200_wordpiece_destroy(b200_wordpiece_t* h);
+int b200_wordpiece_encode(const b200_wordpiece_t* h, const char* texts_blob, const int64_t* offsets, int64_t n_texts,
+                          int32_t max_length, int32_t* ids, int32_t* lengths, int32_t n_threads);
 
 /* Optional per-kernel timing (no reference counterpart), used by bench.py for the roofline line.
  * While enabled, every kernel launch is bracketed by CUDA events on its stream.  profile_read

@@ -55,3 +55,59 @@ def test_encode_batch_padding(vocab):
     assert ids[0, 0] == 101 and ids[0, lens[0] - 1] == 102 and (ids[0, lens[0]:] == 0).all()
     ids, lens = wp.encode_batch(["ba " * 500], max_length=16)
     assert ids.shape == (1, 16) and ids[0, -1] == 102
+
+
+ASCII_TEXTS = [
+    "The working group reached rough consensus on the QUIC draft; see RFC 9000, section 4.2!",
+    "  multiple   spaces\tand\nnewlines\r\n  ",
+    "UPPER lower MiXeD 12345 3.14159 a_b-c/d\\e ~tilde `tick` {brace} |pipe| ^caret",
+    "x" * 150 + " short " + "y" * 100 + " " + "z" * 101,
+    "[CLS] literal specials [SEP] [MASK] [unused5] [PAD] [UNK] [cls]",
+    "ba##be ##ba don't can't it's a.b.c ... !!! ???",
+    "control\x01chars\x7finside\x00words and\x0bvertical\x0ctabs\x1f",
+    "",
+    "   ",
+    "a",
+    "word " * 400,
+]
+
+
+def test_native_tokenizer_equals_python_and_transformers(vocab, tmp_path):
+    """csrc/wordpiece.cu (ASCII fast path, threads) against the Python restatement and against
+    transformers.BertTokenizer, token for token; non-ASCII texts fall back to Python inside encode_many."""
+    wpm = pkg("embedding.wordpiece")
+    wp = wpm.WordPieceTokenizer(vocab)
+    assert wp._native_handle() is not None, "the shared library must load (the tokenizer needs no GPU)"
+    texts = ASCII_TEXTS + TEXTS
+    for max_len in (2, 3, 16, 64, 256):
+        want = [wp.encode(t, max_len) for t in texts]
+        for threads in (1, 0, 5):
+            assert wp.encode_many(texts, max_len, n_threads=threads) == want, (max_len, threads)
+    transformers = pytest.importorskip("transformers")
+    (tmp_path / "vocab.txt").write_text("\n".join(vocab) + "\n", encoding="utf-8")
+    (tmp_path / "tokenizer_config.json").write_text('{"do_lower_case": true, "tokenizer_class": "BertTokenizer"}')
+    hf = transformers.AutoTokenizer.from_pretrained(str(tmp_path))
+    got = wp.encode_many(ASCII_TEXTS, 64)
+    for t, g in zip(ASCII_TEXTS, got):
+        assert g == hf(t, truncation=True, max_length=64)["input_ids"], t
+
+
+def test_native_tokenizer_random_ascii_and_batch_layout(vocab):
+    import random
+
+    wp = pkg("embedding.wordpiece").WordPieceTokenizer(vocab)
+    rnd = random.Random(3)
+    alphabet = "abcdefghijklmnopqrstuvwxyzABCDEFGHIJKLMNOPQRSTUVWXYZ0123456789 .,;:!?-_'\"()[]#/\\\t\n\x02"
+    words = [v for v in vocab if v.isalpha() and v.isascii() and len(v) > 1][:3000]
+    texts = []
+    for i in range(300):
+        if i % 3 == 0:
+            texts.append("".join(rnd.choice(alphabet) for _ in range(rnd.randrange(0, 400))))
+        else:
+            texts.append(" ".join(rnd.choice(words) for _ in range(rnd.randrange(1, 300))))
+    want = [wp.encode(t, 128) for t in texts]
+    assert wp.encode_many(texts, 128) == want
+    ids, lens = wp.encode_batch(texts, 128, pad_to_multiple=16)
+    assert ids.shape[1] % 16 == 0 and ids.dtype == np.int32 and lens.tolist() == [len(r) for r in want]
+    for i, r in enumerate(want):
+        assert ids[i, : len(r)].tolist() == r and (ids[i, len(r):] == wp.pad_id).all()
