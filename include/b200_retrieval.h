@@ -151,14 +151,17 @@ int b200_encode(b200_encoder_t* enc, const int32_t* input_ids, const int32_t* le
  * which: 0 = x (hidden state), 1 = qkv, 2 = ctx (attention output), 3 = y (pre-LayerNorm), 4 = ffn. */
 int b200_encoder_peek(b200_encoder_t* enc, int which, float* out_host, int64_t numel);
 
-/* ---- host-side WordPiece (ASCII fast path) ---------------------------------------------------------
- * Replaces, for text made of ASCII bytes only, the tokenisation `SentenceTransformer.encode` performs
- * inside sentence_transformer_provider.py:93 (uncased BERT recipe: clean, lower-case, split on whitespace
- * and punctuation, greedy longest-match WordPiece, [CLS] ... [SEP], truncation).  No CUDA involved.
+/* ---- host-side WordPiece ---------------------------------------------------------------------------
+ * Replaces the tokenisation `SentenceTransformer.encode` performs inside
+ * sentence_transformer_provider.py:93 (uncased BERT recipe: clean, lower-case + strip accents, split on
+ * whitespace / punctuation / CJK, greedy longest-match WordPiece, [CLS] ... [SEP], truncation) for ASCII
+ * text and, for uncased models, for text of the Basic Multilingual Plane (character classes and folded
+ * forms come from tables generated out of Python's unicodedata: csrc/unicode_tables.h).  No CUDA involved.
  *   vocab_blob / offsets[n_vocab + 1]: the pieces of vocab.txt concatenated (UTF-8), id = line number.
  *   texts_blob / offsets[n_texts + 1]: the texts concatenated (UTF-8).
- *   ids[n_texts * max_length] (padded with [PAD]), lengths[n_texts]; lengths[i] = -1 marks a text with
- *   non-ASCII bytes, which the caller must tokenise with the full Unicode implementation
+ *   ids[n_texts * max_length] (padded with [PAD]), lengths[n_texts]; lengths[i] = -1 marks a text the
+ *   tables do not cover (combining marks, characters beyond U+FFFF, GREEK CAPITAL SIGMA, malformed UTF-8,
+ *   any non-ASCII text of a cased model), which the caller must tokenise with the full implementation
  *   (copilot-for-consensus_b200/embedding/wordpiece.py).  n_threads <= 0: one per hardware thread. */
 int b200_wordpiece_create(const char* vocab_blob, const int64_t* offsets, int32_t n_vocab, int do_lower_case,
                           b200_wordpiece_t** out);

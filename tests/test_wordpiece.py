@@ -111,3 +111,56 @@ def test_native_tokenizer_random_ascii_and_batch_layout(vocab):
     assert ids.shape[1] % 16 == 0 and ids.dtype == np.int32 and lens.tolist() == [len(r) for r in want]
     for i, r in enumerate(want):
         assert ids[i, : len(r)].tolist() == r and (ids[i, len(r):] == wp.pad_id).all()
+
+
+def test_native_tokenizer_unicode_bmp_equals_python(vocab):
+    """Non-ASCII text of the Basic Multilingual Plane goes through the generated tables
+    (csrc/unicode_tables.h, derived from Python's unicodedata by scripts/gen_unicode_tables.py); anything the
+    tables do not cover (combining marks, astral characters, final-sigma contexts) comes back as -1 and is
+    tokenised by the Python implementation -- either way encode_many must equal encode."""
+    import ctypes
+    import random
+
+    wp = pkg("embedding.wordpiece").WordPieceTokenizer(vocab)
+    lib, h = wp._native_handle()
+    samples = [
+        "naïve café résumé — mailing-list thread about DNSSEC key rollover (re: draft-ietf-dnsop)",
+        "“smart quotes” and ‘single’ … ellipsis – en dash — em dash • bullet § section ¶",
+        "Ångström Øresund Łódź Dvořák İstanbul ıspanak ẞ straße ǅ ǆ Ǆ ﬁ ﬂ",
+        "汉字 mixed with ascii 漢字かな交じり文 カタカナ ひらがな ｆｕｌｌｗｉｄｔｈ！",
+        "한국어 텍스트 토큰화 테스트",
+        "Ελληνικά κείμενο ΑΒΓ δοκιμή",          # no capital sigma: stays on the native path
+        "ΣΟΦΟΣ λόγος",                          # capital sigma: Python's context-sensitive lower()
+        "русский текст Ёжик ПРИВЕТ мир",
+        "zero​width nbsp line para　ideographic space﻿bom",
+        "é combining acute and å ring",          # combining marks -> Python
+        "emoji \U0001f600 and astral \U00020000 ideograph",    # beyond the BMP -> Python
+        "תל אביב عربى نص हिन्दी पाठ ไทย ข้อความ",
+        "mixed[CLS]inside and [SEP] alone №5 ½ ² ™ © ® ° ± × ÷",
+    ]
+    rnd = random.Random(11)
+    pools = [list(range(0x20, 0x7F)), list(range(0xA0, 0x250)), list(range(0x370, 0x530)), list(range(0x2000, 0x2070)),
+             list(range(0x3000, 0x3100)), list(range(0x4E00, 0x4E80)), list(range(0xAC00, 0xAC80)), list(range(0xFF00, 0xFFF0)),
+             list(range(0x1E00, 0x2000)), list(range(0x2100, 0x2200))]
+    for _ in range(400):
+        n = rnd.randrange(1, 120)
+        pool = rnd.choice(pools) + pools[0] + [0x20] * 40
+        samples.append("".join(chr(rnd.choice(pool)) for _ in range(n)))
+    # every BMP character once, in words of 7, so that every table entry is exercised
+    cps = [cp for cp in range(0x80, 0x10000) if not 0xD800 <= cp <= 0xDFFF]
+    for i in range(0, len(cps), 700):
+        chunk = cps[i:i + 700]
+        samples.append(" ".join("a" + "".join(chr(c) for c in chunk[j:j + 7]) + "b" for j in range(0, len(chunk), 7)))
+    for max_len in (16, 256, 1024):
+        want = [wp.encode(t, max_len) for t in samples]
+        assert wp.encode_many(samples, max_len) == want
+    # the native path really handles BMP text itself (no silent fallback for the common cases)
+    n = 9
+    enc = [t.encode("utf-8") for t in samples[:n]]
+    offs = np.zeros(n + 1, dtype=np.int64)
+    np.cumsum([len(b) for b in enc], out=offs[1:])
+    ids = np.empty((n, 64), dtype=np.int32)
+    lens = np.empty(n, dtype=np.int32)
+    assert lib.b200_wordpiece_encode(h, ctypes.c_char_p(b"".join(enc)), ctypes.c_void_p(offs.ctypes.data), n, 64,
+                                     ctypes.c_void_p(ids.ctypes.data), ctypes.c_void_p(lens.ctypes.data), 1) == 0
+    assert (lens[[0, 1, 2, 3, 4, 5, 7, 8]] > 0).all() and lens[6] == -1
