@@ -29,6 +29,8 @@ SYMBOLS = {
     "b200_last_error": (_cp, []),
     "b200_version": (_i, []),
     "b200_device_count": (_i, []),
+    "b200_set_option": (_i, [_cp, _i]),
+    "b200_get_option": (_i, [_cp, ctypes.POINTER(_i)]),
     "b200_index_create": (_i, [_i, _i64, _i, _i, ctypes.POINTER(_vp)]),
     "b200_index_destroy": (_i, [_vp]),
     "b200_index_clear": (_i, [_vp]),
@@ -39,6 +41,8 @@ SYMBOLS = {
     "b200_index_remove_rows": (_i, [_vp, _vp, _i64, _vp]),
     "b200_index_get_rows": (_i, [_vp, _vp, _i64, _vp, _i, _vp]),
     "b200_index_search": (_i, [_vp, _vp, _i, _i, _i64, _i, _i64, _vp, _vp, _i, _vp]),
+    "b200_index_certificate_stats": (_i, [_vp, ctypes.POINTER(_i64), ctypes.POINTER(_i64)]),
+    "b200_index_search_l2": (_i, [_vp, _vp, _i, _i, _i64, _i, _i64, _vp, _vp, _i, _vp]),
     "b200_index_search_static": (_i, [_vp, _vp, _i, _i64, _i, _i64, _vp, _vp, _vp]),
     "b200_merge_topk": (_i, [_vp, _vp, _i64, _i, _i, _i, _vp, _vp, _i, _vp]),
     "b200_encoder_create": (_i, [ctypes.POINTER(EncoderConfigC), _i, ctypes.POINTER(_vp)]),
@@ -122,6 +126,35 @@ def current_stream_ptr(device_ordinal: int) -> int:
     except Exception:
         pass
     return 0
+
+
+def set_option(name: str, value: int) -> None:
+    """Process-wide kernel-variant switch (``b200_set_option``); see the header for names and defaults."""
+    check(lib().b200_set_option(name.encode(), int(value)))
+
+
+def get_option(name: str) -> int:
+    v = ctypes.c_int(0)
+    check(lib().b200_get_option(name.encode(), ctypes.byref(v)))
+    return int(v.value)
+
+
+class options:
+    """``with options(fuse_ffn=0, gemm_ast=0): ...`` -- set switches for a block and restore them afterwards."""
+
+    def __init__(self, **kw: int):
+        self._kw, self._old = kw, {}
+
+    def __enter__(self):
+        for k, v in self._kw.items():
+            self._old[k] = get_option(k)
+            set_option(k, v)
+        return self
+
+    def __exit__(self, *exc):
+        for k, v in self._old.items():
+            set_option(k, v)
+        return False
 
 
 def profile(on: bool) -> None:

@@ -345,6 +345,10 @@ B200_DEVINL uint64_t umma_smem_desc(uint32_t smem_addr_bytes, uint32_t layout_ty
 __host__ __device__ constexpr uint32_t umma_idesc_bf16_f32(uint32_t M, uint32_t N) {
   return (1u << 4) | (1u << 7) | (1u << 10) | ((N >> 3) << 17) | ((M >> 4) << 24);
 }
+// same with IEEE half A and B (format code 0)
+__host__ __device__ constexpr uint32_t umma_idesc_f16_f32(uint32_t M, uint32_t N) {
+  return (1u << 4) | ((N >> 3) << 17) | ((M >> 4) << 24);
+}
 // same, with the B operand MN-major (its N index is the contiguous one in shared memory)
 __host__ __device__ constexpr uint32_t umma_idesc_bf16_f32_bmn(uint32_t M, uint32_t N) {
   return umma_idesc_bf16_f32(M, N) | (1u << 16);

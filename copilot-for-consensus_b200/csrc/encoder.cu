@@ -68,6 +68,7 @@ struct b200_encoder {
   DevBuf x, qkv, ctx, y, ffn, ids, lens, out;
   CUtensorMap map_x, map_ctx, map_ffn;                      // A operands: box {64, 128}
   CUtensorMap map_qkv_st, map_y_st, map_ffn_st, map_x_res;  // epilogue boxes {64, 32}: stores and the residual load
+  StreamOrder order;   // calls arriving on different streams share the activation buffers: see host_util.h
   std::mutex mu;
   ~b200_encoder() {
     for (auto* l : layers) delete l;
@@ -91,7 +92,7 @@ struct GemmIO {
   const CUtensorMap* resid;  // residual [M, N], box {64, 32} (TMA load) or the same as out when unused
 };
 
-// Launch attributes of the hot-path kernels: cluster of two (CTA pairs) and, with B200_PDL=1, programmatic
+// Launch attributes of the hot-path kernels: cluster of two (CTA pairs) and, with option pdl=1, programmatic
 // stream serialisation (see pdl_wait in common.cuh).  Off by default: measured +0.3 % on the 512 x 256
 // batch (3.975 -> 3.960 ms per step) -- the kernels are long and persistent, so their boundaries cost
 // little -- which is not worth relaxing the stream order for.  Returns the attribute count.
@@ -102,8 +103,7 @@ static int hot_launch_attrs(cudaLaunchAttribute* attr, bool pair) {
     attr[n].val.clusterDim.x = 2; attr[n].val.clusterDim.y = 1; attr[n].val.clusterDim.z = 1;
     ++n;
   }
-  const char* pdl_env = getenv("B200_PDL");
-  const bool pdl = pdl_env && atoi(pdl_env) != 0;
+  const bool pdl = opt(OPT_PDL) != 0;
   if (pdl && !prof_enabled()) {     // per-kernel timing records events between launches: keep those runs serial
     attr[n].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[n].val.programmaticStreamSerializationAllowed = 1;
@@ -246,13 +246,11 @@ static int launch_ffn_fused(const b200_encoder* e, const LayerWeights* L, int M,
 
 template <int EPI>
 static int launch_gemm(const b200_encoder* e, const GemmIO& io, const GemmParams& p, cudaStream_t st) {
-  // CTA pairs need whole 256-row tiles; B200_GEMM_CG=1 forces single-CTA tiles (A/B timing)
-  const char* cg_env = getenv("B200_GEMM_CG");
-  const bool pair = (p.M % (2 * GEMM_BLOCK_M) == 0) && io.w2 != nullptr && !(cg_env && atoi(cg_env) == 1);
-  // K <= 384: keep the activation slab in shared memory across column tiles (B200_GEMM_AST=0 disables)
-  const char* ast_env = getenv("B200_GEMM_AST");
+  // CTA pairs need whole 256-row tiles; option gemm_pair=0 forces single-CTA tiles (A/B timing)
+  const bool pair = (p.M % (2 * GEMM_BLOCK_M) == 0) && io.w2 != nullptr && opt(OPT_GEMM_PAIR) != 0;
+  // K <= 384: keep the activation slab in shared memory across column tiles (option gemm_ast=0 disables)
   if (pair && pick_block_n(p.N) == 192 && p.K <= GEMM_AST_MAX_KB * GEMM_BLOCK_K && p.N / 192 >= 2 &&
-      !(ast_env && atoi(ast_env) == 0))
+      opt(OPT_GEMM_AST) != 0)
     return launch_gemm_ast<192, EPI>(e, io, p, st);
   switch (pick_block_n(p.N)) {
     case 192: return pair ? launch_gemm_t<192, EPI, 2>(e, io, p, st) : launch_gemm_t<192, EPI, 1>(e, io, p, st);
@@ -323,12 +321,10 @@ static int run_encoder(b200_encoder* e, const int32_t* d_ids, const int32_t* d_l
   else B200_CUDA(cudaFuncSetAttribute(attention_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)att_smem));
 
   // 32-wide heads and sequences up to 256 tokens (MiniLM-class) run on the tcgen05 attention kernel;
-  // other shapes use the mma.sync one.  B200_ATTENTION=legacy forces the latter (A/B timing).
-  const char* att_env = getenv("B200_ATTENTION");
-  const bool use_att_tc = dh == ATT_DH && seq <= ATT_MAX_S && seq % 32 == 0 && !(att_env && strcmp(att_env, "legacy") == 0);
+  // other shapes use the mma.sync one.  Option attention_tc=0 forces the latter (A/B timing).
+  const bool use_att_tc = dh == ATT_DH && seq <= ATT_MAX_S && seq % 32 == 0 && opt(OPT_ATTENTION_TC) != 0;
   const size_t att_tc_smem = ATT_SMEM_BYTES;   // alignment slack, two stages, barriers + exchange buffers
-  const char* att_exact_env = getenv("B200_ATT_EXACT_MAX");
-  const int att_exact_max = att_exact_env && atoi(att_exact_env) != 0;
+  const int att_exact_max = opt(OPT_ATT_EXACT_MAX);
   CUtensorMap map_att_q, map_att_kv, map_att_out;
   if (use_att_tc) {
     B200_TRY(make_tma_2d_bf16_plain(&map_att_out, e->ctx.p, (uint64_t)e->m_cap, (uint64_t)H, 32, ATT_DH / 2));   // one warp's rows x dims
@@ -337,17 +333,13 @@ static int run_encoder(b200_encoder* e, const int32_t* d_ids, const int32_t* d_l
     B200_CUDA(cudaFuncSetAttribute(attention_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)att_tc_smem));
   }
 
-  // hidden 384 = two 192-column tiles: residual + LayerNorm fused into the producing GEMM (B200_FUSE_LN=0 disables)
-  const char* fuse_env = getenv("B200_FUSE_LN");
-  const char* cg_env2 = getenv("B200_GEMM_CG");
-  const char* ffn_env = getenv("B200_FUSE_FFN");
-  const bool fuse_ffn = H == FFN_H && M % 256 == 0 && I % FFN_SLICE == 0 && !(ffn_env && atoi(ffn_env) == 0) &&
-                        !(cg_env2 && atoi(cg_env2) == 1);
-  const bool fuse_ln = H == 384 && M % 256 == 0 && !(fuse_env && atoi(fuse_env) == 0) && !(cg_env2 && atoi(cg_env2) == 1);
+  // hidden 384 = two 192-column tiles: residual + LayerNorm fused into the producing GEMM (option fuse_ln=0 disables)
+  const bool pair_ok = opt(OPT_GEMM_PAIR) != 0;
+  const bool fuse_ffn = H == FFN_H && M % 256 == 0 && I % FFN_SLICE == 0 && opt(OPT_FUSE_FFN) != 0 && pair_ok;
+  const bool fuse_ln = H == 384 && M % 256 == 0 && opt(OPT_FUSE_LN) != 0 && pair_ok;
   // serpentine row order: every kernel walks the rows in the opposite direction of the one before it
-  // (B200_SERPENTINE=0 disables)
-  const char* serp_env = getenv("B200_SERPENTINE");
-  const bool serp = !(serp_env && atoi(serp_env) == 0);
+  // (option serpentine=0 disables)
+  const bool serp = opt(OPT_SERPENTINE) != 0;
   int kcount = 0;
   for (int l = 0; l < e->cfg.layers; ++l) {
     LayerWeights* L = e->layers[l];
@@ -359,7 +351,7 @@ static int run_encoder(b200_encoder* e, const int32_t* d_ids, const int32_t* d_l
       AttParams ap;
       ap.S = seq; ap.H = H; ap.heads = heads; ap.n_mt = (seq + 127) / 128; ap.n_units = batch * heads * ap.n_mt;
       ap.lens = d_lens; ap.exact_max = att_exact_max; ap.reverse = serp ? (kcount++ & 1) : 0;
-      ap.no_turns = getenv("B200_ATT_NO_TURNS") && atoi(getenv("B200_ATT_NO_TURNS")) != 0;
+      ap.no_turns = opt(OPT_ATT_TURNS) == 0;
       B200_PROF("attention", 4.0 * batch * (double)seq * seq * H, 2.0 * 4.0 * n_tok * H, st);
       cudaLaunchConfig_t cfg{};
       cfg.gridDim = dim3(std::min(ap.n_units, e->num_sms));
@@ -434,6 +426,14 @@ int b200_encoder_create(const b200_encoder_config_t* cfg, int device, b200_encod
   e->cfg = *cfg;
   e->device = device;
   cudaDeviceGetAttribute(&e->num_sms, cudaDevAttrMultiProcessorCount, device);
+  {
+    DeviceGuard g(device);
+    const int rc = e->order.init();
+    if (rc != B200_OK) {
+      delete e;
+      return rc;
+    }
+  }
   *out = e;
   return B200_OK;
 }
@@ -545,6 +545,7 @@ int b200_encode(b200_encoder_t* e, const int32_t* input_ids, const int32_t* leng
   cudaStream_t st = (cudaStream_t)stream;
   const int64_t n_tok = (int64_t)batch * seq;
   if (n_tok > (int64_t)1 << 30) B200_FAIL(B200_ERR_UNSUPPORTED, "batch*seq too large");
+  B200_TRY(e->order.enter(st));
   B200_TRY(ensure_activations(e, n_tok, batch, st));
   const int32_t* d_ids = input_ids;
   const int32_t* d_lens = lengths;
@@ -566,10 +567,9 @@ int b200_encode(b200_encoder_t* e, const int32_t* input_ids, const int32_t* leng
     default: B200_FAIL(B200_ERR_UNSUPPORTED, "hidden=%d is not instantiated (128,256,384,512,768,1024)", e->cfg.hidden);
   }
   B200_TRY(rc);
-  if (!out_on_device) {
-    B200_CUDA(cudaMemcpyAsync(out, d_out, (size_t)batch * e->cfg.hidden * 4, cudaMemcpyDeviceToHost, st));
-    B200_CUDA(cudaStreamSynchronize(st));
-  }
+  if (!out_on_device) B200_CUDA(cudaMemcpyAsync(out, d_out, (size_t)batch * e->cfg.hidden * 4, cudaMemcpyDeviceToHost, st));
+  B200_TRY(e->order.leave(st));
+  if (!out_on_device) B200_CUDA(cudaStreamSynchronize(st));
   return B200_OK;
 }
 
@@ -604,10 +604,11 @@ extern "C" int b200_debug_att_timing(unsigned long long* out) {
 
 #ifdef B200_GEMM_TIMING
 extern "C" int b200_debug_gemm_timing(unsigned long long* out) {
+  const unsigned long long flag = out[7];   // the caller passes the experiment flag in through out[7]
   cudaDeviceSynchronize();
   cudaMemcpyFromSymbol(out, b200::g_gemm_timing, 8 * sizeof(unsigned long long));
   unsigned long long z[8] = {0};
-  z[7] = getenv("B200_GEMM_NOEPI") ? (unsigned long long)atoi(getenv("B200_GEMM_NOEPI")) : 0;
+  z[7] = flag;
   cudaMemcpyToSymbol(b200::g_gemm_timing, z, sizeof(z));
   return 0;
 }

@@ -93,7 +93,35 @@ struct DevBuf {
   T* as() const { return reinterpret_cast<T*>(p); }
 };
 
-// 2-D bf16 row-major tensor [rows, cols] -> TMA descriptor with a {box_cols, box_rows} box and
+// Orders the GPU work of successive calls on one handle when they arrive on different streams.  Every
+// handle owns one set of scratch buffers; the handle's mutex serialises the host side of the calls, but
+// with device buffers a call returns while its kernels are still queued, so a second call on another
+// stream could otherwise run over the first one's scratch.  enter() makes the new stream wait for the
+// previous call's last kernel (a no-op when the stream is the same), leave() marks the end of this call.
+struct StreamOrder {
+  cudaEvent_t ev = nullptr;
+  cudaStream_t last = nullptr;
+  bool used = false;
+  int init() {
+    B200_CUDA(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+    return B200_OK;
+  }
+  int enter(cudaStream_t st) {
+    if (used && last != st) B200_CUDA(cudaStreamWaitEvent(st, ev, 0));
+    return B200_OK;
+  }
+  int leave(cudaStream_t st) {
+    B200_CUDA(cudaEventRecord(ev, st));
+    last = st;
+    used = true;
+    return B200_OK;
+  }
+  ~StreamOrder() {
+    if (ev) cudaEventDestroy(ev);
+  }
+};
+
+// 2-D 16-bit row-major tensor [rows, cols] -> TMA descriptor with a {box_cols, box_rows} box and
 // 128-byte swizzle (box_cols must be 64 bf16 = 128 bytes).  Out-of-bounds elements read as zero.
 int make_tma_2d_bf16(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint32_t box_rows,
                      uint32_t box_cols);
@@ -107,6 +135,29 @@ int make_tma_2d_bf16_plain(CUtensorMap* out, const void* base, uint64_t rows, ui
                            uint32_t box_cols);
 
 int check_device_is_sm100(int device);
+
+// Process-wide switches between kernel variants (b200_set_option / b200_get_option in the C ABI).
+// They exist for A/B timing and for the tests that drive every alternative path against the oracle;
+// the library never reads the environment (the reference's adapters are pinned not to:
+// adapters/copilot_vectorstore/tests/test_factory.py:75-107, scripts/check_no_runtime_env_vars.py:6-16).
+enum Option {
+  OPT_PDL = 0,            // 1: programmatic dependent launch between the encoder's kernels          (default 0)
+  OPT_GEMM_PAIR,          // 0: single-CTA GEMM tiles instead of CTA pairs                            (default 1)
+  OPT_GEMM_AST,           // 0: generic GEMM instead of the A-stationary one for K <= 384            (default 1)
+  OPT_ATTENTION_TC,       // 0: mma.sync attention instead of the tcgen05 one                         (default 1)
+  OPT_ATT_EXACT_MAX,      // 1: exact row-maximum pass for every softmax row                          (default 0)
+  OPT_ATT_TURNS,          // 0: softmax groups free-running instead of taking turns on the SFU        (default 1)
+  OPT_ATT_POLY,           // of every 8 exponentials, how many run on the FMA pipe (0..8)            (default set in encoder.cu)
+  OPT_FUSE_LN,            // 0: separate LayerNorm kernel                                             (default 1)
+  OPT_FUSE_FFN,           // 0: FFN1 / FFN2 as two GEMMs                                              (default 1)
+  OPT_SERPENTINE,         // 0: every kernel walks the rows in the same direction                     (default 1)
+  OPT_SIM_PAIR,           // 0: single-CTA similarity tiles even with two or more query tiles        (default 1)
+  OPT_SIM_BOUND,          // bit 0: cross-CTA bucket bound, bit 1: single-CTA stand-in bound          (default 3)
+  OPT_SIM_REFRESH_MASK,   // the shared bounds are re-read every (mask + 1) tiles                     (default 0)
+  OPT_SEARCH_CERTIFY,     // 0: skip the candidate-sufficiency certificate and its exhaustive re-run  (default 1)
+  OPT_COUNT
+};
+int opt(Option o);
 
 // Optional per-kernel timing (off by default): when enabled through b200_profile_enable, each
 // launch site brackets its kernel with a pair of CUDA events on the launching stream;

@@ -12,6 +12,7 @@
 //                                  exact fp32 rescoring of the KP survivors per query
 //   cand    u64 [nq, nsplit, KP]   per-split candidate keys (scratch between K8 and K9)
 #include <algorithm>
+#include <atomic>
 #include <vector>
 
 #include "host_util.h"
@@ -113,6 +114,24 @@ int check_device_is_sm100(int device) {
   return B200_OK;
 }
 
+// ---- kernel-variant switches (b200_set_option) ---------------------------------------------------
+struct OptDef { const char* name; int def, lo, hi; };
+static const OptDef kOptDefs[OPT_COUNT] = {
+    {"pdl", 0, 0, 1},           {"gemm_pair", 1, 0, 1},      {"gemm_ast", 1, 0, 1},   {"attention_tc", 1, 0, 1},
+    {"att_exact_max", 0, 0, 1}, {"att_turns", 1, 0, 1},      {"att_poly", 0, 0, 8},   {"fuse_ln", 1, 0, 1},
+    {"fuse_ffn", 1, 0, 1},      {"serpentine", 1, 0, 1},     {"sim_pair", 1, 0, 1},   {"sim_bound", 3, 0, 3},
+    {"sim_refresh_mask", 0, 0, 1023}, {"search_certify", 1, 0, 1},
+};
+static std::atomic<int> g_opts[OPT_COUNT];
+static std::once_flag g_opts_once;
+static void opts_init() {
+  std::call_once(g_opts_once, [] { for (int i = 0; i < OPT_COUNT; ++i) g_opts[i].store(kOptDefs[i].def, std::memory_order_relaxed); });
+}
+int opt(Option o) {
+  opts_init();
+  return g_opts[o].load(std::memory_order_relaxed);
+}
+
 // ---- optional per-kernel timing ----------------------------------------------------------------
 struct ProfRec {
   const char* name;
@@ -147,9 +166,15 @@ using namespace b200;
 struct b200_index {
   int dim = 0, dpad = 0, device = 0, master_dtype = 0, num_sms = 148;
   int64_t count = 0, capacity = 0;
-  DevBuf search, master, stage, q_bf16, q_f32, cand, gbkt, out_ids, out_scores, tmp;
+  DevBuf search, master, stage, q16, q_f32, qmeta, cand, gbkt, out_ids, out_scores, tmp;
+  // certificate state: persist[0] = rvmax (float bits), persist[2..3] / [4..5] = the two 64-bit counters
+  // of b200_index_certificate_stats; cert = [fail_count][pad to 64 B][ticket nq][fail_idx nq] per search
+  DevBuf persist, cert, exact_part;
+  StreamOrder order;
   std::mutex mu;
   size_t master_elt() const { return master_dtype == B200_INDEX_MASTER_BF16 ? 2 : 4; }
+  uint32_t* rvmax() const { return persist.as<uint32_t>(); }
+  unsigned long long* stats() const { return reinterpret_cast<unsigned long long*>(persist.as<uint8_t>() + 8); }
 };
 
 static constexpr int64_t kMaxRows = (int64_t)1 << 31;  // row ids are uint32 on the device, 2^32-1 is "no row"
@@ -226,10 +251,8 @@ static int launch_sim(b200_index* ix, int nq, int nqt, const CUtensorMap& map_q,
   p.a_stream = a_stream;
   p.cand = ix->cand.as<uint64_t>(); p.gbkt = ix->gbkt.as<uint32_t>(); p.use_bound = nsplit >= KP;
   p.gthr = ix->gbkt.as<uint32_t>() + (size_t)nqt * SIM_BLOCK_M * KP;
-  p.refresh_mask = 0; p.use_gthr = 1; p.split_major = 0;
-  if (const char* e = getenv("B200_SIM_REFRESH")) p.refresh_mask = (uint32_t)atoi(e);   // tuning knobs (benchmarks only)
-  if (const char* e = getenv("B200_SIM_BOUND")) { const int m = atoi(e); p.use_bound = (m & 1) && nsplit >= KP; p.use_gthr = (m >> 1) & 1; p.split_major = (m >> 2) & 1; }
-  if (CG == 2) p.split_major = 0;
+  p.refresh_mask = (uint32_t)opt(OPT_SIM_REFRESH_MASK); p.split_major = 0;
+  { const int m = opt(OPT_SIM_BOUND); p.use_bound = (m & 1) && nsplit >= KP; p.use_gthr = (m >> 1) & 1; }
   auto kern = sim_topk_kernel<BLOCK_N, KP, CG>;
   B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   {
@@ -258,28 +281,60 @@ static int launch_sim(b200_index* ix, int nq, int nqt, const CUtensorMap& map_q,
   return B200_OK;
 }
 
+// bound on the evaluation error of the two scores the certificate compares: the tensor cores' fp32
+// accumulation of d products (<= 2^-23 relative per addition, doubled) and the canonical fp32 routine
+static float certificate_slop(int d) { return (float)d * 2.384185791015625e-7f + (float)(d / 32 + 16) * 1.1920929e-7f + 1e-6f; }
+
+// exact_topk_kernel over the fail list of the K9 launch just issued (or, with fail == nullptr, over all nq queries)
+template <int METRIC_L2>
+static int launch_exact(b200_index* ix, const uint32_t* fail_count, const int32_t* fail_idx, uint32_t* ticket, int nq,
+                        const float* q_f32, int k, int64_t id_base, int64_t* ids_dev, float* sc_dev, cudaStream_t st) {
+  const int grid = ix->num_sms;
+  B200_TRY(ix->exact_part.grow((size_t)2 * grid * EXACT_KEEP * 8, 0, st));
+  ExactParams e{};
+  e.fail_count = fail_count; e.fail_idx = fail_idx; e.nq = nq; e.q_f32 = q_f32;
+  e.master = ix->master.p; e.master_is_bf16 = ix->master_dtype == B200_INDEX_MASTER_BF16;
+  e.n_rows = (uint32_t)ix->count; e.d = ix->dim; e.k = k; e.id_base = id_base;
+  e.part = ix->exact_part.as<uint64_t>(); e.ticket = ticket; e.out_ids = ids_dev; e.out_scores = sc_dev;
+  const size_t smem = (size_t)EXACT_MERGE * 8 + (size_t)ix->dim * 4;
+  auto kern = exact_topk_kernel<METRIC_L2>;
+  B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  {
+    B200_PROF(METRIC_L2 ? "exact_l2" : "exact_topk", 0.0, 0.0, st);
+    kern<<<grid, EXACT_THREADS, smem, st>>>(e);
+  }
+  B200_CUDA(cudaGetLastError());
+  return B200_OK;
+}
+
 static int search_chunk(b200_index* ix, const void* q_dev, int q_dtype, int nq, int k, int kp, int64_t id_base,
                         int64_t* ids_dev, float* sc_dev, cudaStream_t st) {
   int nqt = (nq + SIM_BLOCK_M - 1) / SIM_BLOCK_M;
   // CTA pairs (two query tiles per cluster) for k <= 10 once there are at least two query tiles; an odd
-  // tile count is padded with an empty tile.  B200_SIM_CG=1 forces single-CTA tiles (A/B timing).
-  const char* cg_env = getenv("B200_SIM_CG");
-  const bool pair = kp == 16 && nqt >= 2 && !(cg_env && atoi(cg_env) == 1);
+  // tile count is padded with an empty tile.  Option sim_pair=0 forces single-CTA tiles (A/B timing).
+  const bool pair = kp == 16 && nqt >= 2 && opt(OPT_SIM_PAIR) != 0;
   if (pair) nqt = (nqt + 1) & ~1;
   const int nq_pad = nqt * SIM_BLOCK_M;
-  B200_TRY(ix->q_bf16.grow((size_t)nq_pad * ix->dpad * 2, 0, st));
+  B200_TRY(ix->q16.grow((size_t)nq_pad * ix->dpad * 2, 0, st));
   B200_TRY(ix->q_f32.grow((size_t)nq * ix->dim * 4, 0, st));
+  B200_TRY(ix->qmeta.grow((size_t)nq * 8, 0, st));
+  const bool certify = opt(OPT_SEARCH_CERTIFY) != 0;
+  const size_t cert_bytes = 64 + (size_t)nq * 8;
+  if (certify) {
+    B200_TRY(ix->cert.grow(cert_bytes, 0, st));
+    B200_CUDA(cudaMemsetAsync(ix->cert.p, 0, 64 + (size_t)nq * 4, st));   // fail_count and the tickets
+  }
   const int wpb = 8;
   if (q_dtype == 0)
     prep_queries_kernel<float><<<(nq_pad + wpb - 1) / wpb, wpb * 32, 0, st>>>(
-        (const float*)q_dev, nq, nq_pad, ix->dim, ix->dpad, ix->q_bf16.as<__nv_bfloat16>(), ix->q_f32.as<float>());
+        (const float*)q_dev, nq, nq_pad, ix->dim, ix->dpad, ix->q16.as<__half>(), ix->q_f32.as<float>(), ix->qmeta.as<float2>());
   else
     prep_queries_kernel<__nv_bfloat16><<<(nq_pad + wpb - 1) / wpb, wpb * 32, 0, st>>>(
-        (const __nv_bfloat16*)q_dev, nq, nq_pad, ix->dim, ix->dpad, ix->q_bf16.as<__nv_bfloat16>(), ix->q_f32.as<float>());
+        (const __nv_bfloat16*)q_dev, nq, nq_pad, ix->dim, ix->dpad, ix->q16.as<__half>(), ix->q_f32.as<float>(), ix->qmeta.as<float2>());
   B200_CUDA(cudaGetLastError());
 
   CUtensorMap map_q;
-  B200_TRY(make_tma_2d_bf16(&map_q, ix->q_bf16.p, (uint64_t)nq_pad, (uint64_t)ix->dpad, SIM_BLOCK_M, SIM_BLOCK_K));
+  B200_TRY(make_tma_2d_bf16(&map_q, ix->q16.p, (uint64_t)nq_pad, (uint64_t)ix->dpad, SIM_BLOCK_M, SIM_BLOCK_K));
   int nsplit = 0;
   if (pair) B200_TRY((launch_sim<256, 16, 2>(ix, nq, nqt, map_q, st, &nsplit)));
   else if (kp == 16) B200_TRY((launch_sim<256, 16, 1>(ix, nq, nqt, map_q, st, &nsplit)));
@@ -295,7 +350,12 @@ static int search_chunk(b200_index* ix, const void* q_dev, int q_dtype, int nq, 
   m.cand = ix->cand.as<uint64_t>();
   m.q_f32 = ix->q_f32.as<float>(); m.master = ix->master.p;
   m.master_is_bf16 = ix->master_dtype == B200_INDEX_MASTER_BF16;
-  m.out_ids = ids_dev; m.out_scores = sc_dev; m.out_margin = nullptr;
+  m.out_ids = ids_dev; m.out_scores = sc_dev;
+  uint32_t* fail_count = certify ? ix->cert.as<uint32_t>() : nullptr;
+  uint32_t* ticket = certify ? ix->cert.as<uint32_t>() + 16 : nullptr;
+  int32_t* fail_idx = certify ? reinterpret_cast<int32_t*>(ticket + nq) : nullptr;
+  m.qmeta = ix->qmeta.as<float2>(); m.rvmax = ix->rvmax(); m.slop = certificate_slop(ix->dpad);
+  m.fail_count = fail_count; m.fail_idx = fail_idx; m.stats = ix->stats();
   const size_t msmem = (size_t)pow2 * 8 + (size_t)((ix->dim + 1) & ~1) * 4 + 64 * 8;
   B200_CUDA(cudaFuncSetAttribute(merge_rescore_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)msmem));
   {
@@ -303,6 +363,9 @@ static int search_chunk(b200_index* ix, const void* q_dev, int q_dtype, int nq, 
     merge_rescore_kernel<<<nq, 256, msmem, st>>>(m);
   }
   B200_CUDA(cudaGetLastError());
+  // queries the certificate turned down are redone exactly; the kernel returns at once when there are none
+  if (certify)
+    B200_TRY(launch_exact<0>(ix, fail_count, fail_idx, ticket, nq, ix->q_f32.as<float>(), k, id_base, ids_dev, sc_dev, st));
   return B200_OK;
 }
 
@@ -336,6 +399,30 @@ extern "C" {
 
 const char* b200_last_error(void) { return b200::get_error(); }
 int b200_version(void) { return 100; }
+
+int b200_set_option(const char* name, int value) {
+  if (!name) B200_FAIL(B200_ERR_INVALID, "option name is NULL");
+  opts_init();
+  for (int i = 0; i < OPT_COUNT; ++i) {
+    if (strcmp(name, kOptDefs[i].name) != 0) continue;
+    if (value < kOptDefs[i].lo || value > kOptDefs[i].hi)
+      B200_FAIL(B200_ERR_INVALID, "option '%s' takes %d..%d, got %d", name, kOptDefs[i].lo, kOptDefs[i].hi, value);
+    g_opts[i].store(value, std::memory_order_relaxed);
+    return B200_OK;
+  }
+  B200_FAIL(B200_ERR_INVALID, "unknown option '%s'", name);
+}
+
+int b200_get_option(const char* name, int* value) {
+  if (!name || !value) B200_FAIL(B200_ERR_INVALID, "NULL argument");
+  opts_init();
+  for (int i = 0; i < OPT_COUNT; ++i) {
+    if (strcmp(name, kOptDefs[i].name) != 0) continue;
+    *value = g_opts[i].load(std::memory_order_relaxed);
+    return B200_OK;
+  }
+  B200_FAIL(B200_ERR_INVALID, "unknown option '%s'", name);
+}
 
 int b200_profile_enable(int on) {
   std::lock_guard<std::mutex> lk(g_prof_mu);
@@ -408,6 +495,9 @@ int b200_index_create(int dim, int64_t capacity, int device, int master_dtype, b
   ix->master_dtype = master_dtype;
   cudaDeviceGetAttribute(&ix->num_sms, cudaDevAttrMultiProcessorCount, device);
   int rc = index_reserve_locked(ix, std::max<int64_t>(capacity, 1024), 0);
+  if (rc == B200_OK) rc = ix->persist.alloc(64);
+  if (rc == B200_OK && cudaMemset(ix->persist.p, 0, 64) != cudaSuccess) { set_error("cudaMemset failed"); rc = B200_ERR_CUDA; }
+  if (rc == B200_OK) rc = ix->order.init();
   if (rc != B200_OK) {
     delete ix;
     return rc;
@@ -450,6 +540,7 @@ int b200_index_add(b200_index_t* ix, const void* rows, int64_t n, int rows_on_de
   std::lock_guard<std::mutex> lk(ix->mu);
   DeviceGuard g(ix->device);
   cudaStream_t st = (cudaStream_t)stream;
+  B200_TRY(ix->order.enter(st));
   B200_TRY(index_reserve_locked(ix, ix->count + n, st));
   const size_t elt = ix->master_elt();
   const void* src = rows;
@@ -462,17 +553,18 @@ int b200_index_add(b200_index_t* ix, const void* rows, int64_t n, int rows_on_de
   const unsigned grid = (unsigned)((n + wpb - 1) / wpb);
   if (ix->master_dtype == B200_INDEX_MASTER_F32) {
     if (ix->dim == ix->dpad && (ix->dim % 8) == 0 && ((uintptr_t)src % 16) == 0)
-      ingest_rows_f32_vec_kernel<<<grid, wpb * 32, 0, st>>>((const float*)src, n, ix->dim,
-                                                           ix->search.as<__nv_bfloat16>(), ix->count, ix->master.as<float>());
+      ingest_rows_f32_vec_kernel<<<grid, wpb * 32, 0, st>>>((const float*)src, n, ix->dim, ix->search.as<__half>(),
+                                                           ix->count, ix->master.as<float>(), ix->rvmax());
     else
-      ingest_rows_kernel<float><<<grid, wpb * 32, 0, st>>>((const float*)src, n, ix->dim, ix->dpad,
-                                                           ix->search.as<__nv_bfloat16>(), ix->count, ix->master.as<float>());
+      ingest_rows_kernel<float><<<grid, wpb * 32, 0, st>>>((const float*)src, n, ix->dim, ix->dpad, ix->search.as<__half>(),
+                                                           ix->count, ix->master.as<float>(), ix->rvmax());
   } else {
     ingest_rows_kernel<__nv_bfloat16><<<grid, wpb * 32, 0, st>>>((const __nv_bfloat16*)src, n, ix->dim, ix->dpad,
-                                                                  ix->search.as<__nv_bfloat16>(), ix->count,
-                                                                  ix->master.as<__nv_bfloat16>());
+                                                                  ix->search.as<__half>(), ix->count,
+                                                                  ix->master.as<__nv_bfloat16>(), ix->rvmax());
   }
   B200_CUDA(cudaGetLastError());
+  B200_TRY(ix->order.leave(st));
   if (!rows_on_device) B200_CUDA(cudaStreamSynchronize(st));  // the staging buffer and the caller's rows are reusable
   ix->count += n;
   return B200_OK;
@@ -489,6 +581,7 @@ int b200_index_remove_rows(b200_index_t* ix, const int64_t* rows, int64_t n, voi
   }
   DeviceGuard g(ix->device);
   cudaStream_t st = (cudaStream_t)stream;
+  B200_TRY(ix->order.enter(st));
   const size_t sb = (size_t)ix->dpad * 2, mb = (size_t)ix->dim * ix->master_elt();
   int64_t dst = rows[0];
   for (int64_t i = 0; i < n; ++i) {
@@ -498,6 +591,7 @@ int b200_index_remove_rows(b200_index_t* ix, const int64_t* rows, int64_t n, voi
     B200_TRY(move_rows_down(ix->master.as<uint8_t>(), mb, dst, seg0, seg1 - seg0, ix->tmp, st));
     dst += seg1 - seg0;
   }
+  B200_TRY(ix->order.leave(st));
   ix->count -= n;
   return B200_OK;
 }
@@ -511,6 +605,7 @@ int b200_index_get_rows(b200_index_t* ix, const int64_t* rows, int64_t n, float*
     if (rows[i] < 0 || rows[i] >= ix->count) B200_FAIL(B200_ERR_NOT_FOUND, "row %lld not found (count %lld)", (long long)rows[i], (long long)ix->count);
   DeviceGuard g(ix->device);
   cudaStream_t st = (cudaStream_t)stream;
+  B200_TRY(ix->order.enter(st));
   const size_t idx_bytes = ((size_t)n * 8 + 255) / 256 * 256;
   const size_t out_bytes = (size_t)n * ix->dim * 4;
   B200_TRY(ix->stage.grow(idx_bytes + (out_on_device ? 0 : out_bytes), 0, st));
@@ -523,6 +618,7 @@ int b200_index_get_rows(b200_index_t* ix, const int64_t* rows, int64_t n, float*
     gather_rows_kernel<__nv_bfloat16, float><<<(unsigned)n, 128, 0, st>>>(ix->master.as<__nv_bfloat16>(), d_rows, n, ix->dim, d_out);
   B200_CUDA(cudaGetLastError());
   if (!out_on_device) B200_CUDA(cudaMemcpyAsync(out, d_out, out_bytes, cudaMemcpyDeviceToHost, st));
+  B200_TRY(ix->order.leave(st));
   B200_CUDA(cudaStreamSynchronize(st));
   return B200_OK;
 }
@@ -587,6 +683,7 @@ int b200_index_search(b200_index_t* ix, const void* queries, int q_dtype, int qu
   DeviceGuard g(ix->device);
   cudaStream_t st = (cudaStream_t)stream;
   const size_t qelt = q_dtype == 0 ? 4 : 2;
+  B200_TRY(ix->order.enter(st));
 
   int64_t* d_ids = ids;
   float* d_sc = scores;
@@ -619,8 +716,68 @@ int b200_index_search(b200_index_t* ix, const void* queries, int q_dtype, int qu
   if (!out_on_device) {
     B200_CUDA(cudaMemcpyAsync(ids, d_ids, (size_t)nq * k * 8, cudaMemcpyDeviceToHost, st));
     B200_CUDA(cudaMemcpyAsync(scores, d_sc, (size_t)nq * k * 4, cudaMemcpyDeviceToHost, st));
-    B200_CUDA(cudaStreamSynchronize(st));
   }
+  B200_TRY(ix->order.leave(st));
+  if (!out_on_device) B200_CUDA(cudaStreamSynchronize(st));
+  return B200_OK;
+}
+
+int b200_index_certificate_stats(b200_index_t* ix, int64_t* checked, int64_t* recomputed) {
+  if (!ix || !checked || !recomputed) B200_FAIL(B200_ERR_INVALID, "NULL argument");
+  std::lock_guard<std::mutex> lk(ix->mu);
+  DeviceGuard g(ix->device);
+  unsigned long long h[2] = {0, 0};
+  B200_CUDA(cudaDeviceSynchronize());
+  B200_CUDA(cudaMemcpy(h, ix->stats(), sizeof(h), cudaMemcpyDeviceToHost));
+  *checked = (int64_t)h[0];
+  *recomputed = (int64_t)h[1];
+  return B200_OK;
+}
+
+int b200_index_search_l2(b200_index_t* ix, const void* queries, int q_dtype, int queries_on_device, int64_t nq, int k,
+                         int64_t id_base, int64_t* ids, float* dist, int out_on_device, void* stream) {
+  if (!ix) B200_FAIL(B200_ERR_INVALID, "index is NULL");
+  if (nq < 0 || k < 0) B200_FAIL(B200_ERR_INVALID, "negative nq / k");
+  if (nq == 0 || k == 0) return B200_OK;
+  if (!queries || !ids || !dist) B200_FAIL(B200_ERR_INVALID, "NULL buffer");
+  if (q_dtype != 0) B200_FAIL(B200_ERR_INVALID, "L2 search takes fp32 queries (q_dtype 0)");
+  if (k > EXACT_KEEP) B200_FAIL(B200_ERR_UNSUPPORTED, "k=%d: L2 search returns at most %d neighbours per query", k, EXACT_KEEP);
+  std::lock_guard<std::mutex> lk(ix->mu);
+  DeviceGuard g(ix->device);
+  cudaStream_t st = (cudaStream_t)stream;
+  B200_TRY(ix->order.enter(st));
+  int64_t* d_ids = ids;
+  float* d_sc = dist;
+  if (!out_on_device) {
+    B200_TRY(ix->out_ids.grow((size_t)nq * k * 8, 0, st));
+    B200_TRY(ix->out_scores.grow((size_t)nq * k * 4, 0, st));
+    d_ids = ix->out_ids.as<int64_t>();
+    d_sc = ix->out_scores.as<float>();
+  }
+  if (ix->count == 0) {
+    B200_CUDA(cudaMemsetAsync(d_ids, 0xFF, (size_t)nq * k * 8, st));
+    B200_CUDA(cudaMemsetAsync(d_sc, 0, (size_t)nq * k * 4, st));
+  } else {
+    const float* q_dev = (const float*)queries;
+    if (!queries_on_device) {
+      B200_TRY(ix->stage.grow((size_t)nq * ix->dim * 4, 0, st));
+      B200_CUDA(cudaMemcpyAsync(ix->stage.p, queries, (size_t)nq * ix->dim * 4, cudaMemcpyHostToDevice, st));
+      q_dev = ix->stage.as<float>();
+    }
+    for (int64_t q0 = 0; q0 < nq; q0 += kMaxQueryChunk) {
+      const int n = (int)std::min<int64_t>(kMaxQueryChunk, nq - q0);
+      B200_TRY(ix->cert.grow(64 + (size_t)n * 8, 0, st));
+      B200_CUDA(cudaMemsetAsync(ix->cert.p, 0, 64 + (size_t)n * 4, st));
+      B200_TRY(launch_exact<1>(ix, nullptr, nullptr, ix->cert.as<uint32_t>() + 16, n, q_dev + (size_t)q0 * ix->dim, k, id_base,
+                               d_ids + q0 * k, d_sc + q0 * k, st));
+    }
+  }
+  if (!out_on_device) {
+    B200_CUDA(cudaMemcpyAsync(ids, d_ids, (size_t)nq * k * 8, cudaMemcpyDeviceToHost, st));
+    B200_CUDA(cudaMemcpyAsync(dist, d_sc, (size_t)nq * k * 4, cudaMemcpyDeviceToHost, st));
+  }
+  B200_TRY(ix->order.leave(st));
+  if (!out_on_device) B200_CUDA(cudaStreamSynchronize(st));
   return B200_OK;
 }
 
@@ -752,7 +909,7 @@ extern "C" int b200_index_search_static(b200_index_t* ix, const void* queries_de
     B200_CUDA(cudaMemsetAsync(scores_dev, 0, (size_t)nq * k * 4, st));
     return B200_OK;
   }
-  __nv_bfloat16* q_bf16 = reinterpret_cast<__nv_bfloat16*>(base + kStaticOffQBf16);
+  __half* q16 = reinterpret_cast<__half*>(base + kStaticOffQBf16);
   float* q_f32 = reinterpret_cast<float*>(base + kStaticOffQF32);
   uint64_t* cand = reinterpret_cast<uint64_t*>(base + kStaticOffCand);
   uint32_t* gthr = reinterpret_cast<uint32_t*>(base + kStaticOffGthr);
@@ -765,13 +922,13 @@ extern "C" int b200_index_search_static(b200_index_t* ix, const void* queries_de
   const int n = (int)nq, nq_pad = SIM_BLOCK_M, wpb = 8;
   if (q_dtype == 0)
     prep_queries_kernel<float><<<(nq_pad + wpb - 1) / wpb, wpb * 32, 0, st>>>((const float*)queries_dev, n, nq_pad, ix->dim,
-                                                                           ix->dpad, q_bf16, q_f32);
+                                                                           ix->dpad, q16, q_f32, nullptr);
   else
     prep_queries_kernel<__nv_bfloat16><<<(nq_pad + wpb - 1) / wpb, wpb * 32, 0, st>>>(
-        (const __nv_bfloat16*)queries_dev, n, nq_pad, ix->dim, ix->dpad, q_bf16, q_f32);
+        (const __nv_bfloat16*)queries_dev, n, nq_pad, ix->dim, ix->dpad, q16, q_f32, nullptr);
   B200_CUDA(cudaGetLastError());
   CUtensorMap map_q;
-  B200_TRY(make_tma_2d_bf16(&map_q, q_bf16, (uint64_t)nq_pad, (uint64_t)ix->dpad, SIM_BLOCK_M, SIM_BLOCK_K));
+  B200_TRY(make_tma_2d_bf16(&map_q, q16, (uint64_t)nq_pad, (uint64_t)ix->dpad, SIM_BLOCK_M, SIM_BLOCK_K));
   int nsplit = 0;
   if (kp == 16) B200_TRY((launch_sim_static<256, 16>(ix, n, map_q, cand, gthr, st, &nsplit)));
   else if (kp == 32) B200_TRY((launch_sim_static<128, 32>(ix, n, map_q, cand, gthr, st, &nsplit)));
@@ -784,7 +941,8 @@ extern "C" int b200_index_search_static(b200_index_t* ix, const void* queries_de
   m.n_rows = (uint32_t)ix->count; m.id_base = id_base;
   m.cand = cand; m.q_f32 = q_f32; m.master = ix->master.p;
   m.master_is_bf16 = ix->master_dtype == B200_INDEX_MASTER_BF16;
-  m.out_ids = ids_dev; m.out_scores = scores_dev; m.out_margin = nullptr;
+  m.out_ids = ids_dev; m.out_scores = scores_dev;
+  m.qmeta = nullptr; m.rvmax = nullptr; m.slop = 0.f; m.fail_count = nullptr; m.fail_idx = nullptr; m.stats = nullptr;
   const size_t msmem = (size_t)pow2 * 8 + (size_t)((ix->dim + 1) & ~1) * 4 + 64 * 8;
   B200_CUDA(cudaFuncSetAttribute(merge_rescore_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)msmem));
   merge_rescore_kernel<<<n, 256, msmem, st>>>(m);

@@ -1,35 +1,52 @@
 // search_kernels.cuh -- device code for the cosine top-k path.
 //
-//   ingest_rows_kernel   K11  raw rows -> unit-normalised bf16 search copy (+ master copy)
-//   prep_queries_kernel        raw queries -> zero-padded bf16 tile operand + fp32 copy
+//   ingest_rows_kernel   K11  raw rows -> unit-normalised 16-bit search copy (+ master copy)
+//   prep_queries_kernel        raw queries -> zero-padded 16-bit tile operand + fp32 copy + rounding-error norm
 //   sim_topk_kernel      K8   Q x C^T on tcgen05 (TMA-fed, TMEM accumulators) with the top-KP
 //                             select fused into the TMEM drain: scores never reach HBM
 //   merge_rescore_kernel K9   per query: merge the per-split candidate lists, rescore the KP
 //                             survivors with the reference's fp32 arithmetic in the canonical
-//                             summation order (oracle/search_oracle.c), emit top-k
+//                             summation order (oracle/search_oracle.c), emit top-k; certify that no
+//                             row outside the survivors can belong to the exact top-k
+//   exact_topk_kernel          queries that fail the certificate: exact score of EVERY row
+//
+// The search copy is IEEE half (E5M10), not bf16: its elements are components of unit vectors, which
+// need mantissa, not range.  Same 2 bytes per element and the same tcgen05 kind::f16 rate, but an 8x
+// smaller rounding error -- which is what makes the rigorous candidate-sufficiency bound of K9 tight
+// enough to pass on all but a few queries in 10^5.  The caller's rows (bf16 or fp32) are kept untouched
+// in the master copy.
 //
 // Reference semantics being reproduced: InMemoryVectorStore.query,
 // adapters/copilot_vectorstore/copilot_vectorstore/inmemory.py:96-119.
 #pragma once
+#include <cuda_fp16.h>
+
 #include "common.cuh"
 
 namespace b200 {
 
 constexpr int SIM_BLOCK_M = 128;   // queries per CTA = TMEM lanes
-constexpr int SIM_BLOCK_K = 64;    // bf16 elements per 128-byte swizzle row
+constexpr int SIM_BLOCK_K = 64;    // 16-bit elements per 128-byte swizzle row
 constexpr int SIM_THREADS = 256;   // warp 0 TMA, 1 MMA, 2 TMEM alloc, 3 idle, 4..7 drain/select
 constexpr int SIM_A_CHUNK_BYTES = SIM_BLOCK_M * SIM_BLOCK_K * 2;
 constexpr uint32_t kNoRow = 0xFFFFFFFFu;
 
 // ---------------------------------------------------------------------------------------------
-// K11: one warp per row.  search[r] = bf16( x / (||x|| + 1e-8) ), zero-padded to dpad columns.
+// K11: one warp per row.  search[r] = half( x / (||x|| + 1e-8) ), zero-padded to dpad columns.
 // The search copy only has to rank candidates; exact scores come from the master copy later, so
-// the norm here is an ordinary warp-shuffle reduction.
+// the norm here is an ordinary warp-shuffle reduction.  What the exact pass does need is a bound on
+// how far the rounded row is from the unit row it stands for: rvmax <- max(rvmax, ||x*inv - half(x*inv)||_2)
+// (float bits, non-negative, so an integer atomicMax orders them; see the certificate in K9).
 // ---------------------------------------------------------------------------------------------
+B200_DEVINL void publish_row_error(float err_sq, uint32_t* rvmax) {
+  const uint32_t bits = __float_as_uint(sqrtf(err_sq) * 1.001f + 1e-9f);
+  if (bits > __ldcg(rvmax)) atomicMax(rvmax, bits);
+}
+
 template <typename TIn>
 __global__ void __launch_bounds__(256) ingest_rows_kernel(const TIn* __restrict__ in, int64_t n, int d, int dpad,
-                                                          __nv_bfloat16* __restrict__ search, int64_t row0,
-                                                          TIn* __restrict__ master) {
+                                                          __half* __restrict__ search, int64_t row0,
+                                                          TIn* __restrict__ master, uint32_t* __restrict__ rvmax) {
   const int64_t r = (int64_t)blockIdx.x * (blockDim.x / kWarp) + (threadIdx.x / kWarp);
   if (r >= n) return;
   const int lane = threadIdx.x & 31;
@@ -41,20 +58,28 @@ __global__ void __launch_bounds__(256) ingest_rows_kernel(const TIn* __restrict_
   }
   ss = warp_sum(ss);
   const float inv = 1.0f / (sqrtf(ss) + 1e-8f);
-  __nv_bfloat16* dst = search + (row0 + r) * (int64_t)dpad;
+  __half* dst = search + (row0 + r) * (int64_t)dpad;
   TIn* mdst = master ? master + (row0 + r) * (int64_t)d : nullptr;
+  float es = 0.f;
   for (int i = lane; i < dpad; i += kWarp) {
     float x = (i < d) ? static_cast<float>(src[i]) : 0.f;
-    dst[i] = __float2bfloat16_rn(x * inv);
+    const float u = x * inv;
+    const __half h = __float2half_rn(u);
+    const float e = u - __half2float(h);
+    es = fmaf(e, e, es);
+    dst[i] = h;
     if (mdst && i < d) mdst[i] = src[i];
   }
+  es = warp_sum(es);
+  if (lane == 0) publish_row_error(es, rvmax);
 }
 
 // Vectorised K11 for d % 8 == 0 and d == dpad (the 384/768-d production shapes): 16-byte loads
 // and stores, one warp per row, rows of 384 fp32 = 3 x float4 per lane.
 __global__ void __launch_bounds__(256) ingest_rows_f32_vec_kernel(const float* __restrict__ in, int64_t n, int d,
-                                                                  __nv_bfloat16* __restrict__ search, int64_t row0,
-                                                                  float* __restrict__ master) {
+                                                                  __half* __restrict__ search, int64_t row0,
+                                                                  float* __restrict__ master,
+                                                                  uint32_t* __restrict__ rvmax) {
   const int64_t r = (int64_t)blockIdx.x * (blockDim.x / kWarp) + (threadIdx.x / kWarp);
   if (r >= n) return;
   const int lane = threadIdx.x & 31;
@@ -69,46 +94,99 @@ __global__ void __launch_bounds__(256) ingest_rows_f32_vec_kernel(const float* _
   const float inv = 1.0f / (sqrtf(ss) + 1e-8f);
   uint2* dst = reinterpret_cast<uint2*>(search + (row0 + r) * (int64_t)d);
   float4* mdst = master ? reinterpret_cast<float4*>(master + (row0 + r) * (int64_t)d) : nullptr;
+  float es = 0.f;
   for (int i = lane; i < nv; i += kWarp) {
     float4 x = __ldg(src + i);
-    __nv_bfloat162 lo = __floats2bfloat162_rn(x.x * inv, x.y * inv);
-    __nv_bfloat162 hi = __floats2bfloat162_rn(x.z * inv, x.w * inv);
+    const float u0 = x.x * inv, u1 = x.y * inv, u2 = x.z * inv, u3 = x.w * inv;
+    __half2 lo = __floats2half2_rn(u0, u1);
+    __half2 hi = __floats2half2_rn(u2, u3);
+    const float2 flo = __half22float2(lo), fhi = __half22float2(hi);
+    const float e0 = u0 - flo.x, e1 = u1 - flo.y, e2 = u2 - fhi.x, e3 = u3 - fhi.y;
+    es = fmaf(e0, e0, es); es = fmaf(e1, e1, es); es = fmaf(e2, e2, es); es = fmaf(e3, e3, es);
     uint2 o;
     o.x = *reinterpret_cast<uint32_t*>(&lo);
     o.y = *reinterpret_cast<uint32_t*>(&hi);
     dst[i] = o;
     if (mdst) mdst[i] = x;
   }
+  es = warp_sum(es);
+  if (lane == 0) publish_row_error(es, rvmax);
 }
 
 // ---------------------------------------------------------------------------------------------
-// queries: raw (fp32 or bf16) -> bf16 [nq_pad, dpad] tile operand (zero padded) and fp32 [nq, d]
+// canonical fp32 arithmetic shared with oracle/search_oracle.c (bit-for-bit):
+//   element i accumulates into partial (i & 31) by fused multiply-add, ascending i; partials are
+//   folded 16, 8, 4, 2, 1.  One warp; every lane returns the same value.
+// ---------------------------------------------------------------------------------------------
+template <typename TA>
+B200_DEVINL float canon_dot_self(const TA* __restrict__ x, int d, int lane) {
+  float p = 0.f;
+  for (int i = lane; i < d; i += kWarp) {
+    const float v = static_cast<float>(x[i]);
+    p = __fmaf_rn(v, v, p);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) p = __fadd_rn(p, __shfl_xor_sync(0xffffffffu, p, o));
+  return p;
+}
+
+// score of raw row v against the already-normalised query qh (shared memory, fp32)
+template <typename TV>
+B200_DEVINL float canon_score(const float* __restrict__ qh, const TV* __restrict__ v, int d, int lane) {
+  const float den = __fadd_rn(__fsqrt_rn(canon_dot_self(v, d, lane)), 1e-8f);
+  float p = 0.f;
+  for (int i = lane; i < d; i += kWarp) {
+    const float vh = __fdiv_rn(static_cast<float>(v[i]), den);
+    p = __fmaf_rn(qh[i], vh, p);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) p = __fadd_rn(p, __shfl_xor_sync(0xffffffffu, p, o));
+  return p;
+}
+
+// ---------------------------------------------------------------------------------------------
+// queries: raw (fp32 or bf16) -> half [nq_pad, dpad] tile operand (zero padded) and fp32 [nq, d]
 // for the rescoring pass.  Queries are NOT normalised for the tensor-core pass: a positive
-// per-query scale does not change that query's ranking.  They are scaled by 1/max|q| only to keep
-// bf16 conversion away from denormals for tiny-magnitude inputs.
+// per-query scale does not change that query's ranking.  They are scaled by 1/max|q| so that the
+// half conversion neither overflows nor loses small-magnitude inputs to denormals.
+//
+// qmeta[r] = (inv_scale, r_q) for the certificate in K9:
+//   inv_scale = 1 / (sc * (||q|| + 1e-8))     tensor-core score * inv_scale = score in cosine units
+//   r_q       = || q_hat - q16 * inv_scale ||_2   distance between the query the exact pass uses
+//               (q_hat = q / (||q|| + 1e-8)) and the one the tensor cores saw, in the same units
 // ---------------------------------------------------------------------------------------------
 template <typename TIn>
 __global__ void __launch_bounds__(256) prep_queries_kernel(const TIn* __restrict__ in, int nq, int nq_pad, int d,
-                                                           int dpad, __nv_bfloat16* __restrict__ q_bf16,
-                                                           float* __restrict__ q_f32) {
+                                                           int dpad, __half* __restrict__ q16,
+                                                           float* __restrict__ q_f32, float2* __restrict__ qmeta) {
   const int r = blockIdx.x * (blockDim.x / kWarp) + (threadIdx.x / kWarp);
   if (r >= nq_pad) return;
   const int lane = threadIdx.x & 31;
-  __nv_bfloat16* dst = q_bf16 + (int64_t)r * dpad;
+  __half* dst = q16 + (int64_t)r * dpad;
   if (r >= nq) {
-    for (int i = lane; i < dpad; i += kWarp) dst[i] = __float2bfloat16_rn(0.f);
+    for (int i = lane; i < dpad; i += kWarp) dst[i] = __float2half_rn(0.f);
     return;
   }
   const TIn* src = in + (int64_t)r * d;
   float amax = 0.f;
   for (int i = lane; i < d; i += kWarp) amax = fmaxf(amax, fabsf(static_cast<float>(src[i])));
   amax = warp_max(amax);
-  const float sc = (amax > 0.f && amax < 1e-3f) ? (1.0f / amax) : 1.0f;
+  const float sc = (amax > 0.f && amax < INFINITY) ? (1.0f / amax) : 1.0f;
+  const float den = __fadd_rn(__fsqrt_rn(canon_dot_self(src, d, lane)), 1e-8f);
+  const float inv_scale = 1.0f / (sc * den);
+  float es = 0.f;
   for (int i = lane; i < dpad; i += kWarp) {
     float x = (i < d) ? static_cast<float>(src[i]) : 0.f;
-    dst[i] = __float2bfloat16_rn(x * sc);
-    if (i < d) q_f32[(int64_t)r * d + i] = x;
+    const __half h = __float2half_rn(x * sc);
+    dst[i] = h;
+    if (i < d) {
+      q_f32[(int64_t)r * d + i] = x;
+      const float e = __fdiv_rn(x, den) - __half2float(h) * inv_scale;
+      es = fmaf(e, e, es);
+    }
   }
+  es = warp_sum(es);
+  if (qmeta && lane == 0) qmeta[r] = make_float2(inv_scale, sqrtf(es) * 1.001f + 1e-9f);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -172,7 +250,7 @@ sim_topk_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant
                 const SimParams p) {
   constexpr uint32_t B_ROWS = BLOCK_N / CG;                     // corpus rows this CTA loads per tile
   constexpr uint32_t B_STAGE_BYTES = B_ROWS * SIM_BLOCK_K * 2;
-  constexpr uint32_t IDESC = umma_idesc_bf16_f32(SIM_BLOCK_M * CG, BLOCK_N);
+  constexpr uint32_t IDESC = umma_idesc_f16_f32(SIM_BLOCK_M * CG, BLOCK_N);   // half x half -> fp32
   static_assert(CG == 1 || CG == 2, "CTA group is 1 or 2");
   constexpr uint32_t TMEM_COLS = 2 * BLOCK_N;  // two accumulator stages
   static_assert(TMEM_COLS == 256 || TMEM_COLS == 512, "TMEM allocation must be a power of two");
@@ -438,37 +516,6 @@ sim_topk_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant
   }
 }
 
-// ---------------------------------------------------------------------------------------------
-// canonical fp32 arithmetic shared with oracle/search_oracle.c (bit-for-bit):
-//   element i accumulates into partial (i & 31) by fused multiply-add, ascending i; partials are
-//   folded 16, 8, 4, 2, 1.  One warp; every lane returns the same value.
-// ---------------------------------------------------------------------------------------------
-template <typename TA>
-B200_DEVINL float canon_dot_self(const TA* __restrict__ x, int d, int lane) {
-  float p = 0.f;
-  for (int i = lane; i < d; i += kWarp) {
-    const float v = static_cast<float>(x[i]);
-    p = __fmaf_rn(v, v, p);
-  }
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) p = __fadd_rn(p, __shfl_xor_sync(0xffffffffu, p, o));
-  return p;
-}
-
-// score of raw row v against the already-normalised query qh (shared memory, fp32)
-template <typename TV>
-B200_DEVINL float canon_score(const float* __restrict__ qh, const TV* __restrict__ v, int d, int lane) {
-  const float den = __fadd_rn(__fsqrt_rn(canon_dot_self(v, d, lane)), 1e-8f);
-  float p = 0.f;
-  for (int i = lane; i < d; i += kWarp) {
-    const float vh = __fdiv_rn(static_cast<float>(v[i]), den);
-    p = __fmaf_rn(qh[i], vh, p);
-  }
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) p = __fadd_rn(p, __shfl_xor_sync(0xffffffffu, p, o));
-  return p;
-}
-
 // descending bitonic sort of n (power of two) 64-bit keys in shared memory, whole CTA
 B200_DEVINL void bitonic_sort_desc(uint64_t* keys, int n) {
   for (int k = 2; k <= n; k <<= 1) {
@@ -507,7 +554,13 @@ struct MergeParams {
   int master_is_bf16;
   int64_t* out_ids;         // [nq, k]
   float* out_scores;        // [nq, k]
-  float* out_margin;        // [nq] optional: approx score of the last kept candidate (diagnostics)
+  // --- candidate-sufficiency certificate (all nullptr: skipped) ---
+  const float2* qmeta;      // [nq] (inv_scale, r_q) from prep_queries_kernel
+  const uint32_t* rvmax;    // float bits: max over rows of || unit row - its half image ||_2
+  float slop;               // bound on the fp32 accumulation / evaluation error of both scores
+  uint32_t* fail_count;     // number of queries appended to fail_idx by this launch
+  int32_t* fail_idx;        // [nq] queries whose result is NOT certified (re-run by exact_topk_kernel)
+  unsigned long long* stats;  // [2] cumulative: queries checked, queries that failed the certificate
 };
 
 __global__ void __launch_bounds__(256) merge_rescore_kernel(const MergeParams p) {
@@ -547,11 +600,34 @@ __global__ void __launch_bounds__(256) merge_rescore_kernel(const MergeParams p)
     if (lane == 0) fin[c] = pack_key(s, id);
   }
   __syncthreads();
-  if (p.out_margin && threadIdx.x == 0) {
-    const uint64_t last = keys[p.kp - 1];
-    p.out_margin[q] = last ? orderable_f32((uint32_t)(last >> 32)) : -INFINITY;
-  }
   bitonic_sort_desc(fin, 64);
+  // Certificate.  K8 ranked rows by s16(v) = q16 . v16 (tensor cores, fp32 accumulate) and every row
+  // outside the KP survivors has s16 <= A, the KP-th best.  In cosine units (x inv_scale), for any row v
+  //   exact(v) - s16(v) = q_hat.(v_hat - v16) + (q_hat - q16').v16 + (evaluation error of both sides)
+  //                    <= r_v + r_q (1 + r_v) + slop                      (Cauchy-Schwarz, |q_hat| <= 1)
+  // with r_v <= rvmax kept by the ingest kernel and r_q computed by prep_queries_kernel from the values
+  // actually used.  So no outsider can score above A + eps; if the k-th exact score among the survivors
+  // is strictly above that, the survivors contain the exact top-k, ties included.  Otherwise the query
+  // goes to exact_topk_kernel.  Fewer than KP candidates (corpus smaller than KP) or fewer than k
+  // results means every row was rescored: certified.
+  if (p.fail_count && threadIdx.x == 0) {
+    const uint64_t last = keys[p.kp - 1];
+    const uint64_t kth = fin[p.k - 1];
+    bool ok = true;
+    if (last != 0 && kth != 0) {
+      const float2 qm = p.qmeta[q];
+      const float rv = __uint_as_float(__ldcg(p.rvmax));
+      const float a_norm = orderable_f32((uint32_t)(last >> 32)) * qm.x;
+      const float eps = (rv + qm.y * (1.0f + rv) + p.slop) * 1.001f;
+      const float e_k = orderable_f32((uint32_t)(kth >> 32));
+      ok = (e_k - a_norm) > eps;   // NaN compares false: uncertified
+    }
+    atomicAdd(p.stats, 1ull);
+    if (!ok) {
+      atomicAdd(p.stats + 1, 1ull);
+      p.fail_idx[atomicAdd(p.fail_count, 1u)] = q;
+    }
+  }
   for (int j = threadIdx.x; j < p.k; j += blockDim.x) {
     const uint64_t key = (j < 64) ? fin[j] : 0;
     if (key) {
@@ -561,6 +637,164 @@ __global__ void __launch_bounds__(256) merge_rescore_kernel(const MergeParams p)
       p.out_ids[(size_t)q * p.k + j] = -1;
       p.out_scores[(size_t)q * p.k + j] = 0.f;
     }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Exact top-k for the queries K9 could not certify (near-duplicate rows whose 16-bit images tie, or a
+// k-th and KP-th neighbour closer than the rounding bound): the canonical fp32 score of EVERY row,
+// i.e. exactly what the oracle computes, so the result is bit-identical by construction.  Launched
+// after every K9 with a fixed grid; *fail_count == 0 (the common case) makes it return at once, so
+// the query path needs no host round trip to decide.  One master-copy pass per failed query.
+//
+// Each warp scores rows blockIdx.x * nwarp + warp, + gridDim.x * nwarp, ... and keeps its best 64 keys
+// (two per lane; a candidate replaces the warp's minimum, found again with a butterfly).  A CTA then
+// sorts its warps' keys and writes its best 64; the last CTA to finish a query (atomic ticket) folds
+// the gridDim.x lists 63 at a time and writes the k results.  METRIC_L2 = 1 scores by squared Euclidean
+// distance instead (see exact_l2 below); keys order "better first" either way.
+// ---------------------------------------------------------------------------------------------
+constexpr int EXACT_THREADS = 512;
+constexpr int EXACT_KEEP = 64;
+constexpr int EXACT_MERGE = 4096;
+
+struct ExactParams {
+  const uint32_t* fail_count;   // nullptr: run all nq queries (query j = j)
+  const int32_t* fail_idx;
+  int nq;                       // upper bound on *fail_count / number of queries when fail_count is nullptr
+  const float* q_f32;           // [nq_total, d] raw queries
+  const void* master;
+  int master_is_bf16;
+  uint32_t n_rows;
+  int d, k;
+  int64_t id_base;
+  uint64_t* part;               // [2][gridDim.x][EXACT_KEEP] scratch, alternating between consecutive queries
+  uint32_t* ticket;             // [nq] zeroed before the launch; gridDim.x + 1 = that query's result is written
+  int64_t* out_ids;
+  float* out_scores;
+};
+
+// FAISS IndexFlatL2 semantics (faiss_store.py:99-101,212-224): squared Euclidean distance, ascending; the
+// store converts it to a score 1/(1+d).  Canonical order: element i -> partial i & 31 by fused multiply-add of
+// the difference with itself, halving tree -- shared with oracle/search_oracle.c (l2 entry points).
+template <typename TV>
+B200_DEVINL float canon_l2(const float* __restrict__ q, const TV* __restrict__ v, int d, int lane) {
+  float p = 0.f;
+  for (int i = lane; i < d; i += kWarp) {
+    const float t = __fsub_rn(q[i], static_cast<float>(v[i]));
+    p = __fmaf_rn(t, t, p);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) p = __fadd_rn(p, __shfl_xor_sync(0xffffffffu, p, o));
+  return p;
+}
+
+B200_DEVINL uint64_t shfl_xor_u64(uint64_t v, int o) {
+  const uint32_t lo = __shfl_xor_sync(0xffffffffu, (uint32_t)v, o);
+  const uint32_t hi = __shfl_xor_sync(0xffffffffu, (uint32_t)(v >> 32), o);
+  return ((uint64_t)hi << 32) | lo;
+}
+
+template <int METRIC_L2>
+__global__ void __launch_bounds__(EXACT_THREADS) exact_topk_kernel(const ExactParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint64_t* mkeys = reinterpret_cast<uint64_t*>(smem_raw);                  // [EXACT_MERGE]
+  float* qh = reinterpret_cast<float*>(mkeys + EXACT_MERGE);                // [d]
+  __shared__ float s_den;
+  __shared__ uint32_t s_last;
+  const int nfail = p.fail_count ? (int)min(__ldcg(p.fail_count), (uint32_t)p.nq) : p.nq;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
+  for (int j = 0; j < nfail; ++j) {
+    const int q = p.fail_count ? p.fail_idx[j] : j;
+    const float* qraw = p.q_f32 + (size_t)q * p.d;
+    if (METRIC_L2) {
+      for (int i = threadIdx.x; i < p.d; i += blockDim.x) qh[i] = qraw[i];
+    } else {
+      if (warp == 0) {
+        const float den = __fadd_rn(__fsqrt_rn(canon_dot_self(qraw, p.d, lane)), 1e-8f);
+        if (lane == 0) s_den = den;
+      }
+      __syncthreads();
+      for (int i = threadIdx.x; i < p.d; i += blockDim.x) qh[i] = __fdiv_rn(qraw[i], s_den);
+    }
+    __syncthreads();
+    // --- this warp's rows ---
+    uint64_t k0 = 0, k1 = 0, wmin = 0;       // two kept keys per lane; wmin = the smallest of the 64
+    for (uint32_t row = blockIdx.x * nwarp + warp; row < p.n_rows; row += gridDim.x * nwarp) {
+      float s;
+      if (METRIC_L2) {
+        s = p.master_is_bf16 ? canon_l2(qh, reinterpret_cast<const __nv_bfloat16*>(p.master) + (size_t)row * p.d, p.d, lane)
+                             : canon_l2(qh, reinterpret_cast<const float*>(p.master) + (size_t)row * p.d, p.d, lane);
+        s = -s;                                // smaller distance = better
+      } else {
+        s = p.master_is_bf16 ? canon_score(qh, reinterpret_cast<const __nv_bfloat16*>(p.master) + (size_t)row * p.d, p.d, lane)
+                             : canon_score(qh, reinterpret_cast<const float*>(p.master) + (size_t)row * p.d, p.d, lane);
+      }
+      const uint64_t key = pack_key(s, row);
+      if (key > wmin) {
+        // replace one occurrence of the minimum (empty slots are 0 = the minimum until the set is full)
+        const uint32_t has0 = __ballot_sync(0xffffffffu, k0 == wmin);
+        const uint32_t has1 = __ballot_sync(0xffffffffu, k1 == wmin);
+        if (has0) { if (lane == __ffs(has0) - 1) k0 = key; }
+        else if (lane == __ffs(has1) - 1) k1 = key;
+        uint64_t m = k0 < k1 ? k0 : k1;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+          const uint64_t other = shfl_xor_u64(m, o);
+          m = other < m ? other : m;
+        }
+        wmin = m;
+      }
+    }
+    // --- CTA: best 64 of the warps' keys ---
+    for (int i = threadIdx.x; i < EXACT_MERGE; i += blockDim.x) mkeys[i] = 0;
+    __syncthreads();
+    mkeys[warp * 64 + lane] = k0;
+    mkeys[warp * 64 + 32 + lane] = k1;
+    __syncthreads();
+    bitonic_sort_desc(mkeys, 1024);            // nwarp * 64 <= 1024
+    // the list buffer of query j was last used by query j - 2: wait until that one has been folded
+    // (the CTA doing it already holds its ticket, i.e. is running, so this cannot deadlock)
+    if (j >= 2 && threadIdx.x == 0) {
+      const volatile uint32_t* t2 = p.ticket + (j - 2);
+      while (*t2 != gridDim.x + 1) __nanosleep(200);
+      __threadfence();
+    }
+    __syncthreads();
+    uint64_t* part = p.part + (size_t)(j & 1) * gridDim.x * EXACT_KEEP;
+    if (threadIdx.x < EXACT_KEEP) part[(size_t)blockIdx.x * EXACT_KEEP + threadIdx.x] = mkeys[threadIdx.x];
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) s_last = (atomicAdd(p.ticket + j, 1u) == gridDim.x - 1) ? 1u : 0u;
+    __syncthreads();
+    if (s_last) {
+      __threadfence();
+      // fold the per-CTA lists: carry (64 keys) + up to 63 lists per round
+      for (int i = threadIdx.x; i < EXACT_KEEP; i += blockDim.x) mkeys[i] = 0;
+      for (uint32_t c0 = 0; c0 < gridDim.x; c0 += 63) {
+        const uint32_t nc = min(63u, gridDim.x - c0);
+        for (int i = threadIdx.x; i < 63 * EXACT_KEEP; i += blockDim.x)
+          mkeys[EXACT_KEEP + i] = (uint32_t)i < nc * EXACT_KEEP ? __ldcg(part + (size_t)c0 * EXACT_KEEP + i) : 0ull;
+        __syncthreads();
+        bitonic_sort_desc(mkeys, EXACT_MERGE);
+      }
+      for (int t = threadIdx.x; t < p.k; t += blockDim.x) {
+        const uint64_t key = t < EXACT_KEEP ? mkeys[t] : 0ull;
+        if (key) {
+          p.out_ids[(size_t)q * p.k + t] = p.id_base + (int64_t)(~(uint32_t)(key & 0xFFFFFFFFu));
+          const float sc = orderable_f32((uint32_t)(key >> 32));
+          p.out_scores[(size_t)q * p.k + t] = METRIC_L2 ? -sc : sc;
+        } else {
+          p.out_ids[(size_t)q * p.k + t] = -1;
+          p.out_scores[(size_t)q * p.k + t] = 0.f;
+        }
+      }
+      __syncthreads();
+      if (threadIdx.x == 0) {
+        __threadfence();
+        atomicAdd(p.ticket + j, 1u);           // gridDim.x + 1: this query's list buffer is free again
+      }
+    }
+    __syncthreads();   // qh / mkeys are reused by the next query
   }
 }
 

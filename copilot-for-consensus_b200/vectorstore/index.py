@@ -87,6 +87,38 @@ class B200Index:
                                               self._stream()))
         return ids, sc
 
+    def search_l2(self, queries: Any, k: int = 10, id_base: int = 0):
+        """``b200_index_search_l2``: the k nearest rows by squared Euclidean distance (FAISS-flat semantics,
+        faiss_store.py:99-101,212-224): ``(ids[nq, k], squared distances[nq, k])`` ascending; fp32 queries, k <= 64."""
+        import torch
+
+        if isinstance(queries, torch.Tensor) and queries.is_cuda:
+            if queries.device.index != self.device or not queries.is_contiguous() or queries.shape[1] != self.dim or \
+                    queries.dtype != torch.float32:
+                raise ValueError(f"device queries must be contiguous float32 [nq, {self.dim}] on cuda:{self.device}")
+            nq = queries.shape[0]
+            ids = torch.empty((nq, k), dtype=torch.int64, device=queries.device)
+            dist = torch.empty((nq, k), dtype=torch.float32, device=queries.device)
+            nat.check(self._lib.b200_index_search_l2(
+                self._h, ctypes.c_void_p(queries.data_ptr()), 0, 1, nq, k, id_base, ctypes.c_void_p(ids.data_ptr()),
+                ctypes.c_void_p(dist.data_ptr()), 1, self._stream()))
+            return ids, dist
+        q = np.ascontiguousarray(queries, dtype=np.float32)
+        if q.ndim != 2 or q.shape[1] != self.dim:
+            raise ValueError(f"queries must be [nq, {self.dim}]")
+        ids = np.empty((q.shape[0], k), dtype=np.int64)
+        dist = np.empty((q.shape[0], k), dtype=np.float32)
+        nat.check(self._lib.b200_index_search_l2(self._h, ctypes.c_void_p(q.ctypes.data), 0, 0, q.shape[0], k, id_base,
+                                                 ctypes.c_void_p(ids.ctypes.data), ctypes.c_void_p(dist.ctypes.data), 0,
+                                                 self._stream()))
+        return ids, dist
+
+    def certificate_stats(self) -> tuple[int, int]:
+        """``(queries checked, queries re-scored exhaustively)`` by the fused path since creation (synchronises)."""
+        a, b = ctypes.c_int64(0), ctypes.c_int64(0)
+        nat.check(self._lib.b200_index_certificate_stats(self._h, ctypes.byref(a), ctypes.byref(b)))
+        return int(a.value), int(b.value)
+
     def search_static(self, queries: Any, ids_out: Any, scores_out: Any, id_base: int = 0) -> None:
         """``b200_index_search_static``: the same search for callers that may not allocate device memory
         on the query path (all HBM already owned by the host program's pool, or no tolerance for the

@@ -15,6 +15,10 @@ Deliberate differences, all documented in DESIGN.md:
 
 Extensions (array in / array out, no per-element Python): ``add_embeddings_array``,
 ``query_batch``.
+
+``metric="l2"`` gives the scoring of the reference's second in-process driver, ``FAISSVectorStore`` with a
+flat index (faiss_store.py:99-101 ``IndexFlatL2``; :212-224): nearest by squared Euclidean distance,
+``score = 1 / (1 + distance)``.  Same storage, same methods; only ``query`` / ``query_batch`` differ.
 """
 from __future__ import annotations
 
@@ -28,6 +32,7 @@ from .. import _native as nat
 from .interface import SearchResult, VectorStore
 
 MAX_TOP_K = 1024
+MAX_TOP_K_L2 = 64
 
 
 def _as_ptr(a: np.ndarray) -> ctypes.c_void_p:
@@ -38,7 +43,11 @@ class B200VectorStore(VectorStore):
     """GPU-resident cosine top-k store behind the reference ``VectorStore`` interface."""
 
     def __init__(self, device: str | int = "cuda:0", upsert: bool = False, initial_capacity: int = 4096,
-                 master_dtype: str = "float32"):
+                 master_dtype: str = "float32", metric: str = "cosine", dimension: int | None = None):
+        if metric not in ("cosine", "l2"):
+            raise ValueError("metric must be 'cosine' or 'l2'")
+        self._metric = metric
+        self._fixed_dim = int(dimension) if dimension else None   # faiss_store.py:66: the flat index has a set dimension
         self._device = nat.device_index(device)
         self._upsert = bool(upsert)
         self._initial_capacity = int(initial_capacity)
@@ -81,6 +90,8 @@ class B200VectorStore(VectorStore):
         return ctypes.c_void_p(nat.current_stream_ptr(self._device))
 
     def _ensure_index(self, dim: int) -> None:
+        if self._fixed_dim is not None and dim != self._fixed_dim:
+            raise ValueError(f"Vector dimension ({dim}) doesn't match index dimension ({self._fixed_dim})")
         if self._h is None:
             h = ctypes.c_void_p()
             nat.check(self._lib.b200_index_create(dim, self._initial_capacity, self._device, self._master,
@@ -122,13 +133,15 @@ class B200VectorStore(VectorStore):
     def add_embedding(self, id: str, vector: list[float], metadata: dict[str, Any]) -> None:
         """inmemory.py:35-53."""
         with self._lock:
-            if id in self._row_of:
-                if not self._upsert:
-                    raise ValueError(f"ID '{id}' already exists in the vector store")
-                self.delete(id)
+            if id in self._row_of and not self._upsert:
+                raise ValueError(f"ID '{id}' already exists in the vector store")
             if vector is None or len(vector) == 0:
                 raise ValueError("Vector cannot be empty")
             arr = self._host_rows([vector])
+            if self._dim is not None and arr.shape[1] != self._dim:
+                raise ValueError(f"Vector dimension ({arr.shape[1]}) doesn't match stored vectors dimension ({self._dim})")
+            if id in self._row_of:      # upsert: the old row goes only once the new one is known to be valid
+                self.delete(id)
             self._append_rows([id], arr, [metadata])
 
     def add_embeddings(self, ids: list[str], vectors: list[list[float]], metadatas: list[dict[str, Any]]) -> None:
@@ -177,13 +190,26 @@ class B200VectorStore(VectorStore):
         if not (n == len(vectors) == len(metadatas)):
             raise ValueError("ids, vectors, and metadatas must have the same length")
         with self._lock:
-            if len(set(ids)) != n:
-                raise ValueError("duplicate ids inside the batch already exists in the vector store")
-            for i in ids:
-                if i in self._row_of:
-                    raise ValueError(f"ID '{i}' already exists in the vector store")
             if n == 0:
                 return
+            if self._upsert:
+                # qdrant_store.py:287-297 semantics: stored ids are replaced; inside a batch the last row of an id wins
+                last = {i: j for j, i in enumerate(ids)}
+                if len(last) != n:
+                    keep = sorted(last.values())
+                    vectors = vectors[keep] if hasattr(vectors, "shape") else [vectors[j] for j in keep]
+                    ids = [ids[j] for j in keep]
+                    metadatas = [metadatas[j] for j in keep]
+                    n = len(ids)
+                for i in ids:
+                    if i in self._row_of:
+                        self.delete(i)
+            else:
+                if len(set(ids)) != n:
+                    raise ValueError("duplicate ids inside the batch already exists in the vector store")
+                for i in ids:
+                    if i in self._row_of:
+                        raise ValueError(f"ID '{i}' already exists in the vector store")
             dev_ptr = self._device_tensor_ptr(vectors, want_bf16=self._master == nat.MASTER_BF16)
             if dev_ptr is None:
                 self._append_rows(ids, self._host_rows(vectors), metadatas)
@@ -229,6 +255,8 @@ class B200VectorStore(VectorStore):
                 return []
             rows, scores = self._search_host(q[None, :], k)
             rows, scores = rows[0], scores[0]
+            if self._metric == "l2":     # faiss_store.py:220: score = 1.0 / (1.0 + float(dist)), a Python float
+                scores = 1.0 / (1.0 + scores.astype(np.float64))
             rows = rows[rows >= 0]
             vecs = self._rows_to_host(rows)
             out = []
@@ -239,8 +267,9 @@ class B200VectorStore(VectorStore):
             return out
 
     def _check_k(self, k: int) -> None:
-        if k > MAX_TOP_K:
-            raise RuntimeError(f"top_k={k} is above the supported maximum of {MAX_TOP_K}")
+        limit = MAX_TOP_K_L2 if self._metric == "l2" else MAX_TOP_K
+        if k > limit:
+            raise RuntimeError(f"top_k={k} is above the supported maximum of {limit}")
 
     def _search_host(self, q: np.ndarray, k: int) -> tuple[np.ndarray, np.ndarray]:
         self._check_k(k)
@@ -248,8 +277,8 @@ class B200VectorStore(VectorStore):
         nq = q.shape[0]
         ids = np.empty((nq, k), dtype=np.int64)
         sc = np.empty((nq, k), dtype=np.float32)
-        nat.check(self._lib.b200_index_search(self._h, _as_ptr(q), 0, 0, nq, k, 0, _as_ptr(ids), _as_ptr(sc), 0,
-                                              self._stream()))
+        fn = self._lib.b200_index_search_l2 if self._metric == "l2" else self._lib.b200_index_search
+        nat.check(fn(self._h, _as_ptr(q), 0, 0, nq, k, 0, _as_ptr(ids), _as_ptr(sc), 0, self._stream()))
         return ids, sc
 
     def _rows_to_host(self, rows: np.ndarray) -> np.ndarray:
@@ -263,7 +292,8 @@ class B200VectorStore(VectorStore):
         """Extension: ``[nq, dim]`` queries -> ``(rows[nq, top_k] int64, scores[nq, top_k] fp32)``.
 
         Rows are insertion-order indices (+ ``id_base``), -1 where the store holds fewer than
-        ``top_k`` vectors; map them with :meth:`ids_for_rows`.  A CUDA tensor in (fp32 or bf16, on
+        ``top_k`` vectors; map them with :meth:`ids_for_rows`.  With ``metric="l2"`` the second array holds
+        squared distances, ascending (``1 / (1 + d)`` is the score ``query`` reports).  A CUDA tensor in (fp32 or bf16, on
         this store's GPU) gives CUDA tensors out with no host round trip; numpy in gives numpy out."""
         with self._lock:
             if top_k < 0:
@@ -278,6 +308,8 @@ class B200VectorStore(VectorStore):
                     raise ValueError(f"queries live on {queries.device}, the store on cuda:{self._device}")
                 if queries.dtype not in (torch.float32, torch.bfloat16) or not queries.is_contiguous():
                     raise ValueError("device queries must be contiguous float32 or bfloat16")
+                if self._metric == "l2" and queries.dtype != torch.float32:
+                    raise ValueError("l2 queries must be float32")
                 nq, d = queries.shape
                 ids = torch.full((nq, top_k), -1, dtype=torch.int64, device=queries.device)
                 sc = torch.zeros((nq, top_k), dtype=torch.float32, device=queries.device)
@@ -286,9 +318,9 @@ class B200VectorStore(VectorStore):
                 if d != self._dim:
                     raise ValueError(f"Query vector dimension ({d}) doesn't match stored vectors dimension ({self._dim})")
                 self._flush_deletes()
-                nat.check(self._lib.b200_index_search(
-                    self._h, ctypes.c_void_p(queries.data_ptr()), 0 if queries.dtype == torch.float32 else 1, 1, nq,
-                    top_k, id_base, ctypes.c_void_p(ids.data_ptr()), ctypes.c_void_p(sc.data_ptr()), 1, self._stream()))
+                fn = self._lib.b200_index_search_l2 if self._metric == "l2" else self._lib.b200_index_search
+                nat.check(fn(self._h, ctypes.c_void_p(queries.data_ptr()), 0 if queries.dtype == torch.float32 else 1, 1, nq,
+                             top_k, id_base, ctypes.c_void_p(ids.data_ptr()), ctypes.c_void_p(sc.data_ptr()), 1, self._stream()))
                 return ids, sc
             q = np.ascontiguousarray(queries, dtype=np.float32)
             if q.ndim != 2:
@@ -341,7 +373,22 @@ class B200VectorStore(VectorStore):
 
     @property
     def dimension(self) -> int | None:
-        return self._dim
+        return self._dim if self._dim is not None else self._fixed_dim
+
+    @property
+    def metric(self) -> str:
+        return self._metric
+
+    def certificate_stats(self) -> tuple[int, int]:
+        """``(queries checked, queries re-scored exhaustively)`` since the index was created: how often the
+        fused select's exactness certificate (see ``b200_index_search`` in the header) sent a query to the
+        exhaustive kernel.  Synchronises the device."""
+        with self._lock:
+            if self._h is None:
+                return 0, 0
+            a, b = ctypes.c_int64(0), ctypes.c_int64(0)
+            nat.check(self._lib.b200_index_certificate_stats(self._h, ctypes.byref(a), ctypes.byref(b)))
+            return int(a.value), int(b.value)
 
     @property
     def native_handle(self) -> ctypes.c_void_p | None:

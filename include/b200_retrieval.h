@@ -18,7 +18,12 @@
  *   - `stream` is a cudaStream_t passed as void* (NULL = the legacy default stream).  Calls are
  *     asynchronous with respect to the host when every buffer is on the device; calls with host
  *     output buffers synchronise the stream before returning.
- *   - a handle may be used from several threads; calls on one handle are serialised internally.
+ *   - a handle may be used from several threads and streams.  Calls on one handle are serialised on the
+ *     host by the handle's mutex and on the GPU by an event the handle keeps: a call that arrives on a
+ *     different stream than the previous one first makes its stream wait for that call's last kernel
+ *     (every handle owns one set of scratch buffers).  b200_index_search_static is the exception: see there.
+ *   - the library never reads environment variables (the reference pins its adapters to that:
+ *     adapters/copilot_vectorstore/tests/test_factory.py:75-107, scripts/check_no_runtime_env_vars.py:6-16).
  *   - there is no CPU fallback: without a usable sm_100 device every call fails with
  *     B200_ERR_CUDA / B200_ERR_UNSUPPORTED.
  */
@@ -50,6 +55,13 @@ const char* b200_last_error(void);
 int b200_version(void);
 /* number of visible sm_100 devices; 0 when there is none (then nothing else will work) */
 int b200_device_count(void);
+/* Process-wide switches between kernel variants, for A/B timing and for the tests that drive every
+ * alternative path against the oracle (no reference counterpart).  Names and defaults:
+ *   pdl 0 | gemm_pair 1 | gemm_ast 1 | attention_tc 1 | att_exact_max 0 | att_turns 1 | att_poly (0..8) |
+ *   fuse_ln 1 | fuse_ffn 1 | serpentine 1 | sim_pair 1 | sim_bound 3 | sim_refresh_mask 0 | search_certify 1
+ * Unknown names and out-of-range values are refused with B200_ERR_INVALID. */
+int b200_set_option(const char* name, int value);
+int b200_get_option(const char* name, int* value);
 
 /* ---- vector index: replaces InMemoryVectorStore's storage + query arithmetic ---------------
  * Rows are identified by their position in insertion order (row 0 = first inserted), which is
@@ -62,7 +74,8 @@ enum {
 };
 
 /* dim: vector dimension (1..4096; up to 384 the query tile stays resident in shared memory, beyond that it is
- * streamed); capacity: initial row capacity, grows on demand. */
+ * streamed); capacity: initial row capacity, grows on demand.  Besides the caller's rows (the master copy) the
+ * index keeps a unit-normalised 16-bit copy (IEEE half) that the tensor-core pass streams. */
 int b200_index_create(int dim, int64_t capacity, int device, int master_dtype, b200_index_t** out);
 int b200_index_destroy(b200_index_t* idx);
 /* inmemory.py:145-148 clear() */
@@ -89,9 +102,31 @@ int b200_index_get_rows(b200_index_t* idx, const int64_t* rows_host, int64_t n, 
  * (score descending, row ascending).  ids[nq*k] = id_base + row, -1 where fewer than k rows exist;
  * scores[nq*k].  q_dtype: 0 = fp32, 1 = bf16.  k <= 1024: up to 48 the fused
  * select serves it; 49..1024 (orchestrator/app/context_sources.py:66 asks for 50) scores every row exactly, one
- * query at a time -- same ids, order and scores, HBM-bound on the master copy. */
+ * query at a time -- same ids, order and scores, HBM-bound on the master copy.
+ *
+ * Exactness.  The reference scores EVERY row exactly (inmemory.py:111-119).  The fused path ranks rows by a
+ * 16-bit tensor-core score, keeps KP = 16 / 32 / 64 candidates per query (k <= 10 / 24 / 48) and rescores those
+ * exactly.  It then proves, per query, that no other row can belong to the exact top-k: every row outside the
+ * candidates has a 16-bit score <= A (the KP-th best), its exact score can exceed that by at most
+ * eps = r_v + r_q (1 + r_v) + slop (r_v: largest rounding distance of any stored row, tracked at insert;
+ * r_q: this query's rounding distance; slop: fp32 evaluation error), and the k-th exact score must lie strictly
+ * above A + eps.  A query that fails the test -- near-duplicate rows, ties -- is re-scored against every row by
+ * a second kernel in the same call (no host round trip: the kernel is always launched and returns at once when
+ * nothing failed).  So the ids, their order and the fp32 score bits are those of the exhaustive computation,
+ * always; the cost of an uncertified query is one pass over the master copy. */
 int b200_index_search(b200_index_t* idx, const void* queries, int q_dtype, int queries_on_device, int64_t nq,
                       int k, int64_t id_base, int64_t* ids, float* scores, int out_on_device, void* stream);
+
+/* Cumulative counters of the certificate above (no reference counterpart): queries checked by the fused path
+ * since the index was created, and how many of them had to be re-scored exhaustively.  Synchronises the device. */
+int b200_index_certificate_stats(b200_index_t* idx, int64_t* checked, int64_t* recomputed);
+
+/* adapters/copilot_vectorstore/copilot_vectorstore/faiss_store.py:99-101 (IndexFlatL2), :212-224 (search):
+ * the k nearest rows by squared Euclidean distance, ascending, ties to the lower row; dist[nq*k] holds the
+ * squared distances (the store turns them into scores 1/(1+d), faiss_store.py:220).  Exact brute force over the
+ * master copy -- what a flat FAISS index is -- one HBM pass per query; fp32 queries, k <= 64. */
+int b200_index_search_l2(b200_index_t* idx, const void* queries, int q_dtype, int queries_on_device, int64_t nq,
+                         int k, int64_t id_base, int64_t* ids, float* dist, int out_on_device, void* stream);
 
 /* b200_index_search for callers that must not trigger a device allocation (this entry point has no
  * counterpart in the reference).  Meant for processes that gave all free HBM to their own pool at

@@ -184,6 +184,51 @@ int b200o_topk(const float *queries, int nq, const float *rows, int64_t n, int d
     return 0;
 }
 
+/*
+ * FAISS-flat mode (adapters/copilot_vectorstore/copilot_vectorstore/faiss_store.py:99-101
+ * IndexFlatL2, :212-224 search + score conversion): squared Euclidean distance, ascending,
+ * score = 1 / (1 + dist).  faiss itself is not installable here, so parity
+ * with faiss's own summation order is UNPINNED; pinned are the reference's call site semantics
+ * (exact flat search, ascending distance, 1/(1+d)) against a float64 numpy restatement
+ * (tests/test_oracle_search.py).  Canonical order as above: element i -> partial (i & 31) by
+ * fma(t, t, p) with t = q[i] - v[i] rounded to fp32; halving tree; ties -> lower row.
+ */
+float b200o_l2(const float *q, const float *v, int d)
+{
+    float p[B200O_LANES];
+    for (int l = 0; l < B200O_LANES; ++l) p[l] = 0.0f;
+    for (int i = 0; i < d; ++i) {
+        const float t = q[i] - v[i];
+        p[i & (B200O_LANES - 1)] = __builtin_fmaf(t, t, p[i & (B200O_LANES - 1)]);
+    }
+    for (int s = B200O_LANES / 2; s >= 1; s >>= 1)
+        for (int l = 0; l < s; ++l) p[l] = p[l] + p[l + s];
+    return p[0];
+}
+
+/* nq queries x n rows -> k nearest by squared L2; ids -1 padded, dist 0 padded */
+int b200o_l2_topk(const float *queries, int nq, const float *rows, int64_t n, int d,
+                  int k, int64_t *ids, float *dist)
+{
+    if (nq < 0 || n < 0 || d <= 0 || k < 0) return -1;
+    for (int64_t i = 0; i < (int64_t)nq * k; ++i) { ids[i] = -1; dist[i] = 0.0f; }
+    if (nq == 0 || n == 0 || k == 0) return 0;
+#pragma omp parallel for schedule(dynamic, 1)
+    for (int a = 0; a < nq; ++a) {
+        cand_t *list = (cand_t *)malloc(sizeof(cand_t) * (size_t)k);
+        int cnt = 0;
+        const float *qa = queries + (int64_t)a * d;
+        for (int64_t r = 0; r < n; ++r) {
+            /* "better first" = smaller distance: order by -dist descending, row ascending */
+            const float s = -b200o_l2(qa, rows + r * (int64_t)d, d);
+            if (cnt < k || cand_before(s, r, &list[k - 1])) cand_insert(list, &cnt, k, s, r);
+        }
+        for (int j = 0; j < cnt; ++j) { ids[(int64_t)a * k + j] = list[j].r; dist[(int64_t)a * k + j] = -list[j].s; }
+        free(list);
+    }
+    return 0;
+}
+
 /* bf16 (round-to-nearest-even) helpers so tests can build "identical inputs" */
 static inline uint16_t f32_to_bf16_rne(float f)
 {

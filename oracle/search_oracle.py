@@ -59,6 +59,9 @@ def lib() -> ctypes.CDLL:
         L.b200o_topk.restype = ctypes.c_int
         L.b200o_topk.argtypes = [f32p, ctypes.c_int, f32p, ctypes.c_int64, ctypes.c_int,
                                  ctypes.c_int, i64p, f32p]
+        L.b200o_l2_topk.restype = ctypes.c_int
+        L.b200o_l2_topk.argtypes = [f32p, ctypes.c_int, f32p, ctypes.c_int64, ctypes.c_int,
+                                    ctypes.c_int, i64p, f32p]
         L.b200o_round_bf16.restype = None
         L.b200o_round_bf16.argtypes = [f32p, ctypes.c_int64, f32p]
         _lib = L
@@ -106,6 +109,44 @@ def topk_canonical(queries, rows, k: int) -> tuple[np.ndarray, np.ndarray]:
     if rc != 0:
         raise ValueError("b200o_topk: bad arguments")
     return ids, sc
+
+
+def l2_topk_canonical(queries, rows, k: int) -> tuple[np.ndarray, np.ndarray]:
+    """FAISS-flat mode (faiss_store.py:99-101,212-224): ``(ids[nq,k], squared L2 distances[nq,k])``,
+    ascending distance, ties to the lower row, canonical fp32 summation order."""
+    queries, rows = _f32(queries), _f32(rows)
+    if queries.ndim == 1:
+        queries = queries[None, :]
+    nq, d = queries.shape
+    n = rows.shape[0]
+    ids = np.empty((nq, k), dtype=np.int64)
+    dist = np.empty((nq, k), dtype=np.float32)
+    rc = lib().b200o_l2_topk(_p(queries), nq, _p(rows), n, d, k, _p(ids, ctypes.c_int64), _p(dist))
+    if rc != 0:
+        raise ValueError("b200o_l2_topk: bad arguments")
+    return ids, dist
+
+
+def l2_topk_numpy(queries, rows, k: int) -> tuple[np.ndarray, np.ndarray]:
+    """What ``faiss.IndexFlatL2.search`` defines (exact squared Euclidean distance, ascending), restated in
+    float64 numpy.  faiss is not installable here, so this restatement -- not faiss -- pins the canonical one."""
+    q = np.asarray(queries, dtype=np.float64)
+    x = np.asarray(rows, dtype=np.float64)
+    if q.ndim == 1:
+        q = q[None, :]
+    ids = np.full((q.shape[0], k), -1, dtype=np.int64)
+    dist = np.zeros((q.shape[0], k), dtype=np.float64)
+    for a in range(q.shape[0]):
+        dd = ((x - q[a]) ** 2).sum(axis=1)
+        order = np.argsort(dd, kind="stable")[:k]
+        ids[a, : len(order)] = order
+        dist[a, : len(order)] = dd[order]
+    return ids, dist
+
+
+def l2_score(dist) -> np.ndarray:
+    """faiss_store.py:220: ``score = 1.0 / (1.0 + float(dist))`` (Python float = float64 of the fp32 distance)."""
+    return 1.0 / (1.0 + np.asarray(dist, dtype=np.float32).astype(np.float64))
 
 
 def round_bf16(a) -> np.ndarray:

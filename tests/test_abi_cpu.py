@@ -60,6 +60,24 @@ def test_status_to_exception_mapping():
         nat.device_index("cpu")
 
 
+def test_options_replace_environment_reads():
+    """Kernel-variant switches go through b200_set_option; nothing under csrc/ reads the environment
+    (the reference pins its adapters to that: adapters/copilot_vectorstore/tests/test_factory.py:75-107)."""
+    nat = pkg("_native")
+    assert nat.get_option("fuse_ffn") == 1 and nat.get_option("pdl") == 0 and nat.get_option("search_certify") == 1
+    with nat.options(fuse_ffn=0, sim_bound=1):
+        assert nat.get_option("fuse_ffn") == 0 and nat.get_option("sim_bound") == 1
+    assert nat.get_option("fuse_ffn") == 1 and nat.get_option("sim_bound") == 3
+    with pytest.raises(ValueError, match="unknown option"):
+        nat.set_option("no_such_switch", 1)
+    with pytest.raises(ValueError, match="takes"):
+        nat.set_option("pdl", 7)
+    csrc = os.path.join(ROOT, "copilot-for-consensus_b200", "csrc")
+    for fn in os.listdir(csrc):
+        if fn.endswith((".cu", ".cuh", ".h")):
+            assert "getenv" not in open(os.path.join(csrc, fn)).read(), f"{fn} reads the environment"
+
+
 def test_alias_module_imports_the_package():
     import copilot_for_consensus_b200 as alias
 

@@ -96,42 +96,41 @@ def _scale_qk(weights: dict, scale: float) -> dict:
     return out
 
 
-@pytest.mark.parametrize("qk_scale,exact_env", [(8.0, "0"), (8.0, "1"), (60.0, "0")])
-def test_sharp_attention_both_softmax_reference_paths(monkeypatch, qk_scale, exact_env):
+@pytest.mark.parametrize("qk_scale,exact_max", [(8.0, 0), (8.0, 1), (60.0, 0)])
+def test_sharp_attention_both_softmax_reference_paths(qk_scale, exact_max):
     """Random-init weights give near-uniform attention; real checkpoints do not.  Scaling the query / key
     projections makes the logits 64x (moderately peaked rows: the Cauchy-Schwarz reference path of
     attention_tc.cuh) and 3600x (one-hot rows whose bound exceeds ATT_BOUND_GAP: the exact maximum
-    pass); B200_ATT_EXACT_MAX=1 forces the exact pass on the moderate case, so both paths are checked
+    pass); option att_exact_max=1 forces the exact pass on the moderate case, so both paths are checked
     on the same input against the fp32 oracle."""
     from safetensors.torch import load_file, save_file
 
-    monkeypatch.setenv("B200_ATT_EXACT_MAX", exact_env)
-    mio, prov = pkg("embedding.model_io"), pkg("embedding.provider")
+    mio, prov, nat = pkg("embedding.model_io"), pkg("embedding.provider"), pkg("_native")
     with tempfile.TemporaryDirectory() as td:
         mio.write_random_model(td, "all-MiniLM-L6-v2", seed=5)
         path = td + "/model.safetensors"
         save_file({k: v.contiguous() for k, v in _scale_qk(load_file(path), qk_scale).items()}, path)
         p = prov.B200SentenceTransformerProvider(model_name=td, device="cuda:0")
     w = _scale_qk(eo.make_weights(eo.MINILM_L6, seed=5), qk_scale)
-    for B, S in [(6, 256), (5, 96)]:
-        ids, mask, lens = eo.synthetic_tokens(B, S, 30522, seed=S, ragged=True)
-        got = p.embed_tokens(ids.numpy(), lens.numpy())
-        _check(got, eo.encode(eo.MINILM_L6, w, ids, mask).numpy())
+    with nat.options(att_exact_max=exact_max):
+        for B, S in [(6, 256), (5, 96)]:
+            ids, mask, lens = eo.synthetic_tokens(B, S, 30522, seed=S, ragged=True)
+            got = p.embed_tokens(ids.numpy(), lens.numpy())
+            _check(got, eo.encode(eo.MINILM_L6, w, ids, mask).numpy())
     p.close()
 
 
-@pytest.mark.parametrize("env", [{"B200_FUSE_FFN": "0"}, {"B200_FUSE_FFN": "0", "B200_FUSE_LN": "0"},
-                                 {"B200_FUSE_FFN": "0", "B200_FUSE_LN": "0", "B200_GEMM_AST": "0"},
-                                 {"B200_GEMM_CG": "1"}, {"B200_SERPENTINE": "0"}, {"B200_PDL": "1"},
-                                 {"B200_ATTENTION": "legacy"}])
-def test_alternative_kernel_paths_stay_correct(monkeypatch, minilm, minilm_weights, env):
+@pytest.mark.parametrize("opts", [{"fuse_ffn": 0}, {"fuse_ffn": 0, "fuse_ln": 0},
+                                  {"fuse_ffn": 0, "fuse_ln": 0, "gemm_ast": 0},
+                                  {"gemm_pair": 0}, {"serpentine": 0}, {"pdl": 1},
+                                  {"attention_tc": 0}, {"att_turns": 0}])
+def test_alternative_kernel_paths_stay_correct(minilm, minilm_weights, opts):
     """The kernels the default MiniLM path no longer takes (separate FFN GEMMs, separate LayerNorm, the
     non-A-stationary and single-CTA GEMMs, the mma.sync attention) still serve other shapes; the
-    switches are read per call, so the same provider can be driven through each of them."""
-    for k, v in env.items():
-        monkeypatch.setenv(k, v)
+    switches (b200_set_option) are read per call, so the same provider can be driven through each of them."""
     ids, mask, lens = eo.synthetic_tokens(9, 256, 30522, seed=21, ragged=True)
-    got = minilm.embed_tokens(ids.numpy(), lens.numpy())
+    with pkg("_native").options(**opts):
+        got = minilm.embed_tokens(ids.numpy(), lens.numpy())
     _check(got, eo.encode(eo.MINILM_L6, minilm_weights, ids, mask).numpy())
 
 
