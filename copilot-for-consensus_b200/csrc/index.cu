@@ -288,14 +288,18 @@ static float certificate_slop(int d) { return (float)d * 2.384185791015625e-7f +
 // exact_topk_kernel over the fail list of the K9 launch just issued (or, with fail == nullptr, over all nq queries)
 template <int METRIC_L2>
 static int launch_exact(b200_index* ix, const uint32_t* fail_count, const int32_t* fail_idx, uint32_t* ticket, int nq,
-                        const float* q_f32, int k, int64_t id_base, int64_t* ids_dev, float* sc_dev, cudaStream_t st) {
-  const int grid = ix->num_sms;
-  B200_TRY(ix->exact_part.grow((size_t)2 * grid * EXACT_KEEP * 8, 0, st));
+                        const float* q_f32, int k, int64_t id_base, int64_t* ids_dev, float* sc_dev, cudaStream_t st,
+                        uint64_t* part = nullptr, int grid = 0) {
+  if (!part) {   // the index's own scratch (grown on first use); the no-allocation entry point passes its own
+    grid = ix->num_sms;
+    B200_TRY(ix->exact_part.grow((size_t)2 * grid * EXACT_KEEP * 8, 0, st));
+    part = ix->exact_part.as<uint64_t>();
+  }
   ExactParams e{};
   e.fail_count = fail_count; e.fail_idx = fail_idx; e.nq = nq; e.q_f32 = q_f32;
   e.master = ix->master.p; e.master_is_bf16 = ix->master_dtype == B200_INDEX_MASTER_BF16;
   e.n_rows = (uint32_t)ix->count; e.d = ix->dim; e.k = k; e.id_base = id_base;
-  e.part = ix->exact_part.as<uint64_t>(); e.ticket = ticket; e.out_ids = ids_dev; e.out_scores = sc_dev;
+  e.part = part; e.ticket = ticket; e.out_ids = ids_dev; e.out_scores = sc_dev;
   const size_t smem = (size_t)EXACT_MERGE * 8 + (size_t)ix->dim * 4;
   auto kern = exact_topk_kernel<METRIC_L2>;
   B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -809,7 +813,7 @@ int b200_merge_topk(const int64_t* ids_in, const float* scores_in, int64_t nq, i
 //
 // b200_index_search_static() does the same search with all of its scratch -- the padded bf16 query
 // tile, the fp32 copy of the queries, and the per-split candidate lists -- inside the fixed array
-// below, which is part of the library image: every GPU that loads the library holds these 4.3 MB
+// below, which is part of the library image: every GPU that loads the library holds these 4.7 MB
 // until the process exits, whether or not the entry point is ever used.
 // ================================================================================================
 namespace {
@@ -822,8 +826,15 @@ constexpr size_t kStaticOffQF32 = kStaticOffQBf16 + (size_t)kStaticMaxQueries * 
 constexpr size_t kStaticOffCand = kStaticOffQF32 + (size_t)kStaticMaxQueries * kStaticMaxDpad * 4;
 constexpr size_t kStaticOffGthr = kStaticOffCand + (size_t)kStaticMaxQueries * kStaticMaxCand * 8;
 constexpr size_t kStaticBktBytes = (size_t)kStaticMaxQueries * (64 + 1) * 4;   // [128][up to 64 buckets] + [128] bounds
-constexpr size_t kStaticBytes = kStaticOffGthr + kStaticBktBytes;
-static_assert(kStaticOffQF32 % 256 == 0 && kStaticOffCand % 256 == 0 && kStaticOffGthr % 256 == 0,
+// the exactness certificate's share: per-query rounding data, the fail list, and the exhaustive kernel's lists
+constexpr int kStaticExactGrid = 160;               // CTAs of the exhaustive kernel (at most one per SM)
+constexpr size_t kStaticOffQMeta = kStaticOffGthr + (kStaticBktBytes + 255) / 256 * 256;
+constexpr size_t kStaticOffCert = kStaticOffQMeta + (size_t)kStaticMaxQueries * 8;
+constexpr size_t kStaticCertBytes = 64 + (size_t)kStaticMaxQueries * 8;         // count, tickets, fail list
+constexpr size_t kStaticOffPart = kStaticOffCert + (kStaticCertBytes + 255) / 256 * 256;
+constexpr size_t kStaticBytes = kStaticOffPart + (size_t)2 * kStaticExactGrid * EXACT_KEEP * 8;
+static_assert(kStaticOffQF32 % 256 == 0 && kStaticOffCand % 256 == 0 && kStaticOffGthr % 256 == 0 &&
+              kStaticOffQMeta % 256 == 0 && kStaticOffCert % 256 == 0 && kStaticOffPart % 256 == 0,
               "scratch sub-buffers must stay 256-byte aligned");
 
 }  // namespace
@@ -843,6 +854,17 @@ int static_scratch_for_current_device(int device, unsigned char** out) {
   if (!g_static_ptr[device]) {
     void* p = nullptr;
     B200_CUDA(cudaGetSymbolAddress(&p, g_static_scratch));
+    // With lazy module loading (the CUDA 12 default) a kernel's code is loaded into device memory the first time
+    // it is used.  Touch every kernel this entry point can launch now, so that a later call in another k band or
+    // query dtype loads nothing.
+    cudaFuncAttributes fa;
+    B200_CUDA(cudaFuncGetAttributes(&fa, sim_topk_kernel<256, 16, 1>));
+    B200_CUDA(cudaFuncGetAttributes(&fa, sim_topk_kernel<128, 32, 1>));
+    B200_CUDA(cudaFuncGetAttributes(&fa, sim_topk_kernel<128, 64, 1>));
+    B200_CUDA(cudaFuncGetAttributes(&fa, prep_queries_kernel<float>));
+    B200_CUDA(cudaFuncGetAttributes(&fa, prep_queries_kernel<__nv_bfloat16>));
+    B200_CUDA(cudaFuncGetAttributes(&fa, merge_rescore_kernel));
+    B200_CUDA(cudaFuncGetAttributes(&fa, exact_topk_kernel<0>));
     g_static_ptr[device] = static_cast<unsigned char*>(p);
   }
   *out = g_static_ptr[device];
@@ -913,19 +935,24 @@ extern "C" int b200_index_search_static(b200_index_t* ix, const void* queries_de
   float* q_f32 = reinterpret_cast<float*>(base + kStaticOffQF32);
   uint64_t* cand = reinterpret_cast<uint64_t*>(base + kStaticOffCand);
   uint32_t* gthr = reinterpret_cast<uint32_t*>(base + kStaticOffGthr);
-  // The array keeps whatever the previous call left.  The only part that must start at zero is the
-  // table of score bounds the CTAs share (33 KB): it is cleared here, on the caller's stream.
-  // Everything else is rewritten in full before it is read: prep_queries_kernel writes the whole
-  // padded query tile (zero rows included) and every (query, split) candidate set is stored by its
-  // CTA before the merge kernel looks at it.
+  float2* qmeta = reinterpret_cast<float2*>(base + kStaticOffQMeta);
+  uint32_t* cert = reinterpret_cast<uint32_t*>(base + kStaticOffCert);
+  uint64_t* part = reinterpret_cast<uint64_t*>(base + kStaticOffPart);
+  // The array keeps whatever the previous call left.  What must start at zero is the table of score
+  // bounds the CTAs share (33 KB) and the certificate's fail count and tickets (0.6 KB): they are cleared
+  // here, on the caller's stream.  Everything else is rewritten in full before it is read:
+  // prep_queries_kernel writes the whole padded query tile (zero rows included) and the rounding data of
+  // every query, every (query, split) candidate set is stored by its CTA before the merge kernel looks at
+  // it, and the exhaustive kernel writes its per-CTA lists before the CTA that folds them reads them.
   B200_CUDA(cudaMemsetAsync(gthr, 0, kStaticBktBytes, st));
+  B200_CUDA(cudaMemsetAsync(cert, 0, 64 + (size_t)kStaticMaxQueries * 4, st));
   const int n = (int)nq, nq_pad = SIM_BLOCK_M, wpb = 8;
   if (q_dtype == 0)
     prep_queries_kernel<float><<<(nq_pad + wpb - 1) / wpb, wpb * 32, 0, st>>>((const float*)queries_dev, n, nq_pad, ix->dim,
-                                                                           ix->dpad, q16, q_f32, nullptr);
+                                                                           ix->dpad, q16, q_f32, qmeta);
   else
     prep_queries_kernel<__nv_bfloat16><<<(nq_pad + wpb - 1) / wpb, wpb * 32, 0, st>>>(
-        (const __nv_bfloat16*)queries_dev, n, nq_pad, ix->dim, ix->dpad, q16, q_f32, nullptr);
+        (const __nv_bfloat16*)queries_dev, n, nq_pad, ix->dim, ix->dpad, q16, q_f32, qmeta);
   B200_CUDA(cudaGetLastError());
   CUtensorMap map_q;
   B200_TRY(make_tma_2d_bf16(&map_q, q16, (uint64_t)nq_pad, (uint64_t)ix->dpad, SIM_BLOCK_M, SIM_BLOCK_K));
@@ -942,10 +969,16 @@ extern "C" int b200_index_search_static(b200_index_t* ix, const void* queries_de
   m.cand = cand; m.q_f32 = q_f32; m.master = ix->master.p;
   m.master_is_bf16 = ix->master_dtype == B200_INDEX_MASTER_BF16;
   m.out_ids = ids_dev; m.out_scores = scores_dev;
-  m.qmeta = nullptr; m.rvmax = nullptr; m.slop = 0.f; m.fail_count = nullptr; m.fail_idx = nullptr; m.stats = nullptr;
+  // same exactness certificate as b200_index_search, its bookkeeping inside the static array
+  uint32_t* ticket = cert + 16;
+  int32_t* fail_idx = reinterpret_cast<int32_t*>(ticket + kStaticMaxQueries);
+  m.qmeta = qmeta; m.rvmax = ix->rvmax(); m.slop = certificate_slop(ix->dpad);
+  m.fail_count = cert; m.fail_idx = fail_idx; m.stats = ix->stats();
   const size_t msmem = (size_t)pow2 * 8 + (size_t)((ix->dim + 1) & ~1) * 4 + 64 * 8;
   B200_CUDA(cudaFuncSetAttribute(merge_rescore_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)msmem));
   merge_rescore_kernel<<<n, 256, msmem, st>>>(m);
   B200_CUDA(cudaGetLastError());
+  B200_TRY(launch_exact<0>(ix, cert, fail_idx, ticket, n, q_f32, k, id_base, ids_dev, scores_dev, st, part,
+                           std::min(ix->num_sms, kStaticExactGrid)));
   return B200_OK;
 }

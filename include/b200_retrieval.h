@@ -134,16 +134,21 @@ int b200_index_search_l2(b200_index_t* idx, const void* queries, int q_dtype, in
  * afford the device-wide synchronisation cudaMalloc/cudaFree imply.  Same result as
  * b200_index_search, with these differences:
  *   - it calls no cudaMalloc / cudaFree / allocating library routine.  All scratch lives in a fixed
- *     4.3 MB array inside the library image, resident on every GPU that loads the library until exit.
+ *     4.7 MB array inside the library image, resident on every GPU that loads the library until exit.
  *   - limits: nq <= 128 per call, index dimension <= 384, k <= 48; larger requests are refused with
  *     B200_ERR_UNSUPPORTED and a message naming the limit.
  *   - queries, ids and scores must be device pointers on the index's GPU.
  *   - every call on a GPU shares that one array (across all indexes and threads).  The caller never
- *     has to clear it -- each call zeroes the 33 KB that must start at zero and rewrites the rest
+ *     has to clear it -- each call zeroes the 34 KB that must start at zero and rewrites the rest
  *     before reading it -- but two calls whose kernels overlap on the GPU (different streams) race on
- *     it: keep such calls on one stream or order them yourself.
- *   - the first call on each device looks up the array's device address (cudaGetSymbolAddress);
- *     make that first call before any stream capture begins on that device. */
+ *     it: keep such calls on one stream or order them yourself (the per-handle stream ordering of the
+ *     other entry points does not cover this array, which all indexes share).
+ *   - the first call on each device looks up the array's device address (cudaGetSymbolAddress) and
+ *     has the driver load the code of every kernel this entry point can launch (all k bands, both query
+ *     dtypes), so later calls load nothing; make that first call before any stream capture begins on
+ *     that device.
+ *   - the exactness certificate of b200_index_search applies here too, with its bookkeeping and the
+ *     exhaustive kernel's scratch inside the same array. */
 int b200_index_search_static(b200_index_t* idx, const void* queries_dev, int q_dtype, int64_t nq, int k,
                              int64_t id_base, int64_t* ids_dev, float* scores_dev, void* stream);
 

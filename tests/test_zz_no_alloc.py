@@ -77,3 +77,51 @@ def test_static_scratch_search_refuses_what_does_not_fit():
     assert (ids[:4] == -1).all() and (sc[:4] == 0).all()
     index.close()
     empty.close()
+
+
+_FRESH = r"""
+import sys
+sys.path.insert(0, {root!r})
+import importlib
+import numpy as np, torch
+from oracle import search_oracle as so
+vs = importlib.import_module("copilot-for-consensus_b200.vectorstore")
+dev = torch.device("cuda", 0)
+g = torch.Generator(device=dev).manual_seed(5)
+rows = torch.randn((20000, 384), generator=g, device=dev).bfloat16().float().contiguous()
+index = vs.B200Index(384, device=0, master_dtype="float32", capacity=rows.shape[0])
+index.add(rows)
+qs = {{10: torch.randn((50, 384), generator=g, device=dev).bfloat16().float().contiguous(),
+      24: torch.randn((20, 384), generator=g, device=dev).bfloat16().contiguous(),
+      48: torch.randn((9, 384), generator=g, device=dev).bfloat16().float().contiguous()}}
+outs = {{k: (torch.empty((q.shape[0], k), dtype=torch.int64, device=dev),
+            torch.empty((q.shape[0], k), dtype=torch.float32, device=dev)) for k, q in qs.items()}}
+torch.cuda.synchronize()
+index.search_static(qs[10], *outs[10])          # the very first search of this process
+torch.cuda.synchronize()
+free = torch.cuda.mem_get_info(0)[0]
+for k in (24, 48):                              # other k bands / query dtype: nothing may be loaded or allocated now
+    index.search_static(qs[k], *outs[k])
+torch.cuda.synchronize()
+assert torch.cuda.mem_get_info(0)[0] == free, "a later k band changed free device memory"
+for k, q in qs.items():
+    oi, os_ = so.topk_canonical(q.float().cpu().numpy(), rows.cpu().numpy(), k)
+    assert (outs[k][0].cpu().numpy() == oi).all(), k
+    assert (outs[k][1].cpu().numpy().view(np.uint32) == os_.view(np.uint32)).all(), k
+print("fresh-process static search ok")
+"""
+
+
+def test_static_search_first_thing_in_a_fresh_process():
+    """The no-allocation promise has to hold when this entry point is the FIRST search a process makes: its first
+    call on a device resolves the scratch array's address and has the driver load every kernel it may ever
+    launch, so a later call in another k band or query dtype neither allocates nor loads code.  (The other tests in
+    this file run the regular search first, which would hide a kernel that is only loaded lazily.)"""
+    import subprocess
+    import sys
+
+    from conftest import ROOT
+
+    r = subprocess.run([sys.executable, "-c", _FRESH.format(root=ROOT)], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]
+    assert "fresh-process static search ok" in r.stdout
