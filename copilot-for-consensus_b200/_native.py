@@ -44,6 +44,8 @@ SYMBOLS = {
     "b200_index_certificate_stats": (_i, [_vp, ctypes.POINTER(_i64), ctypes.POINTER(_i64)]),
     "b200_index_search_l2": (_i, [_vp, _vp, _i, _i, _i64, _i, _i64, _vp, _vp, _i, _vp]),
     "b200_index_search_static": (_i, [_vp, _vp, _i, _i64, _i, _i64, _vp, _vp, _vp]),
+    "b200_index_search_packed": (_i, [_vp, _vp, _i, _i64, _i, _i64, _vp, _vp]),
+    "b200_merge_hits": (_i, [_vp, _i, _i64, _i, _i64, _i64, _i, _vp, _vp, _i, _vp]),
     "b200_merge_topk": (_i, [_vp, _vp, _i64, _i, _i, _i, _vp, _vp, _i, _vp]),
     "b200_encoder_create": (_i, [ctypes.POINTER(EncoderConfigC), _i, ctypes.POINTER(_vp)]),
     "b200_encoder_destroy": (_i, [_vp]),

@@ -289,7 +289,7 @@ static float certificate_slop(int d) { return (float)d * 2.384185791015625e-7f +
 template <int METRIC_L2>
 static int launch_exact(b200_index* ix, const uint32_t* fail_count, const int32_t* fail_idx, uint32_t* ticket, int nq,
                         const float* q_f32, int k, int64_t id_base, int64_t* ids_dev, float* sc_dev, cudaStream_t st,
-                        uint64_t* part = nullptr, int grid = 0) {
+                        uint64_t* part = nullptr, int grid = 0, ulonglong2* packed_dev = nullptr) {
   if (!part) {   // the index's own scratch (grown on first use); the no-allocation entry point passes its own
     grid = ix->num_sms;
     B200_TRY(ix->exact_part.grow((size_t)2 * grid * EXACT_KEEP * 8, 0, st));
@@ -299,7 +299,7 @@ static int launch_exact(b200_index* ix, const uint32_t* fail_count, const int32_
   e.fail_count = fail_count; e.fail_idx = fail_idx; e.nq = nq; e.q_f32 = q_f32;
   e.master = ix->master.p; e.master_is_bf16 = ix->master_dtype == B200_INDEX_MASTER_BF16;
   e.n_rows = (uint32_t)ix->count; e.d = ix->dim; e.k = k; e.id_base = id_base;
-  e.part = part; e.ticket = ticket; e.out_ids = ids_dev; e.out_scores = sc_dev;
+  e.part = part; e.ticket = ticket; e.out_ids = ids_dev; e.out_scores = sc_dev; e.out_packed = packed_dev;
   const size_t smem = (size_t)EXACT_MERGE * 8 + (size_t)ix->dim * 4;
   auto kern = exact_topk_kernel<METRIC_L2>;
   B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -312,7 +312,7 @@ static int launch_exact(b200_index* ix, const uint32_t* fail_count, const int32_
 }
 
 static int search_chunk(b200_index* ix, const void* q_dev, int q_dtype, int nq, int k, int kp, int64_t id_base,
-                        int64_t* ids_dev, float* sc_dev, cudaStream_t st) {
+                        int64_t* ids_dev, float* sc_dev, ulonglong2* packed_dev, cudaStream_t st) {
   int nqt = (nq + SIM_BLOCK_M - 1) / SIM_BLOCK_M;
   // CTA pairs (two query tiles per cluster) for k <= 10 once there are at least two query tiles; an odd
   // tile count is padded with an empty tile.  Option sim_pair=0 forces single-CTA tiles (A/B timing).
@@ -354,7 +354,7 @@ static int search_chunk(b200_index* ix, const void* q_dev, int q_dtype, int nq, 
   m.cand = ix->cand.as<uint64_t>();
   m.q_f32 = ix->q_f32.as<float>(); m.master = ix->master.p;
   m.master_is_bf16 = ix->master_dtype == B200_INDEX_MASTER_BF16;
-  m.out_ids = ids_dev; m.out_scores = sc_dev;
+  m.out_ids = ids_dev; m.out_scores = sc_dev; m.out_packed = packed_dev;
   uint32_t* fail_count = certify ? ix->cert.as<uint32_t>() : nullptr;
   uint32_t* ticket = certify ? ix->cert.as<uint32_t>() + 16 : nullptr;
   int32_t* fail_idx = certify ? reinterpret_cast<int32_t*>(ticket + nq) : nullptr;
@@ -369,7 +369,8 @@ static int search_chunk(b200_index* ix, const void* q_dev, int q_dtype, int nq, 
   B200_CUDA(cudaGetLastError());
   // queries the certificate turned down are redone exactly; the kernel returns at once when there are none
   if (certify)
-    B200_TRY(launch_exact<0>(ix, fail_count, fail_idx, ticket, nq, ix->q_f32.as<float>(), k, id_base, ids_dev, sc_dev, st));
+    B200_TRY(launch_exact<0>(ix, fail_count, fail_idx, ticket, nq, ix->q_f32.as<float>(), k, id_base, ids_dev, sc_dev, st,
+                             nullptr, 0, packed_dev));
   return B200_OK;
 }
 
@@ -631,7 +632,7 @@ int b200_index_get_rows(b200_index_t* ix, const int64_t* rows, int64_t n, float*
 
 // top_k in (48, EXH_KEEP]: exhaustive exact scoring, one query at a time (see search_kernels.cuh).
 static int search_exhaustive(b200_index* ix, const uint8_t* q_dev, int q_dtype, int64_t nq, int k, int64_t id_base,
-                             int64_t* d_ids, float* d_sc, cudaStream_t st) {
+                             int64_t* d_ids, float* d_sc, ulonglong2* d_packed, cudaStream_t st) {
   const uint32_t n_rows = (uint32_t)ix->count;
   const uint64_t chunks0 = ((uint64_t)n_rows + EXH_CHUNK - 1) / EXH_CHUNK;
   // scratch: fp32 copy of one query, keys of every row, two ping-pong survivor buffers
@@ -666,20 +667,20 @@ static int search_exhaustive(b200_index* ix, const uint8_t* q_dev, int q_dtype, 
       pp ^= 1;
       if (chunks == 1) break;
     }
-    exh_write_kernel<<<1, 256, 0, st>>>(in, EXH_KEEP, k, id_base, d_ids + q * k, d_sc + q * k);
+    exh_write_kernel<<<1, 256, 0, st>>>(in, EXH_KEEP, k, id_base, d_packed ? nullptr : d_ids + q * k,
+                                        d_packed ? nullptr : d_sc + q * k, d_packed ? d_packed + q * k : nullptr);
     B200_CUDA(cudaGetLastError());
   }
   return B200_OK;
 }
 
-extern "C" {
-
-int b200_index_search(b200_index_t* ix, const void* queries, int q_dtype, int queries_on_device, int64_t nq, int k,
-                      int64_t id_base, int64_t* ids, float* scores, int out_on_device, void* stream) {
+// b200_index_search and b200_index_search_packed: `packed` (device, [nq][k] 16-byte records) replaces ids / scores
+static int search_impl(b200_index* ix, const void* queries, int q_dtype, int queries_on_device, int64_t nq, int k,
+                       int64_t id_base, int64_t* ids, float* scores, ulonglong2* packed, int out_on_device, void* stream) {
   if (!ix) B200_FAIL(B200_ERR_INVALID, "index is NULL");
   if (nq < 0 || k < 0) B200_FAIL(B200_ERR_INVALID, "negative nq / k");
   if (nq == 0 || k == 0) return B200_OK;
-  if (!queries || !ids || !scores) B200_FAIL(B200_ERR_INVALID, "NULL buffer");
+  if (!queries || (!packed && (!ids || !scores))) B200_FAIL(B200_ERR_INVALID, "NULL buffer");
   if (q_dtype != 0 && q_dtype != 1) B200_FAIL(B200_ERR_INVALID, "q_dtype must be 0 (fp32) or 1 (bf16)");
   if (k > EXH_KEEP) B200_FAIL(B200_ERR_UNSUPPORTED, "k=%d: top_k above %d is not supported", k, EXH_KEEP);
   const int kp = k <= 10 ? 16 : (k <= 24 ? 32 : 64);
@@ -691,15 +692,16 @@ int b200_index_search(b200_index_t* ix, const void* queries, int q_dtype, int qu
 
   int64_t* d_ids = ids;
   float* d_sc = scores;
-  if (!out_on_device) {
+  if (!packed && !out_on_device) {
     B200_TRY(ix->out_ids.grow((size_t)nq * k * 8, 0, st));
     B200_TRY(ix->out_scores.grow((size_t)nq * k * 4, 0, st));
     d_ids = ix->out_ids.as<int64_t>();
     d_sc = ix->out_scores.as<float>();
   }
   if (ix->count == 0) {  // inmemory.py:93-94: empty store -> no results
-    B200_CUDA(cudaMemsetAsync(d_ids, 0xFF, (size_t)nq * k * 8, st));
-    B200_CUDA(cudaMemsetAsync(d_sc, 0, (size_t)nq * k * 4, st));
+    const size_t n = (size_t)nq * k;
+    fill_no_hits_kernel<<<(unsigned)std::min<size_t>((n + 255) / 256, 1024), 256, 0, st>>>(d_ids, d_sc, packed, n);
+    B200_CUDA(cudaGetLastError());
   } else {
     const uint8_t* q_dev = (const uint8_t*)queries;
     if (!queries_on_device) {
@@ -708,21 +710,54 @@ int b200_index_search(b200_index_t* ix, const void* queries, int q_dtype, int qu
       q_dev = ix->stage.as<uint8_t>();
     }
     if (k > 48) {
-      B200_TRY(search_exhaustive(ix, q_dev, q_dtype, nq, k, id_base, d_ids, d_sc, st));
+      B200_TRY(search_exhaustive(ix, q_dev, q_dtype, nq, k, id_base, d_ids, d_sc, packed, st));
     } else {
       for (int64_t q0 = 0; q0 < nq; q0 += kMaxQueryChunk) {
         const int n = (int)std::min<int64_t>(kMaxQueryChunk, nq - q0);
-        B200_TRY(search_chunk(ix, q_dev + (size_t)q0 * ix->dim * qelt, q_dtype, n, k, kp, id_base, d_ids + q0 * k,
-                              d_sc + q0 * k, st));
+        B200_TRY(search_chunk(ix, q_dev + (size_t)q0 * ix->dim * qelt, q_dtype, n, k, kp, id_base,
+                              packed ? nullptr : d_ids + q0 * k, packed ? nullptr : d_sc + q0 * k,
+                              packed ? packed + q0 * k : nullptr, st));
       }
     }
   }
-  if (!out_on_device) {
+  if (!packed && !out_on_device) {
     B200_CUDA(cudaMemcpyAsync(ids, d_ids, (size_t)nq * k * 8, cudaMemcpyDeviceToHost, st));
     B200_CUDA(cudaMemcpyAsync(scores, d_sc, (size_t)nq * k * 4, cudaMemcpyDeviceToHost, st));
   }
   B200_TRY(ix->order.leave(st));
-  if (!out_on_device) B200_CUDA(cudaStreamSynchronize(st));
+  if (!packed && !out_on_device) B200_CUDA(cudaStreamSynchronize(st));
+  return B200_OK;
+}
+
+extern "C" {
+
+int b200_index_search(b200_index_t* ix, const void* queries, int q_dtype, int queries_on_device, int64_t nq, int k,
+                      int64_t id_base, int64_t* ids, float* scores, int out_on_device, void* stream) {
+  return search_impl(ix, queries, q_dtype, queries_on_device, nq, k, id_base, ids, scores, nullptr, out_on_device, stream);
+}
+
+int b200_index_search_packed(b200_index_t* ix, const void* queries_dev, int q_dtype, int64_t nq, int k, int64_t id_base,
+                             void* hits_dev, void* stream) {
+  if (!hits_dev) B200_FAIL(B200_ERR_INVALID, "NULL buffer");
+  return search_impl(ix, queries_dev, q_dtype, 1, nq, k, id_base, nullptr, nullptr, static_cast<ulonglong2*>(hits_dev), 1, stream);
+}
+
+int b200_merge_hits(const void* hits_in, int nlists, int64_t nq_per_list, int k_in, int64_t q_first, int64_t nq, int k_out,
+                    int64_t* ids_out, float* scores_out, int device, void* stream) {
+  if (nq < 0 || nlists <= 0 || k_in <= 0 || k_out <= 0 || q_first < 0 || q_first + nq > nq_per_list)
+    B200_FAIL(B200_ERR_INVALID, "bad merge shape");
+  if (nq == 0) return B200_OK;
+  if (!hits_in || !ids_out || !scores_out) B200_FAIL(B200_ERR_INVALID, "NULL buffer");
+  if ((int64_t)nlists * k_in > 4096) B200_FAIL(B200_ERR_UNSUPPORTED, "nlists*k_in = %lld > 4096", (long long)nlists * k_in);
+  DeviceGuard g(device);
+  if (!g.ok) B200_FAIL(B200_ERR_CUDA, "cudaSetDevice(%d) failed", device);
+  const int wpb = 4;
+  {
+    B200_PROF("merge_hits", 0.0, (double)nq * nlists * k_in * 16.0, (cudaStream_t)stream);
+    merge_packed_kernel<<<(unsigned)((nq + wpb - 1) / wpb), wpb * 32, 0, (cudaStream_t)stream>>>(
+        static_cast<const ulonglong2*>(hits_in), nlists, (int)nq_per_list, k_in, (int)q_first, (int)nq, k_out, ids_out, scores_out);
+  }
+  B200_CUDA(cudaGetLastError());
   return B200_OK;
 }
 
@@ -968,7 +1003,7 @@ extern "C" int b200_index_search_static(b200_index_t* ix, const void* queries_de
   m.n_rows = (uint32_t)ix->count; m.id_base = id_base;
   m.cand = cand; m.q_f32 = q_f32; m.master = ix->master.p;
   m.master_is_bf16 = ix->master_dtype == B200_INDEX_MASTER_BF16;
-  m.out_ids = ids_dev; m.out_scores = scores_dev;
+  m.out_ids = ids_dev; m.out_scores = scores_dev; m.out_packed = nullptr;
   // same exactness certificate as b200_index_search, its bookkeeping inside the static array
   uint32_t* ticket = cert + 16;
   int32_t* fail_idx = reinterpret_cast<int32_t*>(ticket + kStaticMaxQueries);

@@ -211,6 +211,25 @@ struct SimParams {
   int split_major;        // 1: blockIdx.x = split, blockIdx.y = query tile (all splits of a tile run together)
 };
 
+// One search hit as a 16-byte record: x = orderable(score) << 32 (0 = no hit), y = global id (-1 = no hit).
+// This is what travels between GPUs: a shard's K9 writes records straight into the all-gather send buffer and
+// K10 reads the gathered buffer, with nothing in between.
+B200_DEVINL void write_hit(int64_t* ids, float* scores, ulonglong2* packed, size_t at, uint64_t key, int64_t id_base,
+                           bool negate_score) {
+  const bool hit = key != 0;
+  const int64_t id = hit ? id_base + (int64_t)(~(uint32_t)(key & 0xFFFFFFFFu)) : -1;
+  if (packed) {
+    ulonglong2 r;
+    r.x = hit ? (key & 0xFFFFFFFF00000000ull) : 0ull;
+    r.y = (unsigned long long)id;
+    packed[at] = r;
+  } else {
+    const float sc = orderable_f32((uint32_t)(key >> 32));
+    ids[at] = id;
+    scores[at] = hit ? (negate_score ? -sc : sc) : 0.f;
+  }
+}
+
 // (score, row) -> one 64-bit key whose unsigned order is "better first": higher score, then lower
 // row.  0 is reserved for "empty slot" (no real key is 0: orderable(-inf) is already 0x007FFFFF).
 B200_DEVINL uint64_t pack_key(float s, uint32_t id) {
@@ -554,6 +573,7 @@ struct MergeParams {
   int master_is_bf16;
   int64_t* out_ids;         // [nq, k]
   float* out_scores;        // [nq, k]
+  ulonglong2* out_packed;   // [nq, k] or nullptr: (orderable(score) << 32, global id) records instead of the two arrays
   // --- candidate-sufficiency certificate (all nullptr: skipped) ---
   const float2* qmeta;      // [nq] (inv_scale, r_q) from prep_queries_kernel
   const uint32_t* rvmax;    // float bits: max over rows of || unit row - its half image ||_2
@@ -628,16 +648,8 @@ __global__ void __launch_bounds__(256) merge_rescore_kernel(const MergeParams p)
       p.fail_idx[atomicAdd(p.fail_count, 1u)] = q;
     }
   }
-  for (int j = threadIdx.x; j < p.k; j += blockDim.x) {
-    const uint64_t key = (j < 64) ? fin[j] : 0;
-    if (key) {
-      p.out_ids[(size_t)q * p.k + j] = p.id_base + (int64_t)(~(uint32_t)(key & 0xFFFFFFFFu));
-      p.out_scores[(size_t)q * p.k + j] = orderable_f32((uint32_t)(key >> 32));
-    } else {
-      p.out_ids[(size_t)q * p.k + j] = -1;
-      p.out_scores[(size_t)q * p.k + j] = 0.f;
-    }
-  }
+  for (int j = threadIdx.x; j < p.k; j += blockDim.x)
+    write_hit(p.out_ids, p.out_scores, p.out_packed, (size_t)q * p.k + j, (j < 64) ? fin[j] : 0ull, p.id_base, false);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -671,6 +683,7 @@ struct ExactParams {
   uint32_t* ticket;             // [nq] zeroed before the launch; gridDim.x + 1 = that query's result is written
   int64_t* out_ids;
   float* out_scores;
+  ulonglong2* out_packed;       // see MergeParams
 };
 
 // FAISS IndexFlatL2 semantics (faiss_store.py:99-101,212-224): squared Euclidean distance, ascending; the
@@ -777,17 +790,9 @@ __global__ void __launch_bounds__(EXACT_THREADS) exact_topk_kernel(const ExactPa
         __syncthreads();
         bitonic_sort_desc(mkeys, EXACT_MERGE);
       }
-      for (int t = threadIdx.x; t < p.k; t += blockDim.x) {
-        const uint64_t key = t < EXACT_KEEP ? mkeys[t] : 0ull;
-        if (key) {
-          p.out_ids[(size_t)q * p.k + t] = p.id_base + (int64_t)(~(uint32_t)(key & 0xFFFFFFFFu));
-          const float sc = orderable_f32((uint32_t)(key >> 32));
-          p.out_scores[(size_t)q * p.k + t] = METRIC_L2 ? -sc : sc;
-        } else {
-          p.out_ids[(size_t)q * p.k + t] = -1;
-          p.out_scores[(size_t)q * p.k + t] = 0.f;
-        }
-      }
+      for (int t = threadIdx.x; t < p.k; t += blockDim.x)
+        write_hit(p.out_ids, p.out_scores, p.out_packed, (size_t)q * p.k + t, t < EXACT_KEEP ? mkeys[t] : 0ull, p.id_base,
+                  METRIC_L2 != 0);
       __syncthreads();
       if (threadIdx.x == 0) {
         __threadfence();
@@ -847,17 +852,16 @@ __global__ void exh_query_f32_kernel(const __nv_bfloat16* __restrict__ q, int d,
 
 // the single surviving sorted list -> ids / scores of one query
 __global__ void exh_write_kernel(const uint64_t* __restrict__ keys, int n_keys, int k, int64_t id_base,
-                                 int64_t* __restrict__ ids, float* __restrict__ scores) {
-  for (int j = threadIdx.x; j < k; j += blockDim.x) {
-    const uint64_t key = j < n_keys ? keys[j] : 0ull;
-    if (key) {
-      ids[j] = id_base + (int64_t)(~(uint32_t)(key & 0xFFFFFFFFu));
-      scores[j] = orderable_f32((uint32_t)(key >> 32));
-    } else {
-      ids[j] = -1;
-      scores[j] = 0.f;
-    }
-  }
+                                 int64_t* __restrict__ ids, float* __restrict__ scores, ulonglong2* __restrict__ packed) {
+  for (int j = threadIdx.x; j < k; j += blockDim.x)
+    write_hit(ids, scores, packed, (size_t)j, j < n_keys ? keys[j] : 0ull, id_base, false);
+}
+
+// "no rows": every slot of an [n] result is the empty hit
+__global__ void fill_no_hits_kernel(int64_t* __restrict__ ids, float* __restrict__ scores, ulonglong2* __restrict__ packed,
+                                    size_t n) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+    write_hit(ids, scores, packed, i, 0ull, 0, false);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -902,6 +906,47 @@ __global__ void __launch_bounds__(128) merge_lists_kernel(const int64_t* __restr
     } else {
       if (lane == 0) { ids_out[(size_t)q * k_out + j] = best_id; sc_out[(size_t)q * k_out + j] = best_s; }
       prev_s = best_s; prev_id = best_id;
+    }
+  }
+}
+
+// K10 over packed records (see write_hit): lists arrive as [nlists][nq_per_list][k_in] -- exactly the buffer an
+// all-gather of every shard's K9 output produces -- and this GPU merges queries [q_first, q_first + nq).
+__global__ void __launch_bounds__(128) merge_packed_kernel(const ulonglong2* __restrict__ in, int nlists, int nq_per_list,
+                                                           int k_in, int q_first, int nq, int k_out,
+                                                           int64_t* __restrict__ ids_out, float* __restrict__ sc_out) {
+  const int q = blockIdx.x * (blockDim.x / kWarp) + (threadIdx.x / kWarp);
+  if (q >= nq) return;
+  const int lane = threadIdx.x & 31;
+  const int total = nlists * k_in;
+  // (x desc, id asc) as one comparison: x carries the orderable score in its high half, ids are non-negative
+  unsigned long long prev_x = ~0ull;
+  long long prev_id = -1;
+  for (int j = 0; j < k_out; ++j) {
+    unsigned long long best_x = 0ull;
+    long long best_id = INT64_MAX;
+    for (int i = lane; i < total; i += kWarp) {
+      const int l = i / k_in, e = i - l * k_in;
+      const ulonglong2 r = __ldg(in + ((size_t)l * nq_per_list + q_first + q) * k_in + e);
+      const long long id = (long long)r.y;
+      if (id < 0) continue;
+      const bool after = (r.x < prev_x) || (r.x == prev_x && id > prev_id);
+      if (!after) continue;
+      if (r.x > best_x || (r.x == best_x && id < best_id)) { best_x = r.x; best_id = id; }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const unsigned long long ox = shfl_xor_u64(best_x, o);
+      const long long oi = (long long)shfl_xor_u64((uint64_t)best_id, o);
+      if (ox > best_x || (ox == best_x && oi < best_id)) { best_x = ox; best_id = oi; }
+    }
+    const size_t at = (size_t)q * k_out + j;
+    if (best_id == INT64_MAX) {
+      if (lane == 0) { ids_out[at] = -1; sc_out[at] = 0.f; }
+      prev_x = 0ull; prev_id = INT64_MAX;
+    } else {
+      if (lane == 0) { ids_out[at] = best_id; sc_out[at] = orderable_f32((uint32_t)(best_x >> 32)); }
+      prev_x = best_x; prev_id = best_id;
     }
   }
 }

@@ -37,14 +37,20 @@ class EncoderConfig:
         return self.hidden // self.heads
 
 
-#: architectures BASELINE.json names
+#: architectures BASELINE.json names.  configs[3] is "mpnet-base-class 768-d encoder (12 layers, seq 384)": the SHAPE
+#: of all-mpnet-base-v2 on the BERT architecture this path implements.  The real all-mpnet-base-v2 checkpoint is an
+#: MPNetModel (relative position bias, other state_dict keys, another tokenizer) and is refused by load_model_dir.
 KNOWN_ARCHS = {
     "all-MiniLM-L6-v2": EncoderConfig(),
-    "all-mpnet-base-v2": EncoderConfig(hidden=768, layers=12, heads=12, intermediate=3072, max_seq_length=384),
+    "bert-base-class": EncoderConfig(hidden=768, layers=12, heads=12, intermediate=3072, max_seq_length=384),
 }
 
 
 def config_from_hf(d: dict, max_seq_length: int | None = None) -> EncoderConfig:
+    mt = d.get("model_type", "bert")
+    if mt != "bert":
+        raise ValueError(f"model_type {mt!r} is not supported: this provider implements the BERT architecture only "
+                         "(MPNet, RoBERTa, DistilBERT... differ in position handling, parameter names or tokenizer)")
     if d.get("hidden_act", "gelu") != "gelu":
         raise ValueError(f"unsupported hidden_act {d.get('hidden_act')!r}: only exact-erf gelu is implemented")
     if d.get("position_embedding_type", "absolute") != "absolute":
@@ -159,16 +165,48 @@ def write_random_model(path: str, arch: str | EncoderConfig = "all-MiniLM-L6-v2"
               os.path.join(path, "model.safetensors"))
     with open(os.path.join(path, "b200_random_init.json"), "w") as f:
         json.dump({"seed": seed, "config": asdict(cfg)}, f)
+    # the sentence-transformers module stack of all-MiniLM-L6-v2: Transformer -> mean Pooling -> Normalize
+    with open(os.path.join(path, "modules.json"), "w") as f:
+        json.dump([{"idx": 0, "name": "0", "path": "", "type": "sentence_transformers.models.Transformer"},
+                   {"idx": 1, "name": "1", "path": "1_Pooling", "type": "sentence_transformers.models.Pooling"},
+                   {"idx": 2, "name": "2", "path": "2_Normalize", "type": "sentence_transformers.models.Normalize"}], f, indent=1)
+    os.makedirs(os.path.join(path, "1_Pooling"), exist_ok=True)
+    with open(os.path.join(path, "1_Pooling", "config.json"), "w") as f:
+        json.dump({"word_embedding_dimension": cfg.hidden, "pooling_mode_cls_token": False, "pooling_mode_mean_tokens": True,
+                   "pooling_mode_max_tokens": False, "pooling_mode_mean_sqrt_len_tokens": False}, f, indent=1)
     return path
+
+
+def check_module_stack(path: str) -> None:
+    """``SentenceTransformer.encode`` runs whatever ``modules.json`` lists.  The kernels implement exactly one
+    stack -- Transformer -> masked-mean Pooling -> Normalize (all-MiniLM-L6-v2's) -- so anything else (CLS or max
+    pooling, no Normalize stage, a Dense head) is refused instead of silently returning other embeddings than the
+    library would.  A bare HuggingFace directory without ``modules.json`` is what sentence-transformers wraps in
+    Transformer + mean Pooling; there the Normalize stage is this provider's documented addition."""
+    mj = os.path.join(path, "modules.json")
+    if not os.path.isfile(mj):
+        return
+    with open(mj) as f:
+        mods = json.load(f)
+    kinds = [str(m.get("type", "")).rsplit(".", 1)[-1] for m in mods]
+    if kinds != ["Transformer", "Pooling", "Normalize"]:
+        raise ValueError(f"unsupported sentence-transformers module stack {kinds}: only Transformer -> Pooling(mean) -> "
+                         "Normalize is implemented")
+    pool_dir = os.path.join(path, str(mods[1].get("path", "1_Pooling")))
+    pc = os.path.join(pool_dir, "config.json")
+    if os.path.isfile(pc):
+        with open(pc) as f:
+            cfg = json.load(f)
+        modes = {k: bool(v) for k, v in cfg.items() if k.startswith("pooling_mode_")}
+        on = sorted(k for k, v in modes.items() if v)
+        if on != ["pooling_mode_mean_tokens"]:
+            raise ValueError(f"unsupported pooling {on}: only pooling_mode_mean_tokens is implemented")
 
 
 def resolve_model_dir(model_name: str, cache_dir: str | None) -> str | None:
     """Where ``SentenceTransformer(model_name, cache_folder=cache_dir)`` would find local files."""
     cands = [model_name]
-    roots = [cache_dir] if cache_dir else []
-    env = os.environ.get("SENTENCE_TRANSFORMERS_HOME")
-    if env:
-        roots.append(env)
+    roots = [cache_dir] if cache_dir else []   # no environment lookups: the reference pins adapters to that
     for root in roots:
         cands += [
             os.path.join(root, model_name),
@@ -185,6 +223,7 @@ def resolve_model_dir(model_name: str, cache_dir: str | None) -> str | None:
 
 def load_model_dir(path: str) -> tuple[EncoderConfig, dict[str, torch.Tensor], list[str], bool]:
     """-> (config, fp32 state dict with the ``bert.`` prefix stripped, vocab, do_lower_case)."""
+    check_module_stack(path)
     tdir = os.path.join(path, "0_Transformer") if os.path.isfile(os.path.join(path, "0_Transformer", "config.json")) else path
     with open(os.path.join(tdir, "config.json")) as f:
         hf = json.load(f)

@@ -101,16 +101,22 @@ class B200SentenceTransformerProvider(EmbeddingProvider):
         """One embedding per text, same validation as :meth:`embed` applied to every element."""
         return self.embed_array(texts).tolist()
 
-    def embed_array(self, texts: Sequence[str]) -> np.ndarray:
+    def embed_array(self, texts: Sequence[str], to_host: bool = True):
         """``[len(texts), dimension]`` fp32.  Texts are bucketed by token length so that short chunks
-        do not pay for the longest one's padding."""
+        do not pay for the longest one's padding.  ``to_host=False`` leaves the result on the GPU (a CUDA
+        tensor), e.g. to feed ``B200VectorStore.query_batch`` without a host round trip."""
         for t in texts:
             if t is None:
                 raise ValueError("Text cannot be None")
             if not t.strip():
                 raise ValueError("Text cannot be empty or whitespace-only")
         n = len(texts)
-        out = np.empty((n, self.dimension), dtype=np.float32)
+        if to_host:
+            out = np.empty((n, self.dimension), dtype=np.float32)
+        else:
+            import torch
+
+            out = torch.empty((n, self.dimension), dtype=torch.float32, device=f"cuda:{self._dev}")
         if n == 0:
             return out
         all_ids, all_lens = self.tokenizer.encode_arrays(texts, self.max_seq_length)
@@ -132,7 +138,12 @@ class B200SentenceTransformerProvider(EmbeddingProvider):
             w = min(S, all_ids.shape[1])
             ids[:, :w] = all_ids[sel, :w]
             lens = np.ascontiguousarray(all_lens[sel])
-            out[sel] = self._encode_host(ids, lens)
+            if to_host:
+                out[sel] = self._encode_host(ids, lens)
+            else:
+                dev = out.device
+                emb = self.embed_tokens(torch.from_numpy(ids).to(dev), torch.from_numpy(lens).to(dev))
+                out[torch.from_numpy(np.ascontiguousarray(sel)).to(dev)] = emb
             i = j
         return out
 

@@ -87,6 +87,23 @@ class B200Index:
                                               self._stream()))
         return ids, sc
 
+    def search_packed(self, queries: Any, k: int, id_base: int, hits_out: Any) -> None:
+        """``b200_index_search_packed``: hits as 16-byte records into ``hits_out`` -- a contiguous CUDA int64 tensor
+        ``[nq, k, 2]`` (``[..., 0]`` = orderable score bits << 32, ``[..., 1]`` = global id), typically the send buffer of
+        an all-gather (see ``sharded.py``)."""
+        import torch
+
+        if not (isinstance(queries, torch.Tensor) and queries.is_cuda and queries.is_contiguous() and queries.shape[1] == self.dim
+                and queries.dtype in (torch.float32, torch.bfloat16) and queries.device.index == self.device):
+            raise ValueError(f"queries must be a contiguous float32/bfloat16 CUDA tensor [nq, {self.dim}] on cuda:{self.device}")
+        nq = queries.shape[0]
+        if not (isinstance(hits_out, torch.Tensor) and hits_out.is_cuda and hits_out.is_contiguous() and hits_out.dtype == torch.int64
+                and tuple(hits_out.shape) == (nq, k, 2)):
+            raise ValueError("hits_out must be a contiguous CUDA int64 tensor [nq, k, 2]")
+        nat.check(self._lib.b200_index_search_packed(self._h, ctypes.c_void_p(queries.data_ptr()),
+                                                     0 if queries.dtype == torch.float32 else 1, nq, k, id_base,
+                                                     ctypes.c_void_p(hits_out.data_ptr()), self._stream()))
+
     def search_l2(self, queries: Any, k: int = 10, id_base: int = 0):
         """``b200_index_search_l2``: the k nearest rows by squared Euclidean distance (FAISS-flat semantics,
         faiss_store.py:99-101,212-224): ``(ids[nq, k], squared distances[nq, k])`` ascending; fp32 queries, k <= 64."""

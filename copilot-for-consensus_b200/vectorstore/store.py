@@ -339,6 +339,29 @@ class B200VectorStore(VectorStore):
         with self._lock:
             return [[self._ids[int(r)] if r >= 0 else None for r in row] for row in rows]
 
+    def metadata_for_ids(self, ids: Sequence[str]) -> dict[str, dict[str, Any]]:
+        """Copies of the stored metadata dicts (what ``SearchResult.metadata`` carries, inmemory.py:125)."""
+        with self._lock:
+            return {i: self._metadata[i].copy() for i in ids}
+
+    def mean_vector_where(self, key: str, value: Any) -> list[float] | None:
+        """Arithmetic mean (fp32) of the stored vectors whose metadata has ``metadata[key] == value``, in
+        insertion order; None when there is none.  Rows are gathered on the GPU (``b200_index_get_rows`` into
+        a device buffer) and averaged there; ``dim`` floats come back."""
+        import torch
+
+        with self._lock:
+            ids = [i for i in self._ids if i is not None and self._metadata[i].get(key) == value]
+            if not ids:
+                return None
+            self._flush_deletes()
+            rows = np.ascontiguousarray([self._row_of[i] for i in ids], dtype=np.int64)
+            with torch.cuda.device(self._device):
+                out = torch.empty((len(rows), self._dim), dtype=torch.float32, device=f"cuda:{self._device}")
+                nat.check(self._lib.b200_index_get_rows(self._h, _as_ptr(rows), len(rows), ctypes.c_void_p(out.data_ptr()), 1,
+                                                        self._stream()))
+                return out.mean(dim=0).cpu().tolist()
+
     def delete(self, id: str) -> None:
         """inmemory.py:130-143."""
         with self._lock:

@@ -152,6 +152,18 @@ int b200_index_search_l2(b200_index_t* idx, const void* queries, int q_dtype, in
 int b200_index_search_static(b200_index_t* idx, const void* queries_dev, int q_dtype, int64_t nq, int k,
                              int64_t id_base, int64_t* ids_dev, float* scores_dev, void* stream);
 
+/* Multi-GPU search without glue kernels (no reference counterpart: the reference is single-process).
+ * b200_index_search_packed is b200_index_search writing each hit as ONE 16-byte record
+ *   { uint64 orderable(score) << 32 (0 = no hit), int64 id_base + row (-1 = no hit) }
+ * into hits_dev[nq*k] -- which may be the send buffer of an all-gather.  b200_merge_hits takes the gathered
+ * buffer, laid out [nlists][nq_per_list][k_in] (list l = shard l's records), and writes the k_out best of
+ * queries [q_first, q_first + nq) under (score desc, id asc) as ids_out[nq*k_out] / scores_out[nq*k_out].
+ * Everything is a device pointer; between a shard's search and the merge there is the collective and nothing else. */
+int b200_index_search_packed(b200_index_t* idx, const void* queries_dev, int q_dtype, int64_t nq, int k,
+                             int64_t id_base, void* hits_dev, void* stream);
+int b200_merge_hits(const void* hits_in, int nlists, int64_t nq_per_list, int k_in, int64_t q_first, int64_t nq,
+                    int k_out, int64_t* ids_out, float* scores_out, int device, void* stream);
+
 /* Multi-GPU candidate merge (no reference counterpart: the reference is single-process).  After an
  * all-gather of per-shard results laid out [nlists][nq][k_in], keep the best k_out per query under
  * the same (score desc, id asc) order.  All pointers are device pointers. */

@@ -101,4 +101,4 @@ if __name__ == "__main__":
     one_layer(256, 4, 512, 128)      # head dim 64
     full("all-MiniLM-L6-v2", 8, 256, False)
     full("all-MiniLM-L6-v2", 16, 256, True)
-    full("all-mpnet-base-v2", 2, 384, True)
+    full("bert-base-class", 2, 384, True)

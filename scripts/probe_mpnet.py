@@ -7,7 +7,7 @@ P = "copilot-for-consensus_b200"
 mio = importlib.import_module(P + ".embedding.model_io")
 prov_mod = importlib.import_module(P + ".embedding.provider")
 with tempfile.TemporaryDirectory() as td:
-    mio.write_random_model(td, "all-mpnet-base-v2", seed=0)
+    mio.write_random_model(td, "bert-base-class", seed=0)
     prov = prov_mod.B200SentenceTransformerProvider(model_name=td, device="cuda:0")
 B, S = 128, 384
 ids = torch.randint(1000, 30522, (B, S), dtype=torch.int32, device="cuda")

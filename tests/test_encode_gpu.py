@@ -167,7 +167,7 @@ def test_small_architectures_head_dims():
 @pytest.mark.slow
 def test_mpnet_base_class_matches_fp32_oracle():
     """BASELINE.json configs[3] architecture: 768-d, 12 layers, 12 heads x 64, seq 384."""
-    p = _provider("all-mpnet-base-v2", seed=0)
+    p = _provider("bert-base-class", seed=0)
     ids, mask, lens = eo.synthetic_tokens(4, 384, 30522, seed=11, ragged=True)
     got = p.embed_tokens(ids.numpy(), lens.numpy())
     _check(got, eo.encode(eo.MPNET_BASE_CLASS, eo.make_weights(eo.MPNET_BASE_CLASS, seed=0), ids, mask).numpy())

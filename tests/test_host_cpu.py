@@ -82,3 +82,31 @@ def test_bench_reference_arm_prints_the_contract_line():
     line = json.loads(out.stdout.strip().splitlines()[-1])
     assert line["impl"] == "reference" and line["unit"] == "chunks/s" and line["value"] > 0
     assert line["cpu_baseline"]["kind"] == "port" and line["e2e"]["h2d_bytes_per_step"] == 0
+
+
+def test_model_dir_refuses_other_module_stacks_and_architectures(tmp_path):
+    """SentenceTransformer.encode runs what modules.json lists; only Transformer -> mean Pooling -> Normalize on a
+    BERT-architecture checkpoint is implemented, anything else must fail at load instead of embedding differently."""
+    mio = pkg("embedding.model_io")
+    cfg = mio.EncoderConfig(vocab_size=1500, hidden=128, layers=1, heads=4, intermediate=256, max_pos=64, max_seq_length=48)
+    d = mio.write_random_model(str(tmp_path / "m"), cfg, seed=1)
+    mio.load_model_dir(d)                                              # the stack write_random_model lays down is accepted
+    pc = os.path.join(d, "1_Pooling", "config.json")
+    pool = json.load(open(pc))
+    pool.update(pooling_mode_cls_token=True, pooling_mode_mean_tokens=False)
+    json.dump(pool, open(pc, "w"))
+    with pytest.raises(ValueError, match="unsupported pooling"):
+        mio.load_model_dir(d)
+    pool.update(pooling_mode_cls_token=False, pooling_mode_mean_tokens=True)
+    json.dump(pool, open(pc, "w"))
+    mods = json.load(open(os.path.join(d, "modules.json")))
+    json.dump(mods[:2], open(os.path.join(d, "modules.json"), "w"))    # no Normalize stage (paraphrase-MiniLM-* style)
+    with pytest.raises(ValueError, match="module stack"):
+        mio.load_model_dir(d)
+    json.dump(mods, open(os.path.join(d, "modules.json"), "w"))
+    hf = json.load(open(os.path.join(d, "config.json")))
+    hf["model_type"] = "mpnet"
+    json.dump(hf, open(os.path.join(d, "config.json"), "w"))
+    with pytest.raises(ValueError, match="model_type 'mpnet'"):
+        mio.load_model_dir(d)
+    assert "all-mpnet-base-v2" not in mio.KNOWN_ARCHS and mio.KNOWN_ARCHS["bert-base-class"].hidden == 768

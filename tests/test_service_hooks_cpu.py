@@ -133,3 +133,76 @@ def test_b200_adapters_take_the_batched_calls(golden):
     assert ids == golden["store_calls"][0]["ids"] and metas == golden["store_calls"][0]["metadatas"]
     assert arr.dtype == np.float32 and arr.shape == (len(out), 8)
     np.testing.assert_array_equal(arr, np.asarray(golden["store_calls"][0]["vectors"], dtype=np.float32))
+
+
+# ---- query side: goldens recorded from the REAL reference methods by oracle/gen_query_golden.py
+@pytest.fixture(scope="module")
+def qgolden():
+    with open(os.path.join(GOLDEN, "query_side_golden.json"), encoding="utf-8") as f:
+        return json.load(f)
+
+
+class _TableProvider:
+    def __init__(self, table):
+        self.table = table
+
+    def embed(self, text):
+        return self.table[text]
+
+
+def _port_store(g):
+    from oracle.search_oracle import InMemoryPort
+
+    st = InMemoryPort()
+    st.add_embeddings(g["ids"], g["vectors"], g["metadatas"])
+    return st
+
+
+def check_topic_golden(hooks, provider, store, g, atol):
+    for key, want in g["search_reports_by_topic"].items():
+        topic, limit, min_score = key.split("|")
+        got = hooks.rank_threads_by_topic(provider, store, topic, limit=int(limit), min_score=float(min_score))
+        assert [t for t, _ in got] == [w["thread_id"] for w in want], key
+        for (_t, s), w in zip(got, want):
+            assert s["chunk_count"] == w["matching_chunks"] == len(s["chunks"])
+            assert abs(s["max_score"] - w["relevance_score"]) <= atol and abs(s["avg_score"] - w["avg_relevance_score"]) <= atol
+
+
+def test_rank_threads_by_topic_equals_the_reference_method(qgolden):
+    """reporting/app/service.py:819-864 through the hook, on the store port: same threads, same order, same max /
+    running-mean / count as ReportingService.search_reports_by_topic returned in the build container."""
+    hooks = pkg("service_hooks")
+    check_topic_golden(hooks, _TableProvider(qgolden["topics"]), _port_store(qgolden), qgolden, atol=3e-7)
+    # the batched form falls back to the per-topic loop for adapters that are not the B200 ones
+    topics = list(qgolden["topics"])
+    many = hooks.rank_threads_by_topics(_TableProvider(qgolden["topics"]), _port_store(qgolden), topics, limit=2, min_score=0.0)
+    for t, got in zip(topics, many):
+        assert [x for x, _ in got] == [w["thread_id"] for w in qgolden["search_reports_by_topic"][f"{t}|2|0.0"]]
+    with pytest.raises(ValueError, match="Topic search requires vector store and embedding provider"):
+        hooks.rank_threads_by_topic(None, _port_store(qgolden), "x")
+    bad = Mock()
+    bad.embed.side_effect = RuntimeError("boom")
+    with pytest.raises(ValueError, match="Failed to generate topic embedding: boom"):
+        hooks.rank_threads_by_topic(bad, _port_store(qgolden), "x")
+    badst = Mock()
+    badst.query.side_effect = RuntimeError("down")
+    with pytest.raises(ValueError, match="Vector store query failed: down"):
+        hooks.rank_threads_by_topic(_TableProvider({"x": [0.0] * 16}), badst, "x")
+
+
+def test_thread_query_vector_is_the_mean_of_the_threads_rows(qgolden):
+    """The vector the orchestrator never passes (orchestrator/app/service.py:559-565): with it, the reference's
+    own ThreadChunksSource.get_candidates returned relevance-ordered chunks (golden) instead of neutral 0.5 scores."""
+    hooks = pkg("service_hooks")
+    st = _port_store(qgolden)
+    for t, rec in qgolden["get_candidates"].items():
+        q = hooks.thread_candidates_query(st, t, top_k=12, min_score=0.0)
+        np.testing.assert_array_equal(np.float32(q["query_vector"]), np.float32(rec["query_vector"]))
+        assert q["top_k"] == 12 and q["min_score"] == 0.0
+        res = st.query(q["query_vector"], top_k=12)
+        mine = [r.id for r in res if r.metadata.get("thread_id") in (None, t)]       # context_sources.py:160-166 thread filter
+        assert mine == [c["_id"] for c in rec["candidates"]]
+        assert all(c["similarity_score"] == 0.5 for c in rec["fallback"])    # what the services get today
+    assert hooks.thread_query_vector(st, "no-such-thread") is None
+    assert hooks.thread_candidates_query(st, "no-such-thread") == {"top_k": 50}
+    assert hooks.thread_query_vector(Mock(), "tA") is None                   # unknown store type: no vector, reference fallback

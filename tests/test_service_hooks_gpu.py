@@ -41,3 +41,56 @@ def test_batched_hooks_equal_per_text_pattern():
     with pytest.raises(ValueError, match="already exists"):
         hooks.store_embeddings(st_a, embs[:2])               # the in-memory slot raises on an existing id
     prov.close()
+
+
+def test_query_side_hooks_on_the_b200_store_match_the_reference_goldens():
+    """Row f3 with the real B200 store: topic ranking and the thread-mean query vector give what the reference
+    methods gave (tests/golden/query_side_golden.json, recorded by oracle/gen_query_golden.py)."""
+    import json
+    import os
+
+    from conftest import GOLDEN
+    from test_service_hooks_cpu import _TableProvider, check_topic_golden
+
+    hooks, vs = pkg("service_hooks"), pkg("vectorstore")
+    g = json.load(open(os.path.join(GOLDEN, "query_side_golden.json"), encoding="utf-8"))
+    st = vs.B200VectorStore(device="cuda:0")
+    st.add_embeddings(g["ids"], g["vectors"], g["metadatas"])
+    check_topic_golden(hooks, _TableProvider(g["topics"]), st, g, atol=3e-7)
+    for t, rec in g["get_candidates"].items():
+        q = hooks.thread_candidates_query(st, t, top_k=12, min_score=0.0)
+        np.testing.assert_allclose(q["query_vector"], rec["query_vector"], rtol=0, atol=1e-6)   # GPU mean: other summation order
+        res = st.query(rec["query_vector"], top_k=12)
+        assert [r.id for r in res if r.metadata.get("thread_id") in (None, t)] == [c["_id"] for c in rec["candidates"]]
+        np.testing.assert_allclose([r.score for r in res if r.metadata.get("thread_id") in (None, t)],
+                                   [c["similarity_score"] for c in rec["candidates"]], rtol=0, atol=3e-7)
+    assert hooks.thread_query_vector(st, "no-such-thread") is None
+    st.close()
+
+
+def test_batched_topic_search_equals_the_per_topic_loop_and_upsert_is_honoured():
+    hooks, mio = pkg("service_hooks"), pkg("embedding.model_io")
+    prov_mod, vs = pkg("embedding.provider"), pkg("vectorstore")
+    with tempfile.TemporaryDirectory() as td:
+        mio.write_random_model(td, "all-MiniLM-L6-v2", seed=4)
+        prov = prov_mod.B200SentenceTransformerProvider(model_name=td, device="cuda:0")
+    words = ["ba", "be", "bi", "bo", "bu", "ca", "ce", "ci", "co", "cu", "da", "de"]
+    chunks = [{"_id": f"c{i}", "text": " ".join(words[(i * 5 + j * (1 + i % 3)) % 12] for j in range(4 + (i * 11) % 60)),
+               "thread_id": f"t{i % 7}"} for i in range(120)]
+    embs = hooks.generate_batch_embeddings(prov, chunks, "m", "b", now=lambda: "<now>")
+    st = vs.B200VectorStore(device="cuda:0", upsert=True)
+    hooks.store_embeddings(st, embs)
+    hooks.store_embeddings(st, embs[:10])            # upsert=True: re-embedding a chunk replaces it (ADVICE r1)
+    assert st.count() == 120
+    assert st.ids_for_rows(np.arange(110, 120)[None])[0] == [e["id"] for e in embs[:10]]   # replaced rows go to the end
+    topics = [c["text"] for c in chunks[::17]] + ["bo bu ca"]
+    many = hooks.rank_threads_by_topics(prov, st, topics, limit=4, min_score=0.2)
+    for t, got in zip(topics, many):
+        one = hooks.rank_threads_by_topic(prov, st, t, limit=4, min_score=0.2)
+        assert [x for x, _ in got] == [x for x, _ in one]
+        for (_a, sa), (_b, sb) in zip(got, one):
+            assert sa["chunks"] == sb["chunks"] and abs(sa["max_score"] - sb["max_score"]) <= 2e-3
+    with pytest.raises(ValueError, match="Failed to generate topic embedding"):
+        hooks.rank_threads_by_topics(prov, st, ["ok", "  "])
+    prov.close()
+    st.close()

@@ -1,7 +1,8 @@
 """Host-side logic of the row-sharded search on CPU: two ``gloo`` ranks, the CUDA local search and
 merge kernel replaced by numpy stand-ins through ShardedSearch's injection points, so that shard
 ranges, id offsets, gather layouts and the per-rank query slicing are exercised without a GPU.
-(The CUDA merge kernel itself is checked on the GPU in tests/test_search_gpu.py::test_merge_topk_abi.)"""
+The stand-ins speak the same 16-byte hit-record format as b200_index_search_packed / b200_merge_hits; the CUDA
+kernels behind those two are checked on the GPU (tests/test_sharded_gpu.py, also with a single rank)."""
 import os
 import socket
 
@@ -21,15 +22,35 @@ def _free_port() -> int:
         return s.getsockname()[1]
 
 
-def _merge_numpy(ids_in: torch.Tensor, sc_in: torch.Tensor, k: int):
-    ids_in, sc_in = ids_in.numpy(), sc_in.numpy()
-    nl, nq, kin = ids_in.shape
+def _orderable(sc: np.ndarray) -> np.ndarray:
+    """fp32 -> uint32 whose unsigned order is the float order (common.cuh f32_orderable)."""
+    u = np.ascontiguousarray(sc, np.float32).view(np.uint32)
+    return np.where(u & 0x80000000, ~u, u | 0x80000000).astype(np.uint32)
+
+
+def _unorderable(o: np.ndarray) -> np.ndarray:
+    o = o.astype(np.uint32)
+    return np.where(o & 0x80000000, o & 0x7FFFFFFF, ~o).astype(np.uint32).view(np.float32)
+
+
+def _pack_numpy(ids: np.ndarray, sc: np.ndarray) -> np.ndarray:
+    """The 16-byte hit record of b200_index_search_packed, as [nq, k, 2] int64."""
+    x = (_orderable(sc).astype(np.uint64) << np.uint64(32))
+    x = np.where(ids >= 0, x, np.uint64(0))
+    return np.stack([x.view(np.int64), ids.astype(np.int64)], axis=-1)
+
+
+def _merge_numpy(gathered: torch.Tensor, q_first: int, nq: int, k: int):
+    g = gathered.numpy()
+    nl, _per, kin, _ = g.shape
     out_i = np.full((nq, k), -1, np.int64)
     out_s = np.zeros((nq, k), np.float32)
     for q in range(nq):
-        cand = sorted((-float(sc_in[l, q, e]), int(ids_in[l, q, e])) for l in range(nl) for e in range(kin) if ids_in[l, q, e] >= 0)
-        for j, (ns, i) in enumerate(cand[:k]):
-            out_i[q, j], out_s[q, j] = i, -ns
+        rec = g[:, q_first + q].reshape(nl * kin, 2)
+        rec = rec[rec[:, 1] >= 0]
+        order = np.lexsort((rec[:, 1], -(rec[:, 0].view(np.uint64) >> np.uint64(32)).astype(np.int64)))[:k]
+        out_i[q, : len(order)] = rec[order, 1]
+        out_s[q, : len(order)] = _unorderable(rec[order, 0].view(np.uint64) >> np.uint64(32))
     return torch.from_numpy(out_i), torch.from_numpy(out_s)
 
 
@@ -46,10 +67,10 @@ def _worker(rank: int, world: int, port: int, n_rows: int, ret):
         r0, r1 = sh.shard_range(n_rows, world, rank)
         shard = rows[r0:r1]
 
-        def local_search(q, k, base):
+        def local_search(q, k, base, hits_out):
             ids, sc = so.topk_canonical(q.numpy(), shard, k)
             ids = np.where(ids >= 0, ids + base, ids)
-            return torch.from_numpy(ids), torch.from_numpy(sc)
+            hits_out.copy_(torch.from_numpy(_pack_numpy(ids, sc)))
 
         ss = sh.ShardedSearch(local_search, r0, merge=_merge_numpy)
         want_i, want_s = so.topk_canonical(q_all, rows, 10)

@@ -62,3 +62,45 @@ def test_two_gpu_sharded_search_equals_single_index():
         ok1, ok2, first, second = ret[rank]
         assert ok1 and ok2, f"rank {rank}: sharded result differs from the single index"
         assert (first, second) == (40, 15_000)
+
+
+@pytest.mark.parametrize("k,nq,n_shards", [(10, 300, 2), (24, 33, 3), (48, 5, 8), (50, 3, 2)])
+def test_packed_hits_and_merge_kernel_on_one_gpu(k, nq, n_shards):
+    """The multi-GPU data path minus the collective, on one GPU: every shard's b200_index_search_packed writes its
+    16-byte hit records into its slot of the would-be all-gather buffer, b200_merge_hits merges a query sub-range --
+    ids and fp32 score bits must equal one index over every row (including the exhaustive k > 48 path, an empty
+    shard, and a tie across a shard boundary)."""
+    vs, sh = pkg("vectorstore"), pkg("sharded")
+    dev = torch.device("cuda", 0)
+    g = torch.Generator(device="cpu").manual_seed(k)
+    n = 30_011
+    rows = torch.randn((n, 384), generator=g).bfloat16().float()
+    rows[n - 7] = rows[40]
+    qs = torch.randn((nq, 384), generator=g).bfloat16().float()
+    qs[0] = rows[40]
+    qd = qs.to(dev).contiguous()
+    full = vs.B200Index(384, device=0, capacity=n)
+    full.add(rows.to(dev).contiguous())
+    want_i, want_s = full.search(qd, k)
+    gathered = torch.empty((n_shards + 1, nq, k, 2), dtype=torch.int64, device=dev)
+    shards = []
+    for r in range(n_shards):
+        r0, r1 = sh.shard_range(n, n_shards, r)
+        ix = vs.B200Index(384, device=0, capacity=max(r1 - r0, 1))
+        ix.add(rows[r0:r1].to(dev).contiguous())
+        ix.search_packed(qd, k, r0, gathered[r])
+        shards.append(ix)
+    empty = vs.B200Index(384, device=0, capacity=16)               # a rank whose shard holds no rows
+    empty.search_packed(qd, k, n, gathered[n_shards])
+    ids, sc = sh.merge_hits_cuda(gathered, 0, nq, k)
+    assert torch.equal(ids, want_i) and torch.equal(sc.view(torch.int32), want_s.view(torch.int32))
+    lo, m = nq // 3, max(1, nq // 2)
+    ids2, sc2 = sh.merge_hits_cuda(gathered, lo, m, k)              # the sub-range a rank merges for its own queries
+    assert torch.equal(ids2, want_i[lo:lo + m]) and torch.equal(sc2.view(torch.int32), want_s[lo:lo + m].view(torch.int32))
+    assert int(want_i[0, 0]) == 40 and int(want_i[0, 1]) == n - 7
+    # single-rank ShardedSearch through the same two entry points (production wiring short-cuts to the plain search)
+    ss = sh.ShardedSearch(lambda q, kk, base, out: full.search_packed(q, kk, base, out), 0)
+    ids3, sc3 = ss.search_local_queries(qd, k)
+    assert torch.equal(ids3, want_i) and torch.equal(sc3.view(torch.int32), want_s.view(torch.int32))
+    for ix in shards + [empty, full]:
+        ix.close()
