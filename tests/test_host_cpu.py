@@ -76,12 +76,18 @@ def test_bench_reference_arm_prints_the_contract_line():
 
     from conftest import ROOT
 
-    out = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--steps", "1", "--warmup", "0"],
-                         capture_output=True, text=True, timeout=300)
+    from oracle import ref_loader
+
+    out = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--steps", "2", "--warmup", "1",
+                          "--corpus-rows", "3000"], capture_output=True, text=True, timeout=300)
     assert out.returncode == 0, out.stderr[-500:]
     line = json.loads(out.stdout.strip().splitlines()[-1])
-    assert line["impl"] == "reference" and line["unit"] == "chunks/s" and line["value"] > 0
-    assert line["cpu_baseline"]["kind"] == "port" and line["e2e"]["h2d_bytes_per_step"] == 0
+    assert line["impl"] == "reference" and line["unit"] == "chunks/s" and line["value"] > 0 and line["steps"] == 2
+    # the real InMemoryVectorStore when oracle/_ref is built (python oracle/make_ref.py), the port otherwise; never scaled
+    assert line["cpu_baseline"]["kind"] == ("reference" if ref_loader.available() else "port")
+    assert "nothing scaled" in line["cpu_baseline"]["sample"] and line["e2e"]["h2d_bytes_per_step"] == 0
+    assert abs(line["ms_per_step"] - 1e3 / line["value"]) < 1e-6
+    assert line["config"]["corpus_rows_global"] == 3000 and line["config"]["parallelism"].startswith("dp1")
 
 
 def test_model_dir_refuses_other_module_stacks_and_architectures(tmp_path):
