@@ -170,6 +170,7 @@ struct b200_index {
   // certificate state: persist[0] = rvmax (float bits), persist[2..3] / [4..5] = the two 64-bit counters
   // of b200_index_certificate_stats; cert = [fail_count][pad to 64 B][ticket nq][fail_idx nq] per search
   DevBuf persist, cert, exact_part;
+  int exact_per_sm[2] = {0, 0};   // resident CTAs per SM of exact_topk_kernel<0 / 1> at this index's dimension
   StreamOrder order;
   std::mutex mu;
   size_t master_elt() const { return master_dtype == B200_INDEX_MASTER_BF16 ? 2 : 4; }
@@ -194,7 +195,7 @@ static int index_reserve_locked(b200_index* ix, int64_t cap, cudaStream_t st) {
 
 // CG = 2 runs CTA pairs (two query tiles per cluster); nqt is then the even number of query tiles.
 template <int BLOCK_N, int KP, int CG>
-static int launch_sim(b200_index* ix, int nq, int nqt, const CUtensorMap& map_q, cudaStream_t st, int* nsplit_out) {
+static int launch_sim(b200_index* ix, int nq, int nqt, const CUtensorMap& map_q, cudaStream_t st, SimParams* used) {
   const int kc = ix->dpad / SIM_BLOCK_K;
   const size_t a_bytes = (size_t)kc * SIM_A_CHUNK_BYTES;
   const size_t list_bytes = (size_t)SIM_BLOCK_M * (KP + 1) * 8;
@@ -252,7 +253,13 @@ static int launch_sim(b200_index* ix, int nq, int nqt, const CUtensorMap& map_q,
   p.cand = ix->cand.as<uint64_t>(); p.gbkt = ix->gbkt.as<uint32_t>(); p.use_bound = nsplit >= KP;
   p.gthr = ix->gbkt.as<uint32_t>() + (size_t)nqt * SIM_BLOCK_M * KP;
   p.refresh_mask = (uint32_t)opt(OPT_SIM_REFRESH_MASK); p.split_major = 0;
-  { const int m = opt(OPT_SIM_BOUND); p.use_bound = (m & 1) && nsplit >= KP; p.use_gthr = (m >> 1) & 1; }
+  {
+    // bit 0: the bucket bound (needs one bucket per kept candidate); bit 1: the single-CTA stand-in bound, which
+    // only earns its atomics while buckets are still unreported, i.e. when the launch takes more than one wave
+    const int m = opt(OPT_SIM_BOUND);
+    p.use_bound = (m & 1) && nsplit >= KP;
+    p.use_gthr = ((m >> 1) & 1) && ((long)nsplit * units > slots || !p.use_bound);
+  }
   auto kern = sim_topk_kernel<BLOCK_N, KP, CG>;
   B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   {
@@ -277,7 +284,7 @@ static int launch_sim(b200_index* ix, int nq, int nqt, const CUtensorMap& map_q,
     }
   }
   B200_CUDA(cudaGetLastError());
-  *nsplit_out = nsplit;
+  *used = p;
   return B200_OK;
 }
 
@@ -290,19 +297,25 @@ template <int METRIC_L2>
 static int launch_exact(b200_index* ix, const uint32_t* fail_count, const int32_t* fail_idx, uint32_t* ticket, int nq,
                         const float* q_f32, int k, int64_t id_base, int64_t* ids_dev, float* sc_dev, cudaStream_t st,
                         uint64_t* part = nullptr, int grid = 0, ulonglong2* packed_dev = nullptr) {
+  const size_t smem = (size_t)EXACT_MERGE * 8 + (size_t)ix->dim * 4;
+  auto kern = exact_topk_kernel<METRIC_L2>;
+  B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  // The kernel's CTAs wait for one another (a query's list buffer is reused two queries later), so every CTA of the
+  // grid must be able to be resident at once: never launch more than the occupancy calculator allows.
+  int& per_sm = ix->exact_per_sm[METRIC_L2];
+  if (per_sm == 0) B200_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, EXACT_THREADS, smem));
+  if (per_sm < 1) B200_FAIL(B200_ERR_UNSUPPORTED, "the exhaustive kernel does not fit on an SM (dimension %d)", ix->dim);
   if (!part) {   // the index's own scratch (grown on first use); the no-allocation entry point passes its own
-    grid = ix->num_sms;
+    grid = std::min(per_sm, 2) * ix->num_sms;
     B200_TRY(ix->exact_part.grow((size_t)2 * grid * EXACT_KEEP * 8, 0, st));
     part = ix->exact_part.as<uint64_t>();
   }
+  grid = std::min(grid, per_sm * ix->num_sms);
   ExactParams e{};
   e.fail_count = fail_count; e.fail_idx = fail_idx; e.nq = nq; e.q_f32 = q_f32;
   e.master = ix->master.p; e.master_is_bf16 = ix->master_dtype == B200_INDEX_MASTER_BF16;
   e.n_rows = (uint32_t)ix->count; e.d = ix->dim; e.k = k; e.id_base = id_base;
   e.part = part; e.ticket = ticket; e.out_ids = ids_dev; e.out_scores = sc_dev; e.out_packed = packed_dev;
-  const size_t smem = (size_t)EXACT_MERGE * 8 + (size_t)ix->dim * 4;
-  auto kern = exact_topk_kernel<METRIC_L2>;
-  B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   {
     B200_PROF(METRIC_L2 ? "exact_l2" : "exact_topk", 0.0, 0.0, st);
     kern<<<grid, EXACT_THREADS, smem, st>>>(e);
@@ -339,13 +352,15 @@ static int search_chunk(b200_index* ix, const void* q_dev, int q_dtype, int nq, 
 
   CUtensorMap map_q;
   B200_TRY(make_tma_2d_bf16(&map_q, ix->q16.p, (uint64_t)nq_pad, (uint64_t)ix->dpad, SIM_BLOCK_M, SIM_BLOCK_K));
-  int nsplit = 0;
-  if (pair) B200_TRY((launch_sim<256, 16, 2>(ix, nq, nqt, map_q, st, &nsplit)));
-  else if (kp == 16) B200_TRY((launch_sim<256, 16, 1>(ix, nq, nqt, map_q, st, &nsplit)));
-  else if (kp == 32) B200_TRY((launch_sim<128, 32, 1>(ix, nq, nqt, map_q, st, &nsplit)));
-  else B200_TRY((launch_sim<128, 64, 1>(ix, nq, nqt, map_q, st, &nsplit)));
+  SimParams sp{};
+  if (pair) B200_TRY((launch_sim<256, 16, 2>(ix, nq, nqt, map_q, st, &sp)));
+  else if (kp == 16) B200_TRY((launch_sim<256, 16, 1>(ix, nq, nqt, map_q, st, &sp)));
+  else if (kp == 32) B200_TRY((launch_sim<128, 32, 1>(ix, nq, nqt, map_q, st, &sp)));
+  else B200_TRY((launch_sim<128, 64, 1>(ix, nq, nqt, map_q, st, &sp)));
+  const int nsplit = sp.nsplit;
 
   MergeParams m;
+  m.gbkt = sp.gbkt; m.gthr = sp.gthr; m.use_bound = sp.use_bound; m.use_gthr = sp.use_gthr;
   m.nq = nq; m.nsplit = nsplit; m.kp = kp; m.k = k; m.d = ix->dim;
   int pow2 = 64;
   while (pow2 < nsplit * kp) pow2 <<= 1;
@@ -908,7 +923,7 @@ int static_scratch_for_current_device(int device, unsigned char** out) {
 
 template <int BLOCK_N, int KP>
 int launch_sim_static(b200_index* ix, int nq, const CUtensorMap& map_q, uint64_t* cand, uint32_t* gthr,
-                      cudaStream_t st, int* nsplit_out) {
+                      cudaStream_t st, SimParams* used) {
   const int kc = ix->dpad / SIM_BLOCK_K;
   const size_t a_bytes = (size_t)kc * SIM_A_CHUNK_BYTES;
   const size_t list_bytes = (size_t)SIM_BLOCK_M * (KP + 1) * 8;
@@ -934,7 +949,7 @@ int launch_sim_static(b200_index* ix, int nq, const CUtensorMap& map_q, uint64_t
   B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   kern<<<dim3(1, nsplit), SIM_THREADS, smem, st>>>(map_q, map_c, p);
   B200_CUDA(cudaGetLastError());
-  *nsplit_out = nsplit;
+  *used = p;
   return B200_OK;
 }
 
@@ -991,11 +1006,13 @@ extern "C" int b200_index_search_static(b200_index_t* ix, const void* queries_de
   B200_CUDA(cudaGetLastError());
   CUtensorMap map_q;
   B200_TRY(make_tma_2d_bf16(&map_q, q16, (uint64_t)nq_pad, (uint64_t)ix->dpad, SIM_BLOCK_M, SIM_BLOCK_K));
-  int nsplit = 0;
-  if (kp == 16) B200_TRY((launch_sim_static<256, 16>(ix, n, map_q, cand, gthr, st, &nsplit)));
-  else if (kp == 32) B200_TRY((launch_sim_static<128, 32>(ix, n, map_q, cand, gthr, st, &nsplit)));
-  else B200_TRY((launch_sim_static<128, 64>(ix, n, map_q, cand, gthr, st, &nsplit)));
+  SimParams sp{};
+  if (kp == 16) B200_TRY((launch_sim_static<256, 16>(ix, n, map_q, cand, gthr, st, &sp)));
+  else if (kp == 32) B200_TRY((launch_sim_static<128, 32>(ix, n, map_q, cand, gthr, st, &sp)));
+  else B200_TRY((launch_sim_static<128, 64>(ix, n, map_q, cand, gthr, st, &sp)));
+  const int nsplit = sp.nsplit;
   MergeParams m;
+  m.gbkt = sp.gbkt; m.gthr = sp.gthr; m.use_bound = sp.use_bound; m.use_gthr = sp.use_gthr;
   m.nq = n; m.nsplit = nsplit; m.kp = kp; m.k = k; m.d = ix->dim;
   int pow2 = 64;
   while (pow2 < nsplit * kp) pow2 <<= 1;

@@ -574,6 +574,10 @@ struct MergeParams {
   int64_t* out_ids;         // [nq, k]
   float* out_scores;        // [nq, k]
   ulonglong2* out_packed;   // [nq, k] or nullptr: (orderable(score) << 32, global id) records instead of the two arrays
+  // --- K8's shared score bounds as it left them (see SimParams): candidates below them cannot be among the KP best ---
+  const uint32_t* gbkt;     // [nq][kp] bucket bests, nullptr or use_bound == 0: not used
+  const uint32_t* gthr;     // [nq] best full-set worst, nullptr or use_gthr == 0: not used
+  int use_bound, use_gthr;
   // --- candidate-sufficiency certificate (all nullptr: skipped) ---
   const float2* qmeta;      // [nq] (inv_scale, r_q) from prep_queries_kernel
   const uint32_t* rvmax;    // float bits: max over rows of || unit row - its half image ||_2
@@ -590,13 +594,40 @@ __global__ void __launch_bounds__(256) merge_rescore_kernel(const MergeParams p)
   uint64_t* fin = reinterpret_cast<uint64_t*>(qh + ((p.d + 1) & ~1));  // [64]
   __shared__ float s_den;
 
+  __shared__ int s_cnt;
   const int q = blockIdx.x;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
   const int ncand = p.nsplit * p.kp;
   const size_t o = (size_t)q * ncand;
-  for (int i = threadIdx.x; i < p.ncand_pow2; i += blockDim.x) {
-    keys[i] = (i < ncand) ? p.cand[o + i] : 0;
+  // Gather with a filter.  Every CTA of K8 hands over a FULL set of KP keys, most of them left from its warm-up
+  // (a set only ever replaces its worst entry), so nsplit * KP keys arrive -- up to 8192 -- of which a few dozen
+  // matter.  K8's shared bounds, as they stand now that it has finished, are lower bounds on this query's KP-th
+  // best score (>= KP distinct rows at or above them are in the sets): everything below goes, and the bitonic sort
+  // runs over what is left, not over 8192 keys (0.15 ms -> 0.02 ms per launch at 128 queries).
+  uint32_t lb = 0;
+  if (p.use_bound && p.gbkt) {
+    lb = 0xFFFFFFFFu;
+    for (int i = 0; i < p.kp; ++i) lb = min(lb, __ldcg(p.gbkt + (size_t)q * p.kp + i));
   }
+  if (p.use_gthr && p.gthr) lb = max(lb, __ldcg(p.gthr + q));
+  if (lb) lb -= 1;                                     // K8 applies the bounds non-strictly (and steps past -0)
+  if (threadIdx.x == 0) s_cnt = 0;
+  __syncthreads();
+  const int ncand_round = (ncand + blockDim.x - 1) / blockDim.x * blockDim.x;
+  for (int i = threadIdx.x; i < ncand_round; i += blockDim.x) {
+    const uint64_t key = (i < ncand) ? __ldcg(p.cand + o + i) : 0ull;
+    const bool keep = key != 0 && (uint32_t)(key >> 32) >= lb;
+    const uint32_t m = __ballot_sync(0xffffffffu, keep);
+    int base = 0;
+    if (lane == 0 && m) base = atomicAdd(&s_cnt, __popc(m));
+    base = __shfl_sync(0xffffffffu, base, 0);
+    if (keep) keys[base + __popc(m & ((1u << lane) - 1u))] = key;
+  }
+  __syncthreads();
+  const int nkept = s_cnt;
+  int npow2 = 64;
+  while (npow2 < nkept) npow2 <<= 1;
+  for (int i = nkept + threadIdx.x; i < npow2; i += blockDim.x) keys[i] = 0;
   // q_hat = q / (||q|| + 1e-8)   (inmemory.py:108)
   const float* qraw = p.q_f32 + (size_t)q * p.d;
   if (warp == 0) {
@@ -606,7 +637,7 @@ __global__ void __launch_bounds__(256) merge_rescore_kernel(const MergeParams p)
   __syncthreads();
   for (int i = threadIdx.x; i < p.d; i += blockDim.x) qh[i] = __fdiv_rn(qraw[i], s_den);
   for (int i = threadIdx.x; i < 64; i += blockDim.x) fin[i] = 0;
-  bitonic_sort_desc(keys, p.ncand_pow2);  // ends with __syncthreads
+  bitonic_sort_desc(keys, npow2);  // ends with __syncthreads
 
   for (int c = warp; c < p.kp; c += nwarp) {
     const uint64_t key = keys[c];
@@ -701,6 +732,117 @@ B200_DEVINL float canon_l2(const float* __restrict__ q, const TV* __restrict__ v
   return p;
 }
 
+// canon_score / canon_l2 of one row, generic in d (the fallback of canon_rows8 below)
+template <int METRIC_L2, typename TV>
+B200_DEVINL float canon_row(const float* __restrict__ qh, const TV* __restrict__ v, int d, int lane) {
+  return METRIC_L2 ? -canon_l2(qh, v, d, lane) : canon_score(qh, v, d, lane);
+}
+
+// eight consecutive elements as they come from memory (16 or 32 bytes), unpacked to fp32 when they are used
+struct Raw8Bf16 { uint4 u; };
+struct Raw8F32 { float4 a, b; };
+B200_DEVINL void load8_raw(const __nv_bfloat16* p, Raw8Bf16& r) { r.u = __ldg(reinterpret_cast<const uint4*>(p)); }
+B200_DEVINL void load8_raw(const float* p, Raw8F32& r) {
+  r.a = __ldg(reinterpret_cast<const float4*>(p));
+  r.b = __ldg(reinterpret_cast<const float4*>(p) + 1);
+}
+B200_DEVINL void unpack8(const Raw8Bf16& r, float (&x)[8]) {
+  const uint32_t w[4] = {r.u.x, r.u.y, r.u.z, r.u.w};
+#pragma unroll
+  for (int t = 0; t < 4; ++t) {
+    x[2 * t] = __uint_as_float(w[t] << 16);
+    x[2 * t + 1] = __uint_as_float(w[t] & 0xFFFF0000u);
+  }
+}
+B200_DEVINL void unpack8(const Raw8F32& r, float (&x)[8]) {
+  x[0] = r.a.x; x[1] = r.a.y; x[2] = r.a.z; x[3] = r.a.w; x[4] = r.b.x; x[5] = r.b.y; x[6] = r.b.z; x[7] = r.b.w;
+}
+template <typename TV> struct Raw8;
+template <> struct Raw8<__nv_bfloat16> { using type = Raw8Bf16; static constexpr int kInFlight = 8; };
+template <> struct Raw8<float> { using type = Raw8F32; static constexpr int kInFlight = 4; };
+
+// The canonical 32 partial sums of a row, folded: lane 4r + m holds partials 8m .. 8m + 7 of row r.
+// Halving tree of oracle/search_oracle.c: p[l] += p[l + 16] (lanes m <- m ^ 2), p[l] += p[l + 8] (m <- m ^ 1), then 4, 2, 1
+// inside the lane.  All four lanes of a row end with the same value.
+B200_DEVINL float fold_partials8(float (&a)[8]) {
+#pragma unroll
+  for (int t = 0; t < 8; ++t) a[t] = __fadd_rn(a[t], __shfl_xor_sync(0xffffffffu, a[t], 2));
+#pragma unroll
+  for (int t = 0; t < 8; ++t) a[t] = __fadd_rn(a[t], __shfl_xor_sync(0xffffffffu, a[t], 1));
+#pragma unroll
+  for (int t = 0; t < 4; ++t) a[t] = __fadd_rn(a[t], a[t + 4]);
+  a[0] = __fadd_rn(a[0], a[2]);
+  a[1] = __fadd_rn(a[1], a[3]);
+  return __fadd_rn(a[0], a[1]);
+}
+
+// Eight consecutive rows per warp with 16-byte loads, bit-identical to canon_score / canon_l2 per row.
+// Lane 4r + m works on row r and on the 8-element chunks c = 4k + m (k = 0, 1, ...): chunk c holds elements
+// 8c .. 8c + 7, which the canonical order sends to partials 8m .. 8m + 7 in ascending k -- so each lane keeps eight
+// of its row's 32 partial sums and adds to them in exactly the canonical sequence, while its loads (one per k, all
+// independent) are 16 bytes wide and four lanes cover 64 contiguous bytes.  One row per warp with 2-byte loads kept
+// ~1 KB in flight per warp and ran at a fifth of the HBM rate.  Needs d % 8 == 0; rows >= n_valid are skipped.
+template <int METRIC_L2, typename TV>
+B200_DEVINL float canon_rows8(const float* __restrict__ qh, const TV* __restrict__ rows, int d, int lane, int n_valid) {
+  using Raw = typename Raw8<TV>::type;
+  constexpr int U = Raw8<TV>::kInFlight;        // loads issued before the first one is consumed (32 registers' worth)
+  const int r = lane >> 2, m = lane & 3;
+  const bool on = r < n_valid;
+  const TV* v = rows + (size_t)r * d;
+  const int nch = d >> 3;                       // chunks per row
+  float a[8], den = 1.f;
+  if (!METRIC_L2) {
+#pragma unroll
+    for (int t = 0; t < 8; ++t) a[t] = 0.f;
+    for (int c0 = m; c0 < nch; c0 += 4 * U) {
+      Raw raw[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u)
+        if (on && c0 + 4 * u < nch) load8_raw(v + 8 * (c0 + 4 * u), raw[u]);
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        if (on && c0 + 4 * u < nch) {
+          float x[8];
+          unpack8(raw[u], x);
+#pragma unroll
+          for (int t = 0; t < 8; ++t) a[t] = __fmaf_rn(x[t], x[t], a[t]);
+        }
+      }
+    }
+    den = __fadd_rn(__fsqrt_rn(fold_partials8(a)), 1e-8f);
+  }
+#pragma unroll
+  for (int t = 0; t < 8; ++t) a[t] = 0.f;
+  for (int c0 = m; c0 < nch; c0 += 4 * U) {
+    Raw raw[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u)
+      if (on && c0 + 4 * u < nch) load8_raw(v + 8 * (c0 + 4 * u), raw[u]);
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int c = c0 + 4 * u;
+      if (on && c < nch) {
+        float x[8];
+        unpack8(raw[u], x);
+        const float4 q0 = *reinterpret_cast<const float4*>(qh + 8 * c);
+        const float4 q1 = *reinterpret_cast<const float4*>(qh + 8 * c + 4);
+        const float qv[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
+#pragma unroll
+        for (int t = 0; t < 8; ++t) {
+          if (METRIC_L2) {
+            const float df = __fsub_rn(qv[t], x[t]);
+            a[t] = __fmaf_rn(df, df, a[t]);
+          } else {
+            a[t] = __fmaf_rn(qv[t], __fdiv_rn(x[t], den), a[t]);
+          }
+        }
+      }
+    }
+  }
+  const float s = fold_partials8(a);
+  return METRIC_L2 ? -s : s;
+}
+
 B200_DEVINL uint64_t shfl_xor_u64(uint64_t v, int o) {
   const uint32_t lo = __shfl_xor_sync(0xffffffffu, (uint32_t)v, o);
   const uint32_t hi = __shfl_xor_sync(0xffffffffu, (uint32_t)(v >> 32), o);
@@ -708,7 +850,7 @@ B200_DEVINL uint64_t shfl_xor_u64(uint64_t v, int o) {
 }
 
 template <int METRIC_L2>
-__global__ void __launch_bounds__(EXACT_THREADS) exact_topk_kernel(const ExactParams p) {
+__global__ void __launch_bounds__(EXACT_THREADS, 1) exact_topk_kernel(const ExactParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint64_t* mkeys = reinterpret_cast<uint64_t*>(smem_raw);                  // [EXACT_MERGE]
   float* qh = reinterpret_cast<float*>(mkeys + EXACT_MERGE);                // [d]
@@ -730,32 +872,42 @@ __global__ void __launch_bounds__(EXACT_THREADS) exact_topk_kernel(const ExactPa
       for (int i = threadIdx.x; i < p.d; i += blockDim.x) qh[i] = __fdiv_rn(qraw[i], s_den);
     }
     __syncthreads();
-    // --- this warp's rows ---
+    // --- this warp's rows, eight at a time ---
     uint64_t k0 = 0, k1 = 0, wmin = 0;       // two kept keys per lane; wmin = the smallest of the 64
-    for (uint32_t row = blockIdx.x * nwarp + warp; row < p.n_rows; row += gridDim.x * nwarp) {
-      float s;
-      if (METRIC_L2) {
-        s = p.master_is_bf16 ? canon_l2(qh, reinterpret_cast<const __nv_bfloat16*>(p.master) + (size_t)row * p.d, p.d, lane)
-                             : canon_l2(qh, reinterpret_cast<const float*>(p.master) + (size_t)row * p.d, p.d, lane);
-        s = -s;                                // smaller distance = better
+    const bool vec = (p.d & 7) == 0 && (reinterpret_cast<uintptr_t>(p.master) & 15) == 0;
+    const uint32_t n_groups = (p.n_rows + 7) / 8;
+    for (uint32_t grp = blockIdx.x * nwarp + warp; grp < n_groups; grp += gridDim.x * nwarp) {
+      const uint32_t row0 = grp * 8;
+      const int n_valid = (int)min(8u, p.n_rows - row0);
+      float mine = 0.f;                       // lanes 4r .. 4r + 3: the score of row row0 + r
+      if (vec) {
+        mine = p.master_is_bf16
+                   ? canon_rows8<METRIC_L2>(qh, reinterpret_cast<const __nv_bfloat16*>(p.master) + (size_t)row0 * p.d, p.d, lane, n_valid)
+                   : canon_rows8<METRIC_L2>(qh, reinterpret_cast<const float*>(p.master) + (size_t)row0 * p.d, p.d, lane, n_valid);
       } else {
-        s = p.master_is_bf16 ? canon_score(qh, reinterpret_cast<const __nv_bfloat16*>(p.master) + (size_t)row * p.d, p.d, lane)
-                             : canon_score(qh, reinterpret_cast<const float*>(p.master) + (size_t)row * p.d, p.d, lane);
-      }
-      const uint64_t key = pack_key(s, row);
-      if (key > wmin) {
-        // replace one occurrence of the minimum (empty slots are 0 = the minimum until the set is full)
-        const uint32_t has0 = __ballot_sync(0xffffffffu, k0 == wmin);
-        const uint32_t has1 = __ballot_sync(0xffffffffu, k1 == wmin);
-        if (has0) { if (lane == __ffs(has0) - 1) k0 = key; }
-        else if (lane == __ffs(has1) - 1) k1 = key;
-        uint64_t m = k0 < k1 ? k0 : k1;
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-          const uint64_t other = shfl_xor_u64(m, o);
-          m = other < m ? other : m;
+        for (int j = 0; j < n_valid; ++j) {
+          const float sj = p.master_is_bf16
+                               ? canon_row<METRIC_L2>(qh, reinterpret_cast<const __nv_bfloat16*>(p.master) + (size_t)(row0 + j) * p.d, p.d, lane)
+                               : canon_row<METRIC_L2>(qh, reinterpret_cast<const float*>(p.master) + (size_t)(row0 + j) * p.d, p.d, lane);
+          if ((lane >> 2) == j) mine = sj;
         }
-        wmin = m;
+      }
+      for (int j = 0; j < n_valid; ++j) {
+        const uint64_t key = pack_key(__shfl_sync(0xffffffffu, mine, 4 * j), row0 + j);
+        if (key > wmin) {
+          // replace one occurrence of the minimum (empty slots are 0 = the minimum until the set is full)
+          const uint32_t has0 = __ballot_sync(0xffffffffu, k0 == wmin);
+          const uint32_t has1 = __ballot_sync(0xffffffffu, k1 == wmin);
+          if (has0) { if (lane == __ffs(has0) - 1) k0 = key; }
+          else if (lane == __ffs(has1) - 1) k1 = key;
+          uint64_t mn = k0 < k1 ? k0 : k1;
+#pragma unroll
+          for (int o = 16; o > 0; o >>= 1) {
+            const uint64_t other = shfl_xor_u64(mn, o);
+            mn = other < mn ? other : mn;
+          }
+          wmin = mn;
+        }
       }
     }
     // --- CTA: best 64 of the warps' keys ---
