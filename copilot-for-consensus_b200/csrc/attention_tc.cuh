@@ -86,6 +86,24 @@ B200_DEVINL float att_exp2(float x) {
   return y;
 }
 
+// 2^x on the FMA / ALU pipes: the SFU delivers one MUFU.EX2 per 8 clocks per scheduler and is what bounds this
+// kernel, while the FMA pipe issues every clock and sat half idle -- so a fixed share of every chunk's
+// exponentials (NPOLY of each 8) is computed here instead and the two pipes run side by side.
+//   r = round(x) through the 1.5 * 2^23 trick (its integer lands in the low mantissa bits of t),
+//   f = x - r in [-0.5, 0.5],  2^f by a degree-3 polynomial (max relative error 1.0e-4, a twentieth of the bf16
+//   rounding step the probability gets next),  2^r by adding r to the exponent field.
+// 8 instructions against one MUFU slot of 8 clocks.  x is clamped at -126 (the MUFU path flushes such values to 0,
+// this one returns ~1e-38: both vanish against a row's leading probabilities).
+B200_DEVINL float att_exp2_fma(float x) {
+  x = fmaxf(x, -126.f);
+  const float t = x + 12582912.f;
+  const float f = x - (t - 12582912.f);
+  float p = fmaf(f, 0.055838283f, 0.24263948f);
+  p = fmaf(p, f, 0.69313675f);
+  p = fmaf(p, f, 0.99992454f);
+  return __int_as_float(__float_as_int(p) + (__float_as_int(t) << 23));
+}
+
 // Reciprocal and square root on the FMA / ALU pipes only (bit-trick seed + Newton steps, relative error
 // < 1e-6 and < 1e-5): the group that is NOT in its exponential pass must stay off the SFU, whose queue
 // the other group keeps full.
@@ -154,7 +172,7 @@ B200_DEVINL float att_chunk_max(const uint32_t (&v)[32], int valid) {
 
 // Probabilities of one 32-key chunk of a row, packed as bf16 pairs: p = 2^(s') for the valid keys, 0
 // for padding.  SUB: the scores carry no reference yet (exact-maximum units), subtract mx first.
-template <bool FULL, bool SUB>
+template <bool FULL, bool SUB, int NPOLY>
 B200_DEVINL void att_probs(const uint32_t (&v)[32], int valid, float mx, uint32_t (&pk)[16]) {
 #pragma unroll
   for (int j = 0; j < 16; ++j) {
@@ -163,7 +181,9 @@ B200_DEVINL void att_probs(const uint32_t (&v)[32], int valid, float mx, uint32_
       a0 -= mx;
       a1 -= mx;
     }
-    float p0 = att_exp2(a0), p1 = att_exp2(a1);
+    // columns c with (c % 8) < NPOLY go to the FMA pipe, spread over the chunk so both pipes stay fed
+    float p0 = ((2 * j) % 8 < NPOLY) ? att_exp2_fma(a0) : att_exp2(a0);
+    float p1 = ((2 * j + 1) % 8 < NPOLY) ? att_exp2_fma(a1) : att_exp2(a1);
     if (!FULL) {
       if (2 * j >= valid) p0 = 0.f;
       if (2 * j + 1 >= valid) p1 = 0.f;
@@ -195,7 +215,7 @@ B200_DEVINL float att_pass_max(uint32_t tS, int ncl, int lenh, uint32_t (&v)[2][
 // the tcgen05.ld of chunk c+1 is in flight while chunk c is processed (two register buffers).
 // `turn` is handed to the other group when this warp STARTS its last chunk: the overlap of one chunk
 // keeps the SFU queue full across the hand-over (warps of a group do not finish together).
-template <bool FULL, bool SUB>
+template <bool FULL, bool SUB, int NPOLY>
 B200_DEVINL void att_pass_exp(uint32_t tS, int ncl, int lenh, float mx, uint32_t (&v)[2][32], uint64_t* turn, int lane) {
   if (ncl > 0) tmem_ld32(tS, v[0]);
   else if (lane == 0) mbar_arrive(turn);
@@ -209,7 +229,7 @@ B200_DEVINL void att_pass_exp(uint32_t tS, int ncl, int lenh, float mx, uint32_t
         if (cc + 1 < ncl) tmem_ld32(tS + (cc + 1) * 32, v[uu ^ 1]);
         if (cc == max(ncl - ATT_HANDOVER, 0) && lane == 0) mbar_arrive(turn);
         uint32_t pk[16];
-        att_probs<FULL, SUB>(v[uu], lenh - cc * 32, mx, pk);
+        att_probs<FULL, SUB, NPOLY>(v[uu], lenh - cc * 32, mx, pk);
         tmem_st16(tS + cc * 16, pk);
       }
     }
@@ -227,6 +247,7 @@ B200_DEVINL void att_pass_exp(uint32_t tS, int ncl, int lenh, float mx, uint32_t
 B200_DEVINL int att_prob_col(int c, int c0) { return c < c0 ? 16 * c : 32 * c0 + 16 * (c - c0); }
 B200_DEVINL int att_out_col(int S) { return S + ATT_ON <= ATT_MAX_S ? S : 64; }
 
+template <int NPOLY>
 __global__ void __launch_bounds__(ATT_THREADS, 1)
 attention_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_kv,
                     const __grid_constant__ CUtensorMap map_out, const AttParams p) {
@@ -484,11 +505,11 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_cons
       if (!p.no_turns) mbar_wait(&xu_turn[grp], grp == 0 ? ((k & 1) ^ 1) : (k & 1));
       ATT_STAMP(t4);
       if (use_bound) {
-        if (all_valid) att_pass_exp<true, false>(tS, ncl, lenh, 0.f, v, &xu_turn[grp ^ 1], lane);
-        else att_pass_exp<false, false>(tS, ncl, lenh, 0.f, v, &xu_turn[grp ^ 1], lane);
+        if (all_valid) att_pass_exp<true, false, NPOLY>(tS, ncl, lenh, 0.f, v, &xu_turn[grp ^ 1], lane);
+        else att_pass_exp<false, false, NPOLY>(tS, ncl, lenh, 0.f, v, &xu_turn[grp ^ 1], lane);
       } else {
-        if (all_valid) att_pass_exp<true, true>(tS, ncl, lenh, mx, v, &xu_turn[grp ^ 1], lane);
-        else att_pass_exp<false, true>(tS, ncl, lenh, mx, v, &xu_turn[grp ^ 1], lane);
+        if (all_valid) att_pass_exp<true, true, NPOLY>(tS, ncl, lenh, mx, v, &xu_turn[grp ^ 1], lane);
+        else att_pass_exp<false, true, NPOLY>(tS, ncl, lenh, mx, v, &xu_turn[grp ^ 1], lane);
       }
       tmem_st_wait();
       tc_fence_before();

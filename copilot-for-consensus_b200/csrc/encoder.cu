@@ -330,8 +330,13 @@ static int run_encoder(b200_encoder* e, const int32_t* d_ids, const int32_t* d_l
     B200_TRY(make_tma_2d_bf16_plain(&map_att_out, e->ctx.p, (uint64_t)e->m_cap, (uint64_t)H, 32, ATT_DH / 2));   // one warp's rows x dims
     B200_TRY(make_tma_2d_bf16_sw64(&map_att_q, e->qkv.p, (uint64_t)e->m_cap, (uint64_t)(3 * H), (uint32_t)std::min(seq, 128), ATT_DH));
     B200_TRY(make_tma_2d_bf16_sw64(&map_att_kv, e->qkv.p, (uint64_t)e->m_cap, (uint64_t)(3 * H), (uint32_t)seq, ATT_DH));
-    B200_CUDA(cudaFuncSetAttribute(attention_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)att_tc_smem));
   }
+  // how many of every 8 exponentials the attention kernel computes on the FMA pipe (option att_poly)
+  typedef void (*AttKernel)(const CUtensorMap, const CUtensorMap, const CUtensorMap, const AttParams);
+  static const AttKernel att_kernels[5] = {attention_tc_kernel<0>, attention_tc_kernel<1>, attention_tc_kernel<2>,
+                                           attention_tc_kernel<3>, attention_tc_kernel<4>};
+  const AttKernel att_kernel = att_kernels[std::min(std::max(opt(OPT_ATT_POLY), 0), 4)];
+  if (use_att_tc) B200_CUDA(cudaFuncSetAttribute(att_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)att_tc_smem));
 
   // hidden 384 = two 192-column tiles: residual + LayerNorm fused into the producing GEMM (option fuse_ln=0 disables)
   const bool pair_ok = opt(OPT_GEMM_PAIR) != 0;
@@ -360,7 +365,7 @@ static int run_encoder(b200_encoder* e, const int32_t* d_ids, const int32_t* d_l
       cfg.stream = st;
       cudaLaunchAttribute attr[2];
       cfg.attrs = attr; cfg.numAttrs = hot_launch_attrs(attr, false);
-      B200_CUDA(cudaLaunchKernelEx(&cfg, attention_tc_kernel, map_att_q, map_att_kv, map_att_out, ap));
+      B200_CUDA(cudaLaunchKernelEx(&cfg, att_kernel, map_att_q, map_att_kv, map_att_out, ap));
     } else {
       B200_PROF("attention", 4.0 * batch * (double)seq * seq * H, 2.0 * 4.0 * n_tok * H, st);
       if (dh == 32)

@@ -147,7 +147,7 @@ enum Option {
   OPT_ATTENTION_TC,       // 0: mma.sync attention instead of the tcgen05 one                         (default 1)
   OPT_ATT_EXACT_MAX,      // 1: exact row-maximum pass for every softmax row                          (default 0)
   OPT_ATT_TURNS,          // 0: softmax groups free-running instead of taking turns on the SFU        (default 1)
-  OPT_ATT_POLY,           // of every 8 exponentials, how many run on the FMA pipe (0..8)            (default set in encoder.cu)
+  OPT_ATT_POLY,           // of every 8 exponentials, how many run on the FMA pipe instead of the SFU (0..4)  (default 1)
   OPT_FUSE_LN,            // 0: separate LayerNorm kernel                                             (default 1)
   OPT_FUSE_FFN,           // 0: FFN1 / FFN2 as two GEMMs                                              (default 1)
   OPT_SERPENTINE,         // 0: every kernel walks the rows in the same direction                     (default 1)

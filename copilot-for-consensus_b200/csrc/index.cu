@@ -118,7 +118,7 @@ int check_device_is_sm100(int device) {
 struct OptDef { const char* name; int def, lo, hi; };
 static const OptDef kOptDefs[OPT_COUNT] = {
     {"pdl", 0, 0, 1},           {"gemm_pair", 1, 0, 1},      {"gemm_ast", 1, 0, 1},   {"attention_tc", 1, 0, 1},
-    {"att_exact_max", 0, 0, 1}, {"att_turns", 1, 0, 1},      {"att_poly", 0, 0, 8},   {"fuse_ln", 1, 0, 1},
+    {"att_exact_max", 0, 0, 1}, {"att_turns", 1, 0, 1},      {"att_poly", 1, 0, 4},   {"fuse_ln", 1, 0, 1},
     {"fuse_ffn", 1, 0, 1},      {"serpentine", 1, 0, 1},     {"sim_pair", 1, 0, 1},   {"sim_bound", 3, 0, 3},
     {"sim_refresh_mask", 0, 0, 1023}, {"search_certify", 1, 0, 1},
 };

@@ -123,7 +123,8 @@ def test_sharp_attention_both_softmax_reference_paths(qk_scale, exact_max):
 @pytest.mark.parametrize("opts", [{"fuse_ffn": 0}, {"fuse_ffn": 0, "fuse_ln": 0},
                                   {"fuse_ffn": 0, "fuse_ln": 0, "gemm_ast": 0},
                                   {"gemm_pair": 0}, {"serpentine": 0}, {"pdl": 1},
-                                  {"attention_tc": 0}, {"att_turns": 0}])
+                                  {"attention_tc": 0}, {"att_turns": 0}, {"att_poly": 0}, {"att_poly": 1}, {"att_poly": 3},
+                                  {"att_poly": 4}])
 def test_alternative_kernel_paths_stay_correct(minilm, minilm_weights, opts):
     """The kernels the default MiniLM path no longer takes (separate FFN GEMMs, separate LayerNorm, the
     non-A-stationary and single-CTA GEMMs, the mma.sync attention) still serve other shapes; the
