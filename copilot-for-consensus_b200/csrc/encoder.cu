@@ -16,6 +16,7 @@
 #include <vector>
 
 #include "attention_tc.cuh"
+#include "attention_tc64.cuh"
 #include "ffn_fused.cuh"
 #include "encoder_kernels.cuh"
 #include "host_util.h"
@@ -66,6 +67,7 @@ struct b200_encoder {
   // activations, sized for m_cap rows
   int64_t m_cap = 0;
   DevBuf x, qkv, ctx, y, ffn, ids, lens, out;
+  DevBuf att_kmax2, att_flag;   // attention_tc64: max |k|^2 per (sequence, head); "take the exact-maximum script" flag
   CUtensorMap map_x, map_ctx, map_ffn;                      // A operands: box {64, 128}
   CUtensorMap map_qkv_st, map_y_st, map_ffn_st, map_x_res;  // epilogue boxes {64, 32}: stores and the residual load
   StreamOrder order;   // calls arriving on different streams share the activation buffers: see host_util.h
@@ -268,6 +270,8 @@ static int ensure_activations(b200_encoder* e, int64_t m_rows, int batch, cudaSt
   const int H = e->cfg.hidden, I = e->cfg.intermediate;
   B200_TRY(e->lens.grow((size_t)std::max(batch, 1) * 4, 0, st));
   B200_TRY(e->out.grow((size_t)std::max(batch, 1) * H * 4, 0, st));
+  B200_TRY(e->att_kmax2.grow((size_t)std::max(batch, 1) * e->cfg.heads * 4, 0, st));
+  B200_TRY(e->att_flag.grow(64, 0, st));
   if (m_rows <= e->m_cap) return B200_OK;
   const int64_t m = (m_rows + 255) / 256 * 256;   // whole 256-row tiles for the CTA-pair GEMM
   B200_TRY(e->ids.grow((size_t)m * 4, 0, st));
@@ -345,6 +349,16 @@ static int run_encoder(b200_encoder* e, const int32_t* d_ids, const int32_t* d_l
   // serpentine row order: every kernel walks the rows in the opposite direction of the one before it
   // (option serpentine=0 disables)
   const bool serp = opt(OPT_SERPENTINE) != 0;
+  // 64-wide heads over whole 128-key blocks (bert-base / mpnet-base-class shapes): the block-wise tcgen05 kernel
+  const bool use_att_tc64 = dh == A64_DH && seq % A64_BK == 0 && opt(OPT_ATTENTION_TC) != 0;
+  typedef void (*Att64Kernel)(const CUtensorMap, const CUtensorMap, const Att64Params);
+  const Att64Kernel att64_kernel = opt(OPT_ATT_POLY) > 0 ? attention_tc64_kernel<1> : attention_tc64_kernel<0>;
+  CUtensorMap map_a64_qkv, map_a64_out;
+  if (use_att_tc64) {
+    B200_TRY(make_tma_2d_bf16(&map_a64_qkv, e->qkv.p, (uint64_t)e->m_cap, (uint64_t)(3 * H), 128, A64_DH));
+    B200_TRY(make_tma_2d_bf16_plain(&map_a64_out, e->ctx.p, (uint64_t)e->m_cap, (uint64_t)H, 32, 32));
+    B200_CUDA(cudaFuncSetAttribute(att64_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)A64_SMEM_BYTES));
+  }
   int kcount = 0;
   for (int l = 0; l < e->cfg.layers; ++l) {
     LayerWeights* L = e->layers[l];
@@ -366,6 +380,24 @@ static int run_encoder(b200_encoder* e, const int32_t* d_ids, const int32_t* d_l
       cudaLaunchAttribute attr[2];
       cfg.attrs = attr; cfg.numAttrs = hot_launch_attrs(attr, false);
       B200_CUDA(cudaLaunchKernelEx(&cfg, att_kernel, map_att_q, map_att_kv, map_att_out, ap));
+    } else if (use_att_tc64) {
+      B200_CUDA(cudaMemsetAsync(e->att_flag.p, 0, 4, st));
+      att_norms_kernel<A64_DH><<<dim3(heads, batch), 128, 0, st>>>(e->qkv.as<__nv_bfloat16>(), seq, H, heads,
+                                                                  e->att_kmax2.as<float>(), e->att_flag.as<int32_t>());
+      B200_CUDA(cudaGetLastError());
+      Att64Params ap{};
+      ap.S = seq; ap.H = H; ap.heads = heads; ap.n_mt = seq / 128; ap.n_units = batch * heads * ap.n_mt;
+      ap.lens = d_lens; ap.kmax2 = e->att_kmax2.as<float>(); ap.exact_flag = e->att_flag.as<int32_t>();
+      ap.force_exact = att_exact_max; ap.reverse = serp ? (kcount++ & 1) : 0;
+      B200_PROF("attention", 4.0 * batch * (double)seq * seq * H, 2.0 * 4.0 * n_tok * H, st);
+      cudaLaunchConfig_t cfg{};
+      cfg.gridDim = dim3(std::min(ap.n_units, e->num_sms));
+      cfg.blockDim = dim3(A64_THREADS);
+      cfg.dynamicSmemBytes = A64_SMEM_BYTES;
+      cfg.stream = st;
+      cudaLaunchAttribute attr[2];
+      cfg.attrs = attr; cfg.numAttrs = 0;
+      B200_CUDA(cudaLaunchKernelEx(&cfg, att64_kernel, map_a64_qkv, map_a64_out, ap));
     } else {
       B200_PROF("attention", 4.0 * batch * (double)seq * seq * H, 2.0 * 4.0 * n_tok * H, st);
       if (dh == 32)

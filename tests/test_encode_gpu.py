@@ -175,6 +175,40 @@ def test_mpnet_base_class_matches_fp32_oracle():
     p.close()
 
 
+@pytest.mark.parametrize("S,qk_scale,exact_max", [(128, 1.0, 0), (256, 1.0, 0), (384, 1.0, 1), (384, 40.0, 0), (512, 1.0, 0)])
+def test_wide_head_attention_block_kernel(S, qk_scale, exact_max):
+    """64-wide heads over whole 128-key blocks run on attention_tc64_kernel (key blocks accumulated under a fixed
+    Cauchy-Schwarz reference).  Both of its scripts against the fp32 oracle: the bound script (random-init weights), the
+    exact-maximum script forced by the option, and the exact script chosen by att_norms_kernel itself when query / key
+    weights are scaled until the bound is unusable; ragged lengths put padding inside and across key blocks."""
+    from safetensors.torch import load_file, save_file
+
+    mio, prov, nat = pkg("embedding.model_io"), pkg("embedding.provider"), pkg("_native")
+    cfg = mio.EncoderConfig(vocab_size=3000, hidden=256, layers=2, heads=4, intermediate=512, max_pos=512, max_seq_length=512)
+    ocfg = eo.EncoderConfig(vocab_size=3000, hidden=256, layers=2, heads=4, intermediate=512, max_pos=512)
+    with tempfile.TemporaryDirectory() as td:
+        mio.write_random_model(td, cfg, seed=9)
+        path = td + "/model.safetensors"
+        save_file({k: v.contiguous() for k, v in _scale_qk(load_file(path), qk_scale).items()}, path)
+        p = prov.B200SentenceTransformerProvider(model_name=td, device="cuda:0")
+    w = _scale_qk(eo.make_weights(ocfg, seed=9), qk_scale)
+    ids, mask, lens = eo.synthetic_tokens(7, S, 3000, seed=S, ragged=True)
+    lens[0], mask[0] = S, 1                                   # one full-length row
+    if S >= 256:
+        lens[1] = 129                                         # one valid key in the second block
+        mask[1] = 0
+        mask[1, :129] = 1
+        ids[1, 129:] = 0
+    with nat.options(att_exact_max=exact_max):
+        got = p.embed_tokens(ids.numpy(), lens.numpy())
+    with nat.options(attention_tc=0):
+        legacy = p.embed_tokens(ids.numpy(), lens.numpy())    # the mma.sync kernel on the same input
+    ref = eo.encode(ocfg, w, ids, mask).numpy()
+    _check(legacy, ref)
+    _check(got, ref)
+    p.close()
+
+
 @pytest.mark.slow
 def test_full_batch_512x256_properties_and_sampled_oracle(minilm, minilm_weights):
     """BASELINE.json configs[1] encode half at full size: every row is checked for unit norm and
