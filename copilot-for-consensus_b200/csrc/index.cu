@@ -180,6 +180,14 @@ struct b200_index {
 
 static constexpr int64_t kMaxRows = (int64_t)1 << 31;  // row ids are uint32 on the device, 2^32-1 is "no row"
 static constexpr int kMaxQueryChunk = 8192;
+// Candidates kept per query and CTA for top_k <= 10.  The certificate fails when the k-th exact score and the KP-th
+// 16-bit score are closer than the rounding bound eps (~7e-4): on random 384-d rows that is a sum of KP - k order-
+// statistic spacings, so its probability falls like eps^(KP - k): measured 2.4e-4 per query at KP = 16, none in
+// 10^5 queries at KP = 20.  A single query tile (<= 128 queries, the HBM-bound regime) has the issue slots to spare
+// for 20; the CTA-pair kernel (tensor-bound, the drain is on its critical path) slows down by 4 - 19 % with 20, more
+// than the one exhaustive re-run per ~4000 queries costs it, and stays at 16.
+static constexpr int kKpSmall = 20;
+static constexpr int kKpPair = 16;
 static constexpr int kMaxCandPerQuery = 8192;
 
 static int index_reserve_locked(b200_index* ix, int64_t cap, cudaStream_t st) {
@@ -289,8 +297,9 @@ static int launch_sim(b200_index* ix, int nq, int nqt, const CUtensorMap& map_q,
 }
 
 // bound on the evaluation error of the two scores the certificate compares: the tensor cores' fp32
-// accumulation of d products (<= 2^-23 relative per addition, doubled) and the canonical fp32 routine
-static float certificate_slop(int d) { return (float)d * 2.384185791015625e-7f + (float)(d / 32 + 16) * 1.1920929e-7f + 1e-6f; }
+// accumulation of d exact products (<= 2^-23 of the running sum per addition even when it truncates, and the sum
+// of the magnitudes is <= 1 in cosine units) and the canonical fp32 routine
+static float certificate_slop(int d) { return (float)d * 1.1920929e-7f + (float)(d / 32 + 16) * 1.1920929e-7f + 1e-6f; }
 
 // exact_topk_kernel over the fail list of the K9 launch just issued (or, with fail == nullptr, over all nq queries)
 template <int METRIC_L2>
@@ -329,7 +338,8 @@ static int search_chunk(b200_index* ix, const void* q_dev, int q_dtype, int nq, 
   int nqt = (nq + SIM_BLOCK_M - 1) / SIM_BLOCK_M;
   // CTA pairs (two query tiles per cluster) for k <= 10 once there are at least two query tiles; an odd
   // tile count is padded with an empty tile.  Option sim_pair=0 forces single-CTA tiles (A/B timing).
-  const bool pair = kp == 16 && nqt >= 2 && opt(OPT_SIM_PAIR) != 0;
+  const bool pair = kp == kKpSmall && nqt >= 2 && opt(OPT_SIM_PAIR) != 0;
+  if (pair) kp = kKpPair;
   if (pair) nqt = (nqt + 1) & ~1;
   const int nq_pad = nqt * SIM_BLOCK_M;
   B200_TRY(ix->q16.grow((size_t)nq_pad * ix->dpad * 2, 0, st));
@@ -353,8 +363,8 @@ static int search_chunk(b200_index* ix, const void* q_dev, int q_dtype, int nq, 
   CUtensorMap map_q;
   B200_TRY(make_tma_2d_bf16(&map_q, ix->q16.p, (uint64_t)nq_pad, (uint64_t)ix->dpad, SIM_BLOCK_M, SIM_BLOCK_K));
   SimParams sp{};
-  if (pair) B200_TRY((launch_sim<256, 16, 2>(ix, nq, nqt, map_q, st, &sp)));
-  else if (kp == 16) B200_TRY((launch_sim<256, 16, 1>(ix, nq, nqt, map_q, st, &sp)));
+  if (pair) B200_TRY((launch_sim<256, kKpPair, 2>(ix, nq, nqt, map_q, st, &sp)));
+  else if (kp == kKpSmall) B200_TRY((launch_sim<256, kKpSmall, 1>(ix, nq, nqt, map_q, st, &sp)));
   else if (kp == 32) B200_TRY((launch_sim<128, 32, 1>(ix, nq, nqt, map_q, st, &sp)));
   else B200_TRY((launch_sim<128, 64, 1>(ix, nq, nqt, map_q, st, &sp)));
   const int nsplit = sp.nsplit;
@@ -698,7 +708,7 @@ static int search_impl(b200_index* ix, const void* queries, int q_dtype, int que
   if (!queries || (!packed && (!ids || !scores))) B200_FAIL(B200_ERR_INVALID, "NULL buffer");
   if (q_dtype != 0 && q_dtype != 1) B200_FAIL(B200_ERR_INVALID, "q_dtype must be 0 (fp32) or 1 (bf16)");
   if (k > EXH_KEEP) B200_FAIL(B200_ERR_UNSUPPORTED, "k=%d: top_k above %d is not supported", k, EXH_KEEP);
-  const int kp = k <= 10 ? 16 : (k <= 24 ? 32 : 64);
+  const int kp = k <= 10 ? kKpSmall : (k <= 24 ? 32 : 64);
   std::lock_guard<std::mutex> lk(ix->mu);
   DeviceGuard g(ix->device);
   cudaStream_t st = (cudaStream_t)stream;
@@ -908,7 +918,7 @@ int static_scratch_for_current_device(int device, unsigned char** out) {
     // it is used.  Touch every kernel this entry point can launch now, so that a later call in another k band or
     // query dtype loads nothing.
     cudaFuncAttributes fa;
-    B200_CUDA(cudaFuncGetAttributes(&fa, sim_topk_kernel<256, 16, 1>));
+    B200_CUDA(cudaFuncGetAttributes(&fa, sim_topk_kernel<256, kKpSmall, 1>));
     B200_CUDA(cudaFuncGetAttributes(&fa, sim_topk_kernel<128, 32, 1>));
     B200_CUDA(cudaFuncGetAttributes(&fa, sim_topk_kernel<128, 64, 1>));
     B200_CUDA(cudaFuncGetAttributes(&fa, prep_queries_kernel<float>));
@@ -968,7 +978,7 @@ extern "C" int b200_index_search_static(b200_index_t* ix, const void* queries_de
   if (ix->dpad > kStaticMaxDpad)
     B200_FAIL(B200_ERR_UNSUPPORTED, "b200_index_search_static covers dimensions up to %d (index has %d)", kStaticMaxDpad, ix->dim);
   if (k > 48) B200_FAIL(B200_ERR_UNSUPPORTED, "k=%d: the fused select keeps at most 64 candidates per query (k <= 48)", k);
-  const int kp = k <= 10 ? 16 : (k <= 24 ? 32 : 64);
+  const int kp = k <= 10 ? kKpSmall : (k <= 24 ? 32 : 64);
   std::lock_guard<std::mutex> lk(ix->mu);
   std::lock_guard<std::mutex> lk2(g_static_mu);
   DeviceGuard g(ix->device);
@@ -1007,7 +1017,7 @@ extern "C" int b200_index_search_static(b200_index_t* ix, const void* queries_de
   CUtensorMap map_q;
   B200_TRY(make_tma_2d_bf16(&map_q, q16, (uint64_t)nq_pad, (uint64_t)ix->dpad, SIM_BLOCK_M, SIM_BLOCK_K));
   SimParams sp{};
-  if (kp == 16) B200_TRY((launch_sim_static<256, 16>(ix, n, map_q, cand, gthr, st, &sp)));
+  if (kp == kKpSmall) B200_TRY((launch_sim_static<256, kKpSmall>(ix, n, map_q, cand, gthr, st, &sp)));
   else if (kp == 32) B200_TRY((launch_sim_static<128, 32>(ix, n, map_q, cand, gthr, st, &sp)));
   else B200_TRY((launch_sim_static<128, 64>(ix, n, map_q, cand, gthr, st, &sp)));
   const int nsplit = sp.nsplit;
