@@ -57,15 +57,19 @@ struct Att64Params {
 // max_j |k_j|^2 and max_r |q_r|^2 of every (sequence, head); raises *flag when the Cauchy-Schwarz reference could
 // leave a row's leading probabilities outside the normal fp32 / bf16 range (see ATT_BOUND_GAP).
 template <int DH>
-__global__ void __launch_bounds__(128) att_norms_kernel(const __nv_bfloat16* __restrict__ qkv, int S, int H, int heads,
+__global__ void __launch_bounds__(256) att_norms_kernel(const __nv_bfloat16* __restrict__ qkv, int S, int H, int heads,
                                                         float* __restrict__ kmax2, int32_t* __restrict__ flag) {
+  // DH / 8 lanes per row, 16 bytes each: a row's 2 * DH bytes are one contiguous, fully used segment
+  constexpr int LPR = DH / 8, RPW = 32 / LPR;
   const int h = blockIdx.x, b = blockIdx.y;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
+  const int sub = lane / LPR, c = lane % LPR;
   float q2m = 0.f, k2m = 0.f;
-  for (int j = threadIdx.x; j < S; j += blockDim.x) {
-    const __nv_bfloat16* row = qkv + (size_t)(b * S + j) * 3 * H + h * DH;
+  for (int j0 = warp * RPW; j0 < S; j0 += nwarp * RPW) {
+    const int j = j0 + sub;
     float q2 = 0.f, k2 = 0.f;
-#pragma unroll
-    for (int c = 0; c < DH / 8; ++c) {
+    if (j < S) {
+      const __nv_bfloat16* row = qkv + (size_t)(b * S + j) * 3 * H + h * DH;
       const uint4 wq = __ldg(reinterpret_cast<const uint4*>(row) + c);
       const uint4 wk = __ldg(reinterpret_cast<const uint4*>(row + H) + c);
       const uint32_t a[4] = {wq.x, wq.y, wq.z, wq.w}, kk[4] = {wk.x, wk.y, wk.z, wk.w};
@@ -77,17 +81,21 @@ __global__ void __launch_bounds__(128) att_norms_kernel(const __nv_bfloat16* __r
         k2 = fmaf(k0, k0, fmaf(k1, k1, k2));
       }
     }
+#pragma unroll
+    for (int o = LPR / 2; o > 0; o >>= 1) {
+      q2 += __shfl_xor_sync(0xffffffffu, q2, o);
+      k2 += __shfl_xor_sync(0xffffffffu, k2, o);
+    }
     q2m = fmaxf(q2m, q2);
     k2m = fmaxf(k2m, k2);
   }
-  __shared__ float sq[4], sk[4];
+  __shared__ float sq[8], sk[8];
   q2m = warp_max(q2m);
   k2m = warp_max(k2m);
-  if ((threadIdx.x & 31) == 0) { sq[threadIdx.x >> 5] = q2m; sk[threadIdx.x >> 5] = k2m; }
+  if (lane == 0) { sq[warp] = q2m; sk[warp] = k2m; }
   __syncthreads();
   if (threadIdx.x == 0) {
-    q2m = fmaxf(fmaxf(sq[0], sq[1]), fmaxf(sq[2], sq[3]));
-    k2m = fmaxf(fmaxf(sk[0], sk[1]), fmaxf(sk[2], sk[3]));
+    for (int w = 1; w < nwarp; ++w) { q2m = fmaxf(q2m, sq[w]); k2m = fmaxf(k2m, sk[w]); }
     kmax2[b * heads + h] = k2m;
     const float gap_sq = 0.25f * ATT_BOUND_GAP * ATT_BOUND_GAP / (ATT_NORM_SLACK * ATT_NORM_SLACK);
     if (!(q2m * k2m <= gap_sq)) atomicOr(flag, 1);

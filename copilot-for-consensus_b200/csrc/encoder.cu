@@ -382,7 +382,7 @@ static int run_encoder(b200_encoder* e, const int32_t* d_ids, const int32_t* d_l
       B200_CUDA(cudaLaunchKernelEx(&cfg, att_kernel, map_att_q, map_att_kv, map_att_out, ap));
     } else if (use_att_tc64) {
       B200_CUDA(cudaMemsetAsync(e->att_flag.p, 0, 4, st));
-      att_norms_kernel<A64_DH><<<dim3(heads, batch), 128, 0, st>>>(e->qkv.as<__nv_bfloat16>(), seq, H, heads,
+      att_norms_kernel<A64_DH><<<dim3(heads, batch), 256, 0, st>>>(e->qkv.as<__nv_bfloat16>(), seq, H, heads,
                                                                   e->att_kmax2.as<float>(), e->att_flag.as<int32_t>());
       B200_CUDA(cudaGetLastError());
       Att64Params ap{};
