@@ -316,7 +316,7 @@ def run_b200(a) -> None:
         mio.write_random_model(td, "all-MiniLM-L6-v2", seed=0)
         prov = prov_mod.B200SentenceTransformerProvider(model_name=td, device=f"cuda:{local}")
     index, r0 = build_index(a.corpus_rows, 1000)
-    searcher = sh.ShardedSearch.over_index(index, r0)
+    searcher = sh.ShardedSearch.over_index(index, r0)      # N > 1: hit records through NVLink peer memory when available
 
     # per-step inputs: fresh token ids each step from a pool larger than L2 would need to be >126 MB; the
     # dominant streams (activations 100 MB+/layer, corpus 768 MB/shard at N=1) already exceed L2 every step
@@ -461,10 +461,14 @@ def run_b200(a) -> None:
             n_big = 10_000_000
             big, b0 = build_index(n_big, 5000)
             bs = sh.ShardedSearch.over_index(big, b0)
+            bs_nccl = sh.ShardedSearch.over_index(big, b0, exchange="nccl") if world > 1 and bs.exchange == "peer" else None
             rows_rank = len(big)
             s10 = {"rows_global": n_big, "rows_per_gpu": rows_rank, "algorithmic_bytes_per_pass_per_gpu": rows_rank * 768,
                    "traffic": traffic_per_launch("sim_topk"),
-                   "api": "ShardedSearch.search_replicated (b200_index_search_packed -> all-gather -> b200_merge_hits)"}
+                   "exchange": bs.exchange,
+                   "api": "ShardedSearch.search_replicated: b200_index_search_exchange (hit records stored into NVLink peer memory) -> "
+                          "b200_merge_hits_wait" if bs.exchange == "peer" else
+                          "ShardedSearch.search_replicated: b200_index_search_packed -> all-gather -> b200_merge_hits"}
             gq = torch.Generator(device=dev).manual_seed(77)
             for nq in (4096, 128, 1):
                 q = torch.randn((nq, 384), generator=gq, device=dev, dtype=torch.float32).bfloat16().contiguous()
@@ -478,6 +482,9 @@ def run_b200(a) -> None:
                                  "frac_burst": max(t_hbm, t_b) / ms, "frac_sustained": max(t_hbm, t_s) / ms,
                                  "gbs_per_gpu": rows_rank * 768 / (ms * 1e-3) / 1e9,
                                  "tflops_per_gpu": nq * rows_rank * 768.0 / (ms * 1e-3) / 1e12}
+                if bs_nccl is not None:
+                    ms2, _, n2 = timed(lambda: bs_nccl.search_replicated(q, a.top_k), 5, 3)
+                    s10[f"q{nq}"]["ms_per_batch_nccl_all_gather"] = ms2 / n2
             chk, redo = big.certificate_stats()
             s10["certificate"] = {"queries_checked": chk, "queries_rescored_exhaustively": redo}
             roofline["search_10M"] = s10

@@ -46,6 +46,8 @@ SYMBOLS = {
     "b200_index_search_static": (_i, [_vp, _vp, _i, _i64, _i, _i64, _vp, _vp, _vp]),
     "b200_index_search_packed": (_i, [_vp, _vp, _i, _i64, _i, _i64, _vp, _vp]),
     "b200_merge_hits": (_i, [_vp, _i, _i64, _i, _i64, _i64, _i, _vp, _vp, _i, _vp]),
+    "b200_index_search_exchange": (_i, [_vp, _vp, _i, _i64, _i, _i64, _vp, _vp, _i, _i, ctypes.c_uint32, _vp]),
+    "b200_merge_hits_wait": (_i, [_vp, _vp, ctypes.c_uint32, _i, _i64, _i, _i64, _i64, _i, _vp, _vp, _i, _vp]),
     "b200_merge_topk": (_i, [_vp, _vp, _i64, _i, _i, _i, _vp, _vp, _i, _vp]),
     "b200_encoder_create": (_i, [ctypes.POINTER(EncoderConfigC), _i, ctypes.POINTER(_vp)]),
     "b200_encoder_destroy": (_i, [_vp]),

@@ -188,6 +188,7 @@ static constexpr int kMaxQueryChunk = 8192;
 // than the one exhaustive re-run per ~4000 queries costs it, and stays at 16.
 static constexpr int kKpSmall = 20;
 static constexpr int kKpPair = 16;
+static constexpr int64_t kPairKp20BelowRows = 500000;
 static constexpr int kMaxCandPerQuery = 8192;
 
 static int index_reserve_locked(b200_index* ix, int64_t cap, cudaStream_t st) {
@@ -305,7 +306,7 @@ static float certificate_slop(int d) { return (float)d * 1.1920929e-7f + (float)
 template <int METRIC_L2>
 static int launch_exact(b200_index* ix, const uint32_t* fail_count, const int32_t* fail_idx, uint32_t* ticket, int nq,
                         const float* q_f32, int k, int64_t id_base, int64_t* ids_dev, float* sc_dev, cudaStream_t st,
-                        uint64_t* part = nullptr, int grid = 0, ulonglong2* packed_dev = nullptr) {
+                        uint64_t* part = nullptr, int grid = 0, HitSink packed_dev = HitSink{}) {
   const size_t smem = (size_t)EXACT_MERGE * 8 + (size_t)ix->dim * 4;
   auto kern = exact_topk_kernel<METRIC_L2>;
   B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -333,13 +334,22 @@ static int launch_exact(b200_index* ix, const uint32_t* fail_count, const int32_
   return B200_OK;
 }
 
+static HitSink sink_at(const HitSink& s, size_t off) {
+  HitSink r = s;
+  if (r.one) r.one += off;
+  for (int i = 0; i < r.n_peers; ++i) r.peer[i] += off;
+  return r;
+}
+static bool sink_on(const HitSink& s) { return s.one != nullptr || s.n_peers > 0; }
+
 static int search_chunk(b200_index* ix, const void* q_dev, int q_dtype, int nq, int k, int kp, int64_t id_base,
-                        int64_t* ids_dev, float* sc_dev, ulonglong2* packed_dev, cudaStream_t st) {
+                        int64_t* ids_dev, float* sc_dev, HitSink packed_dev, cudaStream_t st) {
   int nqt = (nq + SIM_BLOCK_M - 1) / SIM_BLOCK_M;
   // CTA pairs (two query tiles per cluster) for k <= 10 once there are at least two query tiles; an odd
   // tile count is padded with an empty tile.  Option sim_pair=0 forces single-CTA tiles (A/B timing).
   const bool pair = kp == kKpSmall && nqt >= 2 && opt(OPT_SIM_PAIR) != 0;
-  if (pair) kp = kKpPair;
+  // small shards: a re-run's fixed cost outweighs the slower drain (measured cross-over near half a million rows)
+  if (pair && ix->count >= kPairKp20BelowRows) kp = kKpPair;
   if (pair) nqt = (nqt + 1) & ~1;
   const int nq_pad = nqt * SIM_BLOCK_M;
   B200_TRY(ix->q16.grow((size_t)nq_pad * ix->dpad * 2, 0, st));
@@ -363,7 +373,8 @@ static int search_chunk(b200_index* ix, const void* q_dev, int q_dtype, int nq, 
   CUtensorMap map_q;
   B200_TRY(make_tma_2d_bf16(&map_q, ix->q16.p, (uint64_t)nq_pad, (uint64_t)ix->dpad, SIM_BLOCK_M, SIM_BLOCK_K));
   SimParams sp{};
-  if (pair) B200_TRY((launch_sim<256, kKpPair, 2>(ix, nq, nqt, map_q, st, &sp)));
+  if (pair && kp == kKpPair) B200_TRY((launch_sim<256, kKpPair, 2>(ix, nq, nqt, map_q, st, &sp)));
+  else if (pair) B200_TRY((launch_sim<256, kKpSmall, 2>(ix, nq, nqt, map_q, st, &sp)));
   else if (kp == kKpSmall) B200_TRY((launch_sim<256, kKpSmall, 1>(ix, nq, nqt, map_q, st, &sp)));
   else if (kp == 32) B200_TRY((launch_sim<128, 32, 1>(ix, nq, nqt, map_q, st, &sp)));
   else B200_TRY((launch_sim<128, 64, 1>(ix, nq, nqt, map_q, st, &sp)));
@@ -657,7 +668,7 @@ int b200_index_get_rows(b200_index_t* ix, const int64_t* rows, int64_t n, float*
 
 // top_k in (48, EXH_KEEP]: exhaustive exact scoring, one query at a time (see search_kernels.cuh).
 static int search_exhaustive(b200_index* ix, const uint8_t* q_dev, int q_dtype, int64_t nq, int k, int64_t id_base,
-                             int64_t* d_ids, float* d_sc, ulonglong2* d_packed, cudaStream_t st) {
+                             int64_t* d_ids, float* d_sc, HitSink d_packed, cudaStream_t st) {
   const uint32_t n_rows = (uint32_t)ix->count;
   const uint64_t chunks0 = ((uint64_t)n_rows + EXH_CHUNK - 1) / EXH_CHUNK;
   // scratch: fp32 copy of one query, keys of every row, two ping-pong survivor buffers
@@ -692,8 +703,8 @@ static int search_exhaustive(b200_index* ix, const uint8_t* q_dev, int q_dtype, 
       pp ^= 1;
       if (chunks == 1) break;
     }
-    exh_write_kernel<<<1, 256, 0, st>>>(in, EXH_KEEP, k, id_base, d_packed ? nullptr : d_ids + q * k,
-                                        d_packed ? nullptr : d_sc + q * k, d_packed ? d_packed + q * k : nullptr);
+    exh_write_kernel<<<1, 256, 0, st>>>(in, EXH_KEEP, k, id_base, sink_on(d_packed) ? nullptr : d_ids + q * k,
+                                        sink_on(d_packed) ? nullptr : d_sc + q * k, d_packed, sink_on(d_packed) ? (size_t)(q * k) : 0);
     B200_CUDA(cudaGetLastError());
   }
   return B200_OK;
@@ -701,11 +712,12 @@ static int search_exhaustive(b200_index* ix, const uint8_t* q_dev, int q_dtype, 
 
 // b200_index_search and b200_index_search_packed: `packed` (device, [nq][k] 16-byte records) replaces ids / scores
 static int search_impl(b200_index* ix, const void* queries, int q_dtype, int queries_on_device, int64_t nq, int k,
-                       int64_t id_base, int64_t* ids, float* scores, ulonglong2* packed, int out_on_device, void* stream) {
+                       int64_t id_base, int64_t* ids, float* scores, HitSink packed, int out_on_device, void* stream) {
+  const bool is_packed = sink_on(packed);
   if (!ix) B200_FAIL(B200_ERR_INVALID, "index is NULL");
   if (nq < 0 || k < 0) B200_FAIL(B200_ERR_INVALID, "negative nq / k");
   if (nq == 0 || k == 0) return B200_OK;
-  if (!queries || (!packed && (!ids || !scores))) B200_FAIL(B200_ERR_INVALID, "NULL buffer");
+  if (!queries || (!is_packed && (!ids || !scores))) B200_FAIL(B200_ERR_INVALID, "NULL buffer");
   if (q_dtype != 0 && q_dtype != 1) B200_FAIL(B200_ERR_INVALID, "q_dtype must be 0 (fp32) or 1 (bf16)");
   if (k > EXH_KEEP) B200_FAIL(B200_ERR_UNSUPPORTED, "k=%d: top_k above %d is not supported", k, EXH_KEEP);
   const int kp = k <= 10 ? kKpSmall : (k <= 24 ? 32 : 64);
@@ -717,7 +729,7 @@ static int search_impl(b200_index* ix, const void* queries, int q_dtype, int que
 
   int64_t* d_ids = ids;
   float* d_sc = scores;
-  if (!packed && !out_on_device) {
+  if (!is_packed && !out_on_device) {
     B200_TRY(ix->out_ids.grow((size_t)nq * k * 8, 0, st));
     B200_TRY(ix->out_scores.grow((size_t)nq * k * 4, 0, st));
     d_ids = ix->out_ids.as<int64_t>();
@@ -740,35 +752,59 @@ static int search_impl(b200_index* ix, const void* queries, int q_dtype, int que
       for (int64_t q0 = 0; q0 < nq; q0 += kMaxQueryChunk) {
         const int n = (int)std::min<int64_t>(kMaxQueryChunk, nq - q0);
         B200_TRY(search_chunk(ix, q_dev + (size_t)q0 * ix->dim * qelt, q_dtype, n, k, kp, id_base,
-                              packed ? nullptr : d_ids + q0 * k, packed ? nullptr : d_sc + q0 * k,
-                              packed ? packed + q0 * k : nullptr, st));
+                              is_packed ? nullptr : d_ids + q0 * k, is_packed ? nullptr : d_sc + q0 * k,
+                              is_packed ? sink_at(packed, (size_t)(q0 * k)) : HitSink{}, st));
       }
     }
   }
-  if (!packed && !out_on_device) {
+  if (!is_packed && !out_on_device) {
     B200_CUDA(cudaMemcpyAsync(ids, d_ids, (size_t)nq * k * 8, cudaMemcpyDeviceToHost, st));
     B200_CUDA(cudaMemcpyAsync(scores, d_sc, (size_t)nq * k * 4, cudaMemcpyDeviceToHost, st));
   }
   B200_TRY(ix->order.leave(st));
-  if (!packed && !out_on_device) B200_CUDA(cudaStreamSynchronize(st));
+  if (!is_packed && !out_on_device) B200_CUDA(cudaStreamSynchronize(st));
   return B200_OK;
 }
 
 extern "C" {
 
+int b200_index_search_exchange(b200_index_t* ix, const void* queries_dev, int q_dtype, int64_t nq, int k, int64_t id_base,
+                               void* const* peer_hits, void* const* peer_flags, int world, int rank, uint32_t epoch,
+                               void* stream) {
+  if (!ix) B200_FAIL(B200_ERR_INVALID, "index is NULL");
+  if (!peer_hits || !peer_flags) B200_FAIL(B200_ERR_INVALID, "NULL buffer");
+  if (world < 1 || world > kMaxPeers || rank < 0 || rank >= world)
+    B200_FAIL(B200_ERR_UNSUPPORTED, "peer exchange covers 1..%d ranks (got world %d, rank %d)", kMaxPeers, world, rank);
+  HitSink sink{}, flags{};
+  sink.n_peers = flags.n_peers = world;
+  for (int i = 0; i < world; ++i) {
+    if (!peer_hits[i] || !peer_flags[i]) B200_FAIL(B200_ERR_INVALID, "NULL peer buffer %d", i);
+    sink.peer[i] = static_cast<ulonglong2*>(peer_hits[i]);
+    flags.peer[i] = static_cast<ulonglong2*>(peer_flags[i]);
+  }
+  if (nq > 0 && k > 0) B200_TRY(search_impl(ix, queries_dev, q_dtype, 1, nq, k, id_base, nullptr, nullptr, sink, 1, stream));
+  DeviceGuard g(ix->device);
+  signal_peers_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(flags, rank, epoch);
+  B200_CUDA(cudaGetLastError());
+  return B200_OK;
+}
+
 int b200_index_search(b200_index_t* ix, const void* queries, int q_dtype, int queries_on_device, int64_t nq, int k,
                       int64_t id_base, int64_t* ids, float* scores, int out_on_device, void* stream) {
-  return search_impl(ix, queries, q_dtype, queries_on_device, nq, k, id_base, ids, scores, nullptr, out_on_device, stream);
+  return search_impl(ix, queries, q_dtype, queries_on_device, nq, k, id_base, ids, scores, HitSink{}, out_on_device, stream);
 }
 
 int b200_index_search_packed(b200_index_t* ix, const void* queries_dev, int q_dtype, int64_t nq, int k, int64_t id_base,
                              void* hits_dev, void* stream) {
   if (!hits_dev) B200_FAIL(B200_ERR_INVALID, "NULL buffer");
-  return search_impl(ix, queries_dev, q_dtype, 1, nq, k, id_base, nullptr, nullptr, static_cast<ulonglong2*>(hits_dev), 1, stream);
+  HitSink sink{};
+  sink.one = static_cast<ulonglong2*>(hits_dev);
+  return search_impl(ix, queries_dev, q_dtype, 1, nq, k, id_base, nullptr, nullptr, sink, 1, stream);
 }
 
-int b200_merge_hits(const void* hits_in, int nlists, int64_t nq_per_list, int k_in, int64_t q_first, int64_t nq, int k_out,
-                    int64_t* ids_out, float* scores_out, int device, void* stream) {
+static int merge_hits_impl(const void* hits_in, int nlists, int64_t nq_per_list, int k_in, int64_t q_first, int64_t nq, int k_out,
+                           int64_t* ids_out, float* scores_out, const uint32_t* wait_flags, uint32_t epoch, int device,
+                           void* stream) {
   if (nq < 0 || nlists <= 0 || k_in <= 0 || k_out <= 0 || q_first < 0 || q_first + nq > nq_per_list)
     B200_FAIL(B200_ERR_INVALID, "bad merge shape");
   if (nq == 0) return B200_OK;
@@ -780,10 +816,24 @@ int b200_merge_hits(const void* hits_in, int nlists, int64_t nq_per_list, int k_
   {
     B200_PROF("merge_hits", 0.0, (double)nq * nlists * k_in * 16.0, (cudaStream_t)stream);
     merge_packed_kernel<<<(unsigned)((nq + wpb - 1) / wpb), wpb * 32, 0, (cudaStream_t)stream>>>(
-        static_cast<const ulonglong2*>(hits_in), nlists, (int)nq_per_list, k_in, (int)q_first, (int)nq, k_out, ids_out, scores_out);
+        static_cast<const ulonglong2*>(hits_in), nlists, (int)nq_per_list, k_in, (int)q_first, (int)nq, k_out, ids_out, scores_out,
+        wait_flags, epoch);
   }
   B200_CUDA(cudaGetLastError());
   return B200_OK;
+}
+
+int b200_merge_hits(const void* hits_in, int nlists, int64_t nq_per_list, int k_in, int64_t q_first, int64_t nq, int k_out,
+                    int64_t* ids_out, float* scores_out, int device, void* stream) {
+  return merge_hits_impl(hits_in, nlists, nq_per_list, k_in, q_first, nq, k_out, ids_out, scores_out, nullptr, 0, device, stream);
+}
+
+int b200_merge_hits_wait(const void* hits_local, const void* flags_local, uint32_t epoch, int nlists, int64_t nq_per_list, int k_in,
+                         int64_t q_first, int64_t nq, int k_out, int64_t* ids_out, float* scores_out, int device, void* stream) {
+  if (!flags_local) B200_FAIL(B200_ERR_INVALID, "NULL flags");
+  if (nlists > 32) B200_FAIL(B200_ERR_UNSUPPORTED, "at most 32 lists can be waited for");
+  return merge_hits_impl(hits_local, nlists, nq_per_list, k_in, q_first, nq, k_out, ids_out, scores_out,
+                         static_cast<const uint32_t*>(flags_local), epoch, device, stream);
 }
 
 int b200_index_certificate_stats(b200_index_t* ix, int64_t* checked, int64_t* recomputed) {
@@ -1030,7 +1080,7 @@ extern "C" int b200_index_search_static(b200_index_t* ix, const void* queries_de
   m.n_rows = (uint32_t)ix->count; m.id_base = id_base;
   m.cand = cand; m.q_f32 = q_f32; m.master = ix->master.p;
   m.master_is_bf16 = ix->master_dtype == B200_INDEX_MASTER_BF16;
-  m.out_ids = ids_dev; m.out_scores = scores_dev; m.out_packed = nullptr;
+  m.out_ids = ids_dev; m.out_scores = scores_dev; m.out_packed = HitSink{};
   // same exactness certificate as b200_index_search, its bookkeeping inside the static array
   uint32_t* ticket = cert + 16;
   int32_t* fail_idx = reinterpret_cast<int32_t*>(ticket + kStaticMaxQueries);

@@ -214,15 +214,27 @@ struct SimParams {
 // One search hit as a 16-byte record: x = orderable(score) << 32 (0 = no hit), y = global id (-1 = no hit).
 // This is what travels between GPUs: a shard's K9 writes records straight into the all-gather send buffer and
 // K10 reads the gathered buffer, with nothing in between.
-B200_DEVINL void write_hit(int64_t* ids, float* scores, ulonglong2* packed, size_t at, uint64_t key, int64_t id_base,
+// Where a packed result goes: one buffer, or the same slot of a buffer on EVERY GPU of the group (peer-mapped
+// pointers: plain stores over NVLink), which replaces the all-gather of the sharded search (see sharded.py).
+constexpr int kMaxPeers = 8;
+struct HitSink {
+  ulonglong2* one;                 // nullptr: not a packed result (ids / scores arrays) unless n_peers > 0
+  ulonglong2* peer[kMaxPeers];     // n_peers > 0: this shard's slot in every rank's receive buffer
+  int n_peers;
+};
+
+B200_DEVINL void write_hit(int64_t* ids, float* scores, const HitSink& sink, size_t at, uint64_t key, int64_t id_base,
                            bool negate_score) {
   const bool hit = key != 0;
   const int64_t id = hit ? id_base + (int64_t)(~(uint32_t)(key & 0xFFFFFFFFu)) : -1;
-  if (packed) {
+  if (sink.one || sink.n_peers) {
     ulonglong2 r;
     r.x = hit ? (key & 0xFFFFFFFF00000000ull) : 0ull;
     r.y = (unsigned long long)id;
-    packed[at] = r;
+    if (sink.one) sink.one[at] = r;
+#pragma unroll
+    for (int i = 0; i < kMaxPeers; ++i)
+      if (i < sink.n_peers) sink.peer[i][at] = r;
   } else {
     const float sc = orderable_f32((uint32_t)(key >> 32));
     ids[at] = id;
@@ -573,7 +585,7 @@ struct MergeParams {
   int master_is_bf16;
   int64_t* out_ids;         // [nq, k]
   float* out_scores;        // [nq, k]
-  ulonglong2* out_packed;   // [nq, k] or nullptr: (orderable(score) << 32, global id) records instead of the two arrays
+  HitSink out_packed;       // packed [nq, k] records (orderable(score) << 32, global id) instead of the two arrays
   // --- K8's shared score bounds as it left them (see SimParams): candidates below them cannot be among the KP best ---
   const uint32_t* gbkt;     // [nq][kp] bucket bests, nullptr or use_bound == 0: not used
   const uint32_t* gthr;     // [nq] best full-set worst, nullptr or use_gthr == 0: not used
@@ -714,7 +726,7 @@ struct ExactParams {
   uint32_t* ticket;             // [nq] zeroed before the launch; gridDim.x + 1 = that query's result is written
   int64_t* out_ids;
   float* out_scores;
-  ulonglong2* out_packed;       // see MergeParams
+  HitSink out_packed;           // see MergeParams
 };
 
 // FAISS IndexFlatL2 semantics (faiss_store.py:99-101,212-224): squared Euclidean distance, ascending; the
@@ -1048,13 +1060,13 @@ __global__ void exh_query_f32_kernel(const __nv_bfloat16* __restrict__ q, int d,
 
 // the single surviving sorted list -> ids / scores of one query
 __global__ void exh_write_kernel(const uint64_t* __restrict__ keys, int n_keys, int k, int64_t id_base,
-                                 int64_t* __restrict__ ids, float* __restrict__ scores, ulonglong2* __restrict__ packed) {
+                                 int64_t* __restrict__ ids, float* __restrict__ scores, const HitSink packed, size_t at0) {
   for (int j = threadIdx.x; j < k; j += blockDim.x)
-    write_hit(ids, scores, packed, (size_t)j, j < n_keys ? keys[j] : 0ull, id_base, false);
+    write_hit(ids, scores, packed, at0 + (size_t)j, j < n_keys ? keys[j] : 0ull, id_base, false);
 }
 
 // "no rows": every slot of an [n] result is the empty hit
-__global__ void fill_no_hits_kernel(int64_t* __restrict__ ids, float* __restrict__ scores, ulonglong2* __restrict__ packed,
+__global__ void fill_no_hits_kernel(int64_t* __restrict__ ids, float* __restrict__ scores, const HitSink packed,
                                     size_t n) {
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
     write_hit(ids, scores, packed, i, 0ull, 0, false);
@@ -1108,12 +1120,35 @@ __global__ void __launch_bounds__(128) merge_lists_kernel(const int64_t* __restr
 
 // K10 over packed records (see write_hit): lists arrive as [nlists][nq_per_list][k_in] -- exactly the buffer an
 // all-gather of every shard's K9 output produces -- and this GPU merges queries [q_first, q_first + nq).
+// Peer exchange, producer side: after the kernels that stored this shard's records into every rank's buffer
+// (same stream, so their stores are complete), publish "search number `epoch` of rank `rank` has arrived" to every rank.
+__global__ void signal_peers_kernel(const HitSink flags, int rank, uint32_t epoch) {
+  const int i = threadIdx.x;
+  if (i < flags.n_peers) {
+    __threadfence_system();
+    uint32_t* f = reinterpret_cast<uint32_t*>(flags.peer[i]) + rank;
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(f), "r"(epoch) : "memory");
+  }
+}
+
+// wait_flags != nullptr: consumer side of the peer exchange -- before reading, wait until every rank has published
+// `epoch` (flags only grow; a rank may already be one search ahead, which uses the other half of the buffer).
 __global__ void __launch_bounds__(128) merge_packed_kernel(const ulonglong2* __restrict__ in, int nlists, int nq_per_list,
                                                            int k_in, int q_first, int nq, int k_out,
-                                                           int64_t* __restrict__ ids_out, float* __restrict__ sc_out) {
+                                                           int64_t* __restrict__ ids_out, float* __restrict__ sc_out,
+                                                           const uint32_t* __restrict__ wait_flags, uint32_t epoch) {
   const int q = blockIdx.x * (blockDim.x / kWarp) + (threadIdx.x / kWarp);
-  if (q >= nq) return;
   const int lane = threadIdx.x & 31;
+  if (wait_flags) {
+    if (lane < nlists) {
+      uint32_t v;
+      do {
+        asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(wait_flags + lane) : "memory");
+      } while ((int32_t)(v - epoch) < 0);
+    }
+    __syncwarp();
+  }
+  if (q >= nq) return;
   const int total = nlists * k_in;
   // (x desc, id asc) as one comparison: x carries the orderable score in its high half, ids are non-negative
   unsigned long long prev_x = ~0ull;
@@ -1123,7 +1158,7 @@ __global__ void __launch_bounds__(128) merge_packed_kernel(const ulonglong2* __r
     long long best_id = INT64_MAX;
     for (int i = lane; i < total; i += kWarp) {
       const int l = i / k_in, e = i - l * k_in;
-      const ulonglong2 r = __ldg(in + ((size_t)l * nq_per_list + q_first + q) * k_in + e);
+      const ulonglong2 r = __ldcg(in + ((size_t)l * nq_per_list + q_first + q) * k_in + e);   // not the read-only path: peers wrote it
       const long long id = (long long)r.y;
       if (id < 0) continue;
       const bool after = (r.x < prev_x) || (r.x == prev_x && id > prev_id);

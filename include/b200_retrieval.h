@@ -164,6 +164,21 @@ int b200_index_search_packed(b200_index_t* idx, const void* queries_dev, int q_d
 int b200_merge_hits(const void* hits_in, int nlists, int64_t nq_per_list, int k_in, int64_t q_first, int64_t nq,
                     int k_out, int64_t* ids_out, float* scores_out, int device, void* stream);
 
+/* The same exchange without the collective (no reference counterpart): every rank's receive buffer and flag array are
+ * mapped into every other rank (NVLink peer memory, e.g. torch symmetric memory).  b200_index_search_exchange runs the
+ * search and has its last kernels STORE this shard's hit records straight into slot `rank` of every rank's buffer
+ *   peer_hits[i] -> rank i's buffer for this search, laid out [world][nq][k] records; peer_flags[i] -> rank i's uint32[world]
+ * then publishes `epoch` into flag `rank` of every rank (release, system scope).  b200_merge_hits_wait is b200_merge_hits
+ * that first waits until all `nlists` flags of THIS rank have reached `epoch`.  Use two receive buffers alternately
+ * (epoch parity) and epochs that grow by one per search: a rank can then run at most one search ahead of the slowest,
+ * into the other buffer, and no further synchronisation is needed.  world <= 8. */
+int b200_index_search_exchange(b200_index_t* idx, const void* queries_dev, int q_dtype, int64_t nq, int k, int64_t id_base,
+                               void* const* peer_hits, void* const* peer_flags, int world, int rank, uint32_t epoch,
+                               void* stream);
+int b200_merge_hits_wait(const void* hits_local, const void* flags_local, uint32_t epoch, int nlists, int64_t nq_per_list,
+                         int k_in, int64_t q_first, int64_t nq, int k_out, int64_t* ids_out, float* scores_out, int device,
+                         void* stream);
+
 /* Multi-GPU candidate merge (no reference counterpart: the reference is single-process).  After an
  * all-gather of per-shard results laid out [nlists][nq][k_in], keep the best k_out per query under
  * the same (score desc, id asc) order.  All pointers are device pointers. */

@@ -26,6 +26,7 @@ def main():
     ap.add_argument("--queries", default="4096,128,1")
     ap.add_argument("--k", type=int, default=10)
     ap.add_argument("--iters", type=int, default=5)
+    ap.add_argument("--exchange", default="nccl,peer", help="comma list: nccl (all-gather of hit records) and/or peer (stores into NVLink peer memory)")
     a = ap.parse_args()
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -42,7 +43,7 @@ def main():
     for c0 in range(0, n, 1 << 20):
         m = min(1 << 20, n - c0)
         index.add(torch.randn((m, 384), generator=g, device="cuda").bfloat16().contiguous())
-    searcher = sh.ShardedSearch.over_index(index, r0)
+    searchers = {x: sh.ShardedSearch.over_index(index, r0, exchange=x) for x in a.exchange.split(",") if world > 1 or x == "nccl"}
     hbm, tf = 6555.2e9, 1388.2e12                     # MEASURED_PEAKS.json (copy bandwidth, sustained bf16)
     try:
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
@@ -52,7 +53,7 @@ def main():
     except Exception:  # noqa: BLE001
         pass
     gq = torch.Generator(device="cuda").manual_seed(2)
-    for nq in [int(x) for x in a.queries.split(",")]:
+    for nq, (xname, searcher) in [(int(x), it) for x in a.queries.split(",") for it in searchers.items()]:
         q = torch.randn((nq, 384), generator=gq, device="cuda").bfloat16().contiguous()
         for _ in range(3):
             searcher.search_replicated(q, a.k)
@@ -70,7 +71,7 @@ def main():
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         t_min = max(n * 768 / hbm, nq * n * 768.0 / tf) * 1e3      # per-rank roofline, ms
         if rank == 0:
-            print(json.dumps({"metric": "top-10 queries/s", "rows_total": a.rows_total, "rows_per_gpu": n, "n_gpus": world,
+            print(json.dumps({"metric": "top-10 queries/s", "exchange": xname, "rows_total": a.rows_total, "rows_per_gpu": n, "n_gpus": world,
                               "queries_per_batch": nq, "ms_per_batch": float(ms), "qps": nq / (float(ms) * 1e-3),
                               "roofline_ms_per_rank": t_min, "frac_of_roofline": t_min / float(ms),
                               "bound": "tensor" if nq > 212 else "hbm"}), flush=True)

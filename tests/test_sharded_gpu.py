@@ -45,8 +45,17 @@ def _worker(rank: int, world: int, port: int, ret):
         mine = slice(rank * 70, (rank + 1) * 70)
         ids, sc = ss.search_local_queries(q_all[mine].to(dev).contiguous(), 10)
         ok2 = torch.equal(ids, want_i[mine]) and torch.equal(sc.view(torch.int32), want_s[mine].view(torch.int32))
+        # the same two searches with the hit records stored into NVLink peer memory instead of all-gathered, several
+        # times in a row (the receive buffers alternate, flags only grow)
+        sp = sh.ShardedSearch.over_index(shard, r0, exchange="peer")
+        ok3 = True
+        for _rep in range(5):
+            ids, sc = sp.search_replicated(q_all.to(dev).contiguous(), 10)
+            ok3 = ok3 and torch.equal(ids, want_i) and torch.equal(sc.view(torch.int32), want_s.view(torch.int32))
+            ids, sc = sp.search_local_queries(q_all[mine].to(dev).contiguous(), 10)
+            ok3 = ok3 and torch.equal(ids, want_i[mine]) and torch.equal(sc.view(torch.int32), want_s[mine].view(torch.int32))
         torch.cuda.synchronize()
-        ret[rank] = (bool(ok1), bool(ok2), int(want_i[0, 0]), int(want_i[0, 1]))
+        ret[rank] = (bool(ok1), bool(ok2 and ok3), int(want_i[0, 0]), int(want_i[0, 1]))
     finally:
         dist.destroy_process_group()
 
