@@ -464,7 +464,9 @@ def run_b200(a) -> None:
             bs_nccl = sh.ShardedSearch.over_index(big, b0, exchange="nccl") if world > 1 and bs.exchange == "peer" else None
             rows_rank = len(big)
             s10 = {"rows_global": n_big, "rows_per_gpu": rows_rank, "algorithmic_bytes_per_pass_per_gpu": rows_rank * 768,
-                   "traffic": traffic_per_launch("sim_topk"),
+                   "traffic": {"single_tile_kernel_128_queries": traffic_per_launch("sim_topk_kernel<256, 20, 1>"),
+                               "cta_pair_kernel_4096_queries": traffic_per_launch("sim_topk_kernel<256, 16, 2>"),
+                               "note": "dram bytes per launch over ALL 10 M rows on one GPU (profiles/r02_ncu_search.md); algorithmic = 7.68e9"},
                    "exchange": bs.exchange,
                    "api": "ShardedSearch.search_replicated: b200_index_search_exchange (hit records stored into NVLink peer memory) -> "
                           "b200_merge_hits_wait" if bs.exchange == "peer" else

@@ -120,7 +120,7 @@ static const OptDef kOptDefs[OPT_COUNT] = {
     {"pdl", 0, 0, 1},           {"gemm_pair", 1, 0, 1},      {"gemm_ast", 1, 0, 1},   {"attention_tc", 1, 0, 1},
     {"att_exact_max", 0, 0, 1}, {"att_turns", 1, 0, 1},      {"att_poly", 1, 0, 4},   {"fuse_ln", 1, 0, 1},
     {"fuse_ffn", 1, 0, 1},      {"serpentine", 1, 0, 1},     {"sim_pair", 1, 0, 1},   {"sim_bound", 3, 0, 3},
-    {"sim_refresh_mask", 0, 0, 1023}, {"search_certify", 1, 0, 1},
+    {"sim_refresh_mask", 0, 0, 1023}, {"search_certify", 1, 0, 1}, {"sim_pair_kp", 0, 0, 20},
 };
 static std::atomic<int> g_opts[OPT_COUNT];
 static std::once_flag g_opts_once;
@@ -184,11 +184,12 @@ static constexpr int kMaxQueryChunk = 8192;
 // 16-bit score are closer than the rounding bound eps (~7e-4): on random 384-d rows that is a sum of KP - k order-
 // statistic spacings, so its probability falls like eps^(KP - k): measured 2.4e-4 per query at KP = 16, none in
 // 10^5 queries at KP = 20.  A single query tile (<= 128 queries, the HBM-bound regime) has the issue slots to spare
-// for 20; the CTA-pair kernel (tensor-bound, the drain is on its critical path) slows down by 4 - 19 % with 20, more
-// than the one exhaustive re-run per ~4000 queries costs it, and stays at 16.
+// for 20; the CTA-pair kernel (tensor-bound; the larger sets cost it one of its seven pipeline stages) slows down by
+// 5 % (10 M rows) to 27 % (1.25 M and fewer) with 20 -- more than the one exhaustive re-run per ~4000 queries costs it
+// on all but very large shards -- and stays at 16 below kPairKp20FromRows.
 static constexpr int kKpSmall = 20;
 static constexpr int kKpPair = 16;
-static constexpr int64_t kPairKp20BelowRows = 500000;
+static constexpr int64_t kPairKp20FromRows = 12000000;
 static constexpr int kMaxCandPerQuery = 8192;
 
 static int index_reserve_locked(b200_index* ix, int64_t cap, cudaStream_t st) {
@@ -266,7 +267,8 @@ static int launch_sim(b200_index* ix, int nq, int nqt, const CUtensorMap& map_q,
     // bit 0: the bucket bound (needs one bucket per kept candidate); bit 1: the single-CTA stand-in bound, which
     // only earns its atomics while buckets are still unreported, i.e. when the launch takes more than one wave
     const int m = opt(OPT_SIM_BOUND);
-    p.use_bound = (m & 1) && nsplit >= KP;
+    p.bkt_per_cta = nsplit >= KP ? 1 : (KP + nsplit - 1) / nsplit;
+    p.use_bound = (m & 1) && (int)tps >= p.bkt_per_cta;
     p.use_gthr = ((m >> 1) & 1) && ((long)nsplit * units > slots || !p.use_bound);
   }
   auto kern = sim_topk_kernel<BLOCK_N, KP, CG>;
@@ -348,8 +350,11 @@ static int search_chunk(b200_index* ix, const void* q_dev, int q_dtype, int nq, 
   // CTA pairs (two query tiles per cluster) for k <= 10 once there are at least two query tiles; an odd
   // tile count is padded with an empty tile.  Option sim_pair=0 forces single-CTA tiles (A/B timing).
   const bool pair = kp == kKpSmall && nqt >= 2 && opt(OPT_SIM_PAIR) != 0;
-  // small shards: a re-run's fixed cost outweighs the slower drain (measured cross-over near half a million rows)
-  if (pair && ix->count >= kPairKp20BelowRows) kp = kKpPair;
+  // 16 candidates in the CTA-pair kernel unless the shard is so large that one exhaustive re-run per ~4000 queries
+  // (0.03 ms + 0.155 ms per million rows) costs more than the 5 % the slower drain takes at that size
+  if (pair && ix->count < kPairKp20FromRows) kp = kKpPair;
+  if (pair && opt(OPT_SIM_PAIR_KP) == kKpPair) kp = kKpPair;      // A/B timing
+  if (pair && opt(OPT_SIM_PAIR_KP) == kKpSmall) kp = kKpSmall;
   if (pair) nqt = (nqt + 1) & ~1;
   const int nq_pad = nqt * SIM_BLOCK_M;
   B200_TRY(ix->q16.grow((size_t)nq_pad * ix->dpad * 2, 0, st));
@@ -1002,7 +1007,8 @@ int launch_sim_static(b200_index* ix, int nq, const CUtensorMap& map_q, uint64_t
   B200_TRY(make_tma_2d_bf16(&map_c, ix->search.p, (uint64_t)ix->count, (uint64_t)ix->dpad, BLOCK_N, SIM_BLOCK_K));
   SimParams p{};
   p.nq = nq; p.kc = kc; p.nstage = nstage; p.n_rows = n_rows; p.tiles_per_split = tps; p.nsplit = nsplit;
-  p.cand = cand; p.gbkt = gthr; p.use_bound = nsplit >= KP;
+  p.bkt_per_cta = nsplit >= KP ? 1 : (KP + nsplit - 1) / nsplit;
+  p.cand = cand; p.gbkt = gthr; p.use_bound = (int)tps >= p.bkt_per_cta;
   p.gthr = gthr + (size_t)kStaticMaxQueries * KP;
   p.refresh_mask = 0; p.use_gthr = 0; p.split_major = 0;
   auto kern = sim_topk_kernel<BLOCK_N, KP, 1>;

@@ -204,7 +204,9 @@ struct SimParams {
   uint64_t* cand;         // [nq][nsplit][KP] packed (score, row) keys, 0 = empty slot
   uint32_t* gbkt;         // [nq][KP] per-query, per-bucket best score seen by any CTA of the bucket
                           // (orderable bits, 0 = nothing yet), zeroed before the launch; see the drain
-  int use_bound;          // 1 when there are at least KP splits (one bucket per kept candidate)
+  int use_bound;          // 1: the bucket bound is on
+  int bkt_per_cta;        // buckets a CTA feeds: tile t of split s reports into bucket (s * bkt_per_cta + t % bkt_per_cta) % KP,
+                          // so that KP buckets exist (over disjoint rows) even when there are fewer than KP splits
   uint32_t* gthr;         // [nq] best "worst kept score" of any CTA whose set is full (orderable bits, 0 = none)
   uint32_t refresh_mask;  // the shared bounds are re-read every (refresh_mask + 1) tiles
   int use_gthr;
@@ -444,11 +446,15 @@ sim_topk_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant
     // applied non-strictly (rows EQUAL to it still pass, hence "just below"): ties at the boundary
     // must all survive so that the lower row can win in the merge, whichever slice it sits in.
     float thr_own = live ? -INFINITY : INFINITY;     // padded query rows never insert
-    float thr = thr_own, best_own = -INFINITY;
+    float thr = thr_own;
     const bool bound_on = live && p.use_bound;
     uint32_t* my_bkt = p.gbkt + (size_t)(live ? qg : 0) * KP;
     for (uint32_t t = 0; t < ntiles; ++t) {
       const uint32_t as = t & 1, aph = (t >> 1) & 1;
+      // the bucket this tile's rows report into, and the best score it is known to hold (a bucket's rows are disjoint
+      // from every other bucket's; its best row either stays in some CTA's set or is pushed out by KP better ones)
+      const int bkt = (int)(((uint32_t)split * (uint32_t)p.bkt_per_cta + t % (uint32_t)p.bkt_per_cta) % (uint32_t)KP);
+      uint32_t bkt_best = bound_on ? __ldcg(my_bkt + bkt) : 0xFFFFFFFFu;
       if (live && (t & p.refresh_mask) == 0) {
         uint32_t gb = 0xFFFFFFFFu;
         if (!bound_on) gb = 0;
@@ -517,9 +523,10 @@ sim_topk_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant
                     wpos = (int)(uint32_t)r;
                     thr = fmaxf(thr, thr_own);
                     if (p.use_gthr && thr_own > -INFINITY) atomicMax(p.gthr + qg, f32_orderable(thr_own));   // set is full
-                    if (s > best_own) {
-                      best_own = s;
-                      if (bound_on) atomicMax(my_bkt + (split % KP), f32_orderable(s));
+                    const uint32_t os = f32_orderable(s);
+                    if (os > bkt_best) {
+                      bkt_best = os;
+                      atomicMax(my_bkt + bkt, os);
                     }
                   }
                 }
