@@ -156,6 +156,7 @@ enum Option {
   OPT_SIM_REFRESH_MASK,   // the shared bounds are re-read every (mask + 1) tiles                     (default 0)
   OPT_SEARCH_CERTIFY,     // 0: skip the candidate-sufficiency certificate and its exhaustive re-run  (default 1)
   OPT_SIM_PAIR_KP,        // 16 / 20: candidates per query kept by the CTA-pair similarity kernel; 0 = by shard size (default 0)
+  OPT_SIM_NSPLIT,         // > 0: force the number of corpus slices of the similarity kernel (A/B timing)             (default 0)
   OPT_COUNT
 };
 int opt(Option o);

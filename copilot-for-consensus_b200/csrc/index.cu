@@ -120,7 +120,7 @@ static const OptDef kOptDefs[OPT_COUNT] = {
     {"pdl", 0, 0, 1},           {"gemm_pair", 1, 0, 1},      {"gemm_ast", 1, 0, 1},   {"attention_tc", 1, 0, 1},
     {"att_exact_max", 0, 0, 1}, {"att_turns", 1, 0, 1},      {"att_poly", 1, 0, 4},   {"fuse_ln", 1, 0, 1},
     {"fuse_ffn", 1, 0, 1},      {"serpentine", 1, 0, 1},     {"sim_pair", 1, 0, 1},   {"sim_bound", 3, 0, 3},
-    {"sim_refresh_mask", 0, 0, 1023}, {"search_certify", 1, 0, 1}, {"sim_pair_kp", 0, 0, 20},
+    {"sim_refresh_mask", 0, 0, 1023}, {"search_certify", 1, 0, 1}, {"sim_pair_kp", 0, 0, 20}, {"sim_nsplit", 0, 0, 4096},
 };
 static std::atomic<int> g_opts[OPT_COUNT];
 static std::once_flag g_opts_once;
@@ -244,8 +244,10 @@ static int launch_sim(b200_index* ix, int nq, int nqt, const CUtensorMap& map_q,
     const double cost = (double)waves * ((double)t + 2.0);
     if (cost < best_cost * 0.995) { best_cost = cost; best = ns; }
   }
-  const int nsplit = best;
+  int nsplit = best;
+  if (opt(OPT_SIM_NSPLIT) > 0) nsplit = std::min(max_split, opt(OPT_SIM_NSPLIT));     // A/B timing
   const uint32_t tps = (total_tiles + nsplit - 1) / nsplit;
+  nsplit = (int)((total_tiles + tps - 1) / tps);
 
   const size_t cand_n = (size_t)nqt * SIM_BLOCK_M * nsplit * KP;
   B200_TRY(ix->cand.grow(cand_n * 8, 0, st));
@@ -262,7 +264,7 @@ static int launch_sim(b200_index* ix, int nq, int nqt, const CUtensorMap& map_q,
   p.a_stream = a_stream;
   p.cand = ix->cand.as<uint64_t>(); p.gbkt = ix->gbkt.as<uint32_t>(); p.use_bound = nsplit >= KP;
   p.gthr = ix->gbkt.as<uint32_t>() + (size_t)nqt * SIM_BLOCK_M * KP;
-  p.refresh_mask = (uint32_t)opt(OPT_SIM_REFRESH_MASK); p.split_major = 0;
+  p.refresh_mask = (uint32_t)opt(OPT_SIM_REFRESH_MASK);
   {
     // bit 0: the bucket bound (needs one bucket per kept candidate); bit 1: the single-CTA stand-in bound, which
     // only earns its atomics while buckets are still unreported, i.e. when the launch takes more than one wave
@@ -288,8 +290,6 @@ static int launch_sim(b200_index* ix, int nq, int nqt, const CUtensorMap& map_q,
       attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
       cfg.attrs = attr; cfg.numAttrs = 1;
       B200_CUDA(cudaLaunchKernelEx(&cfg, kern, map_q, map_c, p));
-    } else if (p.split_major) {
-      kern<<<dim3(nsplit, nqt), SIM_THREADS, smem, st>>>(map_q, map_c, p);
     } else {
       kern<<<dim3(nqt, nsplit), SIM_THREADS, smem, st>>>(map_q, map_c, p);
     }
@@ -1010,7 +1010,7 @@ int launch_sim_static(b200_index* ix, int nq, const CUtensorMap& map_q, uint64_t
   p.bkt_per_cta = nsplit >= KP ? 1 : (KP + nsplit - 1) / nsplit;
   p.cand = cand; p.gbkt = gthr; p.use_bound = (int)tps >= p.bkt_per_cta;
   p.gthr = gthr + (size_t)kStaticMaxQueries * KP;
-  p.refresh_mask = 0; p.use_gthr = 0; p.split_major = 0;
+  p.refresh_mask = 0; p.use_gthr = 0;
   auto kern = sim_topk_kernel<BLOCK_N, KP, 1>;
   B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   kern<<<dim3(1, nsplit), SIM_THREADS, smem, st>>>(map_q, map_c, p);

@@ -210,7 +210,6 @@ struct SimParams {
   uint32_t* gthr;         // [nq] best "worst kept score" of any CTA whose set is full (orderable bits, 0 = none)
   uint32_t refresh_mask;  // the shared bounds are re-read every (refresh_mask + 1) tiles
   int use_gthr;
-  int split_major;        // 1: blockIdx.x = split, blockIdx.y = query tile (all splits of a tile run together)
 };
 
 // One search hit as a 16-byte record: x = orderable(score) << 32 (0 = no hit), y = global id (-1 = no hit).
@@ -307,8 +306,8 @@ sim_topk_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant
 
   const int warp = uniform_warp_idx();
   const int lane = threadIdx.x & 31;
-  const int qtile = (CG == 1 && p.split_major) ? blockIdx.y : blockIdx.x;   // CTA pair = query tiles (2i, 2i+1)
-  const int split = (CG == 1 && p.split_major) ? blockIdx.x : blockIdx.y;
+  const int qtile = blockIdx.x;                     // CTA pair = query tiles (2i, 2i+1); CTAs sharing a corpus slice run together
+  const int split = blockIdx.y;
   const int rank = (CG == 2) ? (int)cluster_ctarank() : 0;
   const bool leader = rank == 0;
 

@@ -116,3 +116,46 @@ def test_model_dir_refuses_other_module_stacks_and_architectures(tmp_path):
     with pytest.raises(ValueError, match="model_type 'mpnet'"):
         mio.load_model_dir(d)
     assert "all-mpnet-base-v2" not in mio.KNOWN_ARCHS and mio.KNOWN_ARCHS["bert-base-class"].hidden == 768
+
+
+def test_factory_with_the_reference_packages_installed_behaves_like_the_reference_factory():
+    """With copilot_config / copilot_vectorstore importable the drop-in factory validates the driver config through the
+    reference's own schema validator (adapter_factory.py:61-67) and then fails / succeeds exactly where the reference's
+    factory does; the store it builds IS a copilot_vectorstore.VectorStore.  Needs /root/reference (build container)."""
+    import subprocess
+    import sys
+
+    from conftest import ROOT
+
+    ref = "/root/reference/adapters"
+    if not os.path.isdir(ref):
+        pytest.skip("the reference tree is not on this machine")
+    code = r"""
+import importlib, sys
+from copilot_config.generated.adapters.vector_store import (AdapterConfig_VectorStore, DriverConfig_VectorStore_Inmemory,
+                                                            DriverConfig_VectorStore_Faiss)
+import copilot_vectorstore.factory as rf
+from copilot_vectorstore.interface import VectorStore
+vs = importlib.import_module("copilot-for-consensus_b200.vectorstore")
+def outcome(f, cfg):
+    try:
+        return ("ok", type(f(cfg)).__name__)
+    except Exception as e:
+        return (type(e).__name__, str(e))
+for vtype, drv in [("inmemory", object()), ("inmemory", DriverConfig_VectorStore_Faiss(dimension=8)), ("nope", None)]:
+    cfg = AdapterConfig_VectorStore(vector_store_type=vtype, driver=drv)
+    a, b = outcome(rf.create_vector_store, cfg), outcome(vs.create_vector_store, cfg)
+    assert a == b, (vtype, a, b)
+st = vs.create_vector_store(AdapterConfig_VectorStore(vector_store_type="inmemory", driver=DriverConfig_VectorStore_Inmemory()))
+assert isinstance(st, VectorStore) and type(st).__name__ == "B200VectorStore"
+# the faiss slot is only taken over on request, and only for a flat index without persistence
+fcfg = AdapterConfig_VectorStore(vector_store_type="faiss", driver=DriverConfig_VectorStore_Faiss(dimension=8, index_type="flat"))
+vs.factory.configure(serve_faiss_flat=True)
+st = vs.create_vector_store(fcfg)
+assert type(st).__name__ == "B200VectorStore" and st.metric == "l2" and st.dimension == 8
+vs.factory.configure(serve_faiss_flat=False)
+print("factory parity ok")
+"""
+    env = dict(os.environ, PYTHONPATH=os.pathsep.join([ref + "/copilot_config", ref + "/copilot_vectorstore", ROOT]))
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300, env=env, cwd="/tmp")
+    assert r.returncode == 0 and "factory parity ok" in r.stdout, r.stdout[-2000:] + r.stderr[-3000:]
