@@ -121,6 +121,7 @@ static const OptDef kOptDefs[OPT_COUNT] = {
     {"att_exact_max", 0, 0, 1}, {"att_turns", 1, 0, 1},      {"att_poly", 1, 0, 4},   {"fuse_ln", 1, 0, 1},
     {"fuse_ffn", 1, 0, 1},      {"serpentine", 1, 0, 1},     {"sim_pair", 1, 0, 1},   {"sim_bound", 3, 0, 3},
     {"sim_refresh_mask", 0, 0, 1023}, {"search_certify", 1, 0, 1}, {"sim_pair_kp", 0, 0, 20}, {"sim_nsplit", 0, 0, 4096},
+    {"search_screen", 1, 0, 1},
 };
 static std::atomic<int> g_opts[OPT_COUNT];
 static std::once_flag g_opts_once;
@@ -170,7 +171,7 @@ struct b200_index {
   // certificate state: persist[0] = rvmax (float bits), persist[2..3] / [4..5] = the two 64-bit counters
   // of b200_index_certificate_stats; cert = [fail_count][pad to 64 B][ticket nq][fail_idx nq] per search
   DevBuf persist, cert, exact_part;
-  int exact_per_sm[2] = {0, 0};   // resident CTAs per SM of exact_topk_kernel<0 / 1> at this index's dimension
+  int exact_per_sm[3] = {0, 0, 0};   // resident CTAs per SM of exact_topk_kernel<0,0 / 1,0 / 0,1> at this index's dimension
   StreamOrder order;
   std::mutex mu;
   size_t master_elt() const { return master_dtype == B200_INDEX_MASTER_BF16 ? 2 : 4; }
@@ -189,7 +190,7 @@ static constexpr int kMaxQueryChunk = 8192;
 // on all but very large shards -- and stays at 16 below kPairKp20FromRows.
 static constexpr int kKpSmall = 20;
 static constexpr int kKpPair = 16;
-static constexpr int64_t kPairKp20FromRows = 12000000;
+static constexpr int64_t kPairKp20FromRows = 6000000;
 static constexpr int kMaxCandPerQuery = 8192;
 
 static int index_reserve_locked(b200_index* ix, int64_t cap, cudaStream_t st) {
@@ -305,20 +306,23 @@ static int launch_sim(b200_index* ix, int nq, int nqt, const CUtensorMap& map_q,
 static float certificate_slop(int d) { return (float)d * 1.1920929e-7f + (float)(d / 32 + 16) * 1.1920929e-7f + 1e-6f; }
 
 // exact_topk_kernel over the fail list of the K9 launch just issued (or, with fail == nullptr, over all nq queries)
-template <int METRIC_L2>
+template <int METRIC_L2, int SCREEN = 0>
 static int launch_exact(b200_index* ix, const uint32_t* fail_count, const int32_t* fail_idx, uint32_t* ticket, int nq,
                         const float* q_f32, int k, int64_t id_base, int64_t* ids_dev, float* sc_dev, cudaStream_t st,
-                        uint64_t* part = nullptr, int grid = 0, HitSink packed_dev = HitSink{}) {
-  const size_t smem = (size_t)EXACT_MERGE * 8 + (size_t)ix->dim * 4;
-  auto kern = exact_topk_kernel<METRIC_L2>;
+                        uint64_t* part = nullptr, int grid = 0, HitSink packed_dev = HitSink{},
+                        uint32_t* fail2_count = nullptr, int32_t* fail2_idx = nullptr) {
+  // shared memory: room to stage one 64-key list per CTA (one CTA per SM: the kernel is register-bound to that anyway)
+  const int stage_keys = std::max(1024, ix->num_sms * EXACT_KEEP);
+  const size_t smem = (size_t)stage_keys * 8 + (size_t)ix->dim * 4;
+  auto kern = exact_topk_kernel<METRIC_L2, SCREEN>;
   B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   // The kernel's CTAs wait for one another (a query's list buffer is reused two queries later), so every CTA of the
   // grid must be able to be resident at once: never launch more than the occupancy calculator allows.
-  int& per_sm = ix->exact_per_sm[METRIC_L2];
+  int& per_sm = ix->exact_per_sm[METRIC_L2 + 2 * SCREEN];
   if (per_sm == 0) B200_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, EXACT_THREADS, smem));
   if (per_sm < 1) B200_FAIL(B200_ERR_UNSUPPORTED, "the exhaustive kernel does not fit on an SM (dimension %d)", ix->dim);
   if (!part) {   // the index's own scratch (grown on first use); the no-allocation entry point passes its own
-    grid = std::min(per_sm, 2) * ix->num_sms;
+    grid = ix->num_sms;
     B200_TRY(ix->exact_part.grow((size_t)2 * grid * EXACT_KEEP * 8, 0, st));
     part = ix->exact_part.as<uint64_t>();
   }
@@ -327,9 +331,12 @@ static int launch_exact(b200_index* ix, const uint32_t* fail_count, const int32_
   e.fail_count = fail_count; e.fail_idx = fail_idx; e.nq = nq; e.q_f32 = q_f32;
   e.master = ix->master.p; e.master_is_bf16 = ix->master_dtype == B200_INDEX_MASTER_BF16;
   e.n_rows = (uint32_t)ix->count; e.d = ix->dim; e.k = k; e.id_base = id_base;
-  e.part = part; e.ticket = ticket; e.out_ids = ids_dev; e.out_scores = sc_dev; e.out_packed = packed_dev;
+  e.part = part; e.stage_keys = stage_keys; e.ticket = ticket; e.out_ids = ids_dev; e.out_scores = sc_dev; e.out_packed = packed_dev;
+  e.fail2_count = fail2_count; e.fail2_idx = fail2_idx;
+  // screen and canonical score are two fp32 evaluations of the same number: apart by at most a few d * 2^-24
+  e.screen_margin = 1e-4f + (float)ix->dim * 4.8e-7f;
   {
-    B200_PROF(METRIC_L2 ? "exact_l2" : "exact_topk", 0.0, 0.0, st);
+    B200_PROF(METRIC_L2 ? "exact_l2" : (SCREEN ? "exact_topk" : "exact_full"), 0.0, 0.0, st);
     kern<<<grid, EXACT_THREADS, smem, st>>>(e);
   }
   B200_CUDA(cudaGetLastError());
@@ -351,7 +358,7 @@ static int search_chunk(b200_index* ix, const void* q_dev, int q_dtype, int nq, 
   // tile count is padded with an empty tile.  Option sim_pair=0 forces single-CTA tiles (A/B timing).
   const bool pair = kp == kKpSmall && nqt >= 2 && opt(OPT_SIM_PAIR) != 0;
   // 16 candidates in the CTA-pair kernel unless the shard is so large that one exhaustive re-run per ~4000 queries
-  // (0.03 ms + 0.155 ms per million rows) costs more than the 5 % the slower drain takes at that size
+  // (0.03 ms + ~0.17 ms per million rows) costs more than the 5 - 10 % the slower drain takes at that size
   if (pair && ix->count < kPairKp20FromRows) kp = kKpPair;
   if (pair && opt(OPT_SIM_PAIR_KP) == kKpPair) kp = kKpPair;      // A/B timing
   if (pair && opt(OPT_SIM_PAIR_KP) == kKpSmall) kp = kKpSmall;
@@ -361,10 +368,11 @@ static int search_chunk(b200_index* ix, const void* q_dev, int q_dtype, int nq, 
   B200_TRY(ix->q_f32.grow((size_t)nq * ix->dim * 4, 0, st));
   B200_TRY(ix->qmeta.grow((size_t)nq * 8, 0, st));
   const bool certify = opt(OPT_SEARCH_CERTIFY) != 0;
-  const size_t cert_bytes = 64 + (size_t)nq * 8;
+  // cert = [fail count, second fail count, pad to 64 B][tickets nq][tickets of the second pass nq][fail list nq][second fail list nq]
+  const size_t cert_bytes = 64 + (size_t)nq * 16;
   if (certify) {
     B200_TRY(ix->cert.grow(cert_bytes, 0, st));
-    B200_CUDA(cudaMemsetAsync(ix->cert.p, 0, 64 + (size_t)nq * 4, st));   // fail_count and the tickets
+    B200_CUDA(cudaMemsetAsync(ix->cert.p, 0, 64 + (size_t)nq * 8, st));   // the counts and the tickets
   }
   const int wpb = 8;
   if (q_dtype == 0)
@@ -398,7 +406,10 @@ static int search_chunk(b200_index* ix, const void* q_dev, int q_dtype, int nq, 
   m.out_ids = ids_dev; m.out_scores = sc_dev; m.out_packed = packed_dev;
   uint32_t* fail_count = certify ? ix->cert.as<uint32_t>() : nullptr;
   uint32_t* ticket = certify ? ix->cert.as<uint32_t>() + 16 : nullptr;
-  int32_t* fail_idx = certify ? reinterpret_cast<int32_t*>(ticket + nq) : nullptr;
+  uint32_t* ticket2 = certify ? ticket + nq : nullptr;
+  int32_t* fail_idx = certify ? reinterpret_cast<int32_t*>(ticket + 2 * (size_t)nq) : nullptr;
+  int32_t* fail2_idx = certify ? fail_idx + nq : nullptr;
+  uint32_t* fail2_count = certify ? ix->cert.as<uint32_t>() + 1 : nullptr;
   m.qmeta = ix->qmeta.as<float2>(); m.rvmax = ix->rvmax(); m.slop = certificate_slop(ix->dpad);
   m.fail_count = fail_count; m.fail_idx = fail_idx; m.stats = ix->stats();
   const size_t msmem = (size_t)pow2 * 8 + (size_t)((ix->dim + 1) & ~1) * 4 + 64 * 8;
@@ -408,10 +419,21 @@ static int search_chunk(b200_index* ix, const void* q_dev, int q_dtype, int nq, 
     merge_rescore_kernel<<<nq, 256, msmem, st>>>(m);
   }
   B200_CUDA(cudaGetLastError());
-  // queries the certificate turned down are redone exactly; the kernel returns at once when there are none
-  if (certify)
-    B200_TRY(launch_exact<0>(ix, fail_count, fail_idx, ticket, nq, ix->q_f32.as<float>(), k, id_base, ids_dev, sc_dev, st,
-                             nullptr, 0, packed_dev));
+  // Queries the certificate turned down are redone against every row; the kernels return at once when there are none.
+  // First the screened pass (one cheap pass over the rows, canonical scores for the best 64 only), then the full one
+  // for what the screened pass could not settle (large clusters of near-duplicates).
+  if (certify) {
+    const bool screen = (ix->dim & 7) == 0 && opt(OPT_SEARCH_SCREEN) != 0;
+    if (screen) {
+      B200_TRY((launch_exact<0, 1>(ix, fail_count, fail_idx, ticket, nq, ix->q_f32.as<float>(), k, id_base, ids_dev, sc_dev, st,
+                                   nullptr, 0, packed_dev, fail2_count, fail2_idx)));
+      B200_TRY((launch_exact<0, 0>(ix, fail2_count, fail2_idx, ticket2, nq, ix->q_f32.as<float>(), k, id_base, ids_dev, sc_dev, st,
+                                   nullptr, 0, packed_dev)));
+    } else {
+      B200_TRY((launch_exact<0, 0>(ix, fail_count, fail_idx, ticket, nq, ix->q_f32.as<float>(), k, id_base, ids_dev, sc_dev, st,
+                                   nullptr, 0, packed_dev)));
+    }
+  }
   return B200_OK;
 }
 
@@ -887,8 +909,8 @@ int b200_index_search_l2(b200_index_t* ix, const void* queries, int q_dtype, int
       const int n = (int)std::min<int64_t>(kMaxQueryChunk, nq - q0);
       B200_TRY(ix->cert.grow(64 + (size_t)n * 8, 0, st));
       B200_CUDA(cudaMemsetAsync(ix->cert.p, 0, 64 + (size_t)n * 4, st));
-      B200_TRY(launch_exact<1>(ix, nullptr, nullptr, ix->cert.as<uint32_t>() + 16, n, q_dev + (size_t)q0 * ix->dim, k, id_base,
-                               d_ids + q0 * k, d_sc + q0 * k, st));
+      B200_TRY((launch_exact<1, 0>(ix, nullptr, nullptr, ix->cert.as<uint32_t>() + 16, n, q_dev + (size_t)q0 * ix->dim, k, id_base,
+                               d_ids + q0 * k, d_sc + q0 * k, st)));
     }
   }
   if (!out_on_device) {
@@ -979,7 +1001,7 @@ int static_scratch_for_current_device(int device, unsigned char** out) {
     B200_CUDA(cudaFuncGetAttributes(&fa, prep_queries_kernel<float>));
     B200_CUDA(cudaFuncGetAttributes(&fa, prep_queries_kernel<__nv_bfloat16>));
     B200_CUDA(cudaFuncGetAttributes(&fa, merge_rescore_kernel));
-    B200_CUDA(cudaFuncGetAttributes(&fa, exact_topk_kernel<0>));
+    B200_CUDA(cudaFuncGetAttributes(&fa, exact_topk_kernel<0, 0>));
     g_static_ptr[device] = static_cast<unsigned char*>(p);
   }
   *out = g_static_ptr[device];

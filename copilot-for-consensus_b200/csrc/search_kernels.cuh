@@ -716,7 +716,6 @@ __global__ void __launch_bounds__(256) merge_rescore_kernel(const MergeParams p)
 // ---------------------------------------------------------------------------------------------
 constexpr int EXACT_THREADS = 512;
 constexpr int EXACT_KEEP = 64;
-constexpr int EXACT_MERGE = 4096;
 
 struct ExactParams {
   const uint32_t* fail_count;   // nullptr: run all nq queries (query j = j)
@@ -728,6 +727,10 @@ struct ExactParams {
   uint32_t n_rows;
   int d, k;
   int64_t id_base;
+  uint32_t* fail2_count;        // SCREEN only: queries the screened pass could not settle (for the unscreened re-run)
+  int32_t* fail2_idx;
+  float screen_margin;
+  int stage_keys;               // keys of shared memory for staging the per-CTA lists (>= 1024, normally gridDim.x * 64)
   uint64_t* part;               // [2][gridDim.x][EXACT_KEEP] scratch, alternating between consecutive queries
   uint32_t* ticket;             // [nq] zeroed before the launch; gridDim.x + 1 = that query's result is written
   int64_t* out_ids;
@@ -792,6 +795,47 @@ B200_DEVINL float fold_partials8(float (&a)[8]) {
   a[0] = __fadd_rn(a[0], a[2]);
   a[1] = __fadd_rn(a[1], a[3]);
   return __fadd_rn(a[0], a[1]);
+}
+
+// Cosine screen for the exhaustive kernel: one pass, one division per ROW -- q_hat . v / (|v| + 1e-8) in ordinary fp32
+// (any summation order), within a few 1e-6 of the canonical score (which costs two passes and one IEEE division per
+// ELEMENT: three quarters of the kernel's time).  Same lane layout as canon_rows8; all four lanes of a row return its value.
+template <typename TV>
+B200_DEVINL float screen_rows8(const float* __restrict__ qh, const TV* __restrict__ rows, int d, int lane, int n_valid) {
+  using Raw = typename Raw8<TV>::type;
+  constexpr int U = Raw8<TV>::kInFlight;
+  const int r = lane >> 2, m = lane & 3;
+  const bool on = r < n_valid;
+  const TV* v = rows + (size_t)r * d;
+  const int nch = d >> 3;
+  float ss = 0.f, dot = 0.f;
+  for (int c0 = m; c0 < nch; c0 += 4 * U) {
+    Raw raw[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u)
+      if (on && c0 + 4 * u < nch) load8_raw(v + 8 * (c0 + 4 * u), raw[u]);
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int c = c0 + 4 * u;
+      if (on && c < nch) {
+        float x[8];
+        unpack8(raw[u], x);
+        const float4 q0 = *reinterpret_cast<const float4*>(qh + 8 * c);
+        const float4 q1 = *reinterpret_cast<const float4*>(qh + 8 * c + 4);
+        const float qv[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
+#pragma unroll
+        for (int t = 0; t < 8; ++t) {
+          ss = fmaf(x[t], x[t], ss);
+          dot = fmaf(qv[t], x[t], dot);
+        }
+      }
+    }
+  }
+  ss += __shfl_xor_sync(0xffffffffu, ss, 1);
+  dot += __shfl_xor_sync(0xffffffffu, dot, 1);
+  ss += __shfl_xor_sync(0xffffffffu, ss, 2);
+  dot += __shfl_xor_sync(0xffffffffu, dot, 2);
+  return on ? dot / (sqrtf(ss) + 1e-8f) : -INFINITY;
 }
 
 // Eight consecutive rows per warp with 16-byte loads, bit-identical to canon_score / canon_l2 per row.
@@ -867,14 +911,43 @@ B200_DEVINL uint64_t shfl_xor_u64(uint64_t v, int o) {
   return ((uint64_t)hi << 32) | lo;
 }
 
-template <int METRIC_L2>
+// max of a 64-bit key over the warp: the high words first, then the low words of the lanes that hold the maximum
+B200_DEVINL uint64_t warp_max_u64(uint64_t v) {
+  const uint32_t hi = (uint32_t)(v >> 32);
+  const uint32_t mhi = __reduce_max_sync(0xffffffffu, hi);
+  const uint32_t mlo = __reduce_max_sync(0xffffffffu, hi == mhi ? (uint32_t)v : 0u);
+  return ((uint64_t)mhi << 32) | mlo;
+}
+
+// One warp merges up to 32 sorted lists (better first, 0 = end), one per lane, into out[0 .. kk).  Keys are unique
+// across the lists, so exactly one lane owns each winner and steps its cursor.  `len` = 0: this lane has no list.
+__device__ __noinline__ void warp_merge_heads(const uint64_t* lst, int len, int kk, uint64_t* out, int lane) {
+  int pos = 0;
+  uint64_t head = len > 0 ? lst[0] : 0ull;
+  for (int t = 0; t < kk; ++t) {
+    const uint64_t wbest = warp_max_u64(head);
+    if (lane == 0) out[t] = wbest;
+    if (wbest != 0 && head == wbest) {
+      ++pos;
+      head = pos < len ? lst[pos] : 0ull;
+    }
+  }
+}
+
+// SCREEN (cosine only, d % 8 == 0): rank every row by the screen value instead, then compute the canonical score of the
+// best 64 only and check that it settles the top-k: the 64th screen value must lie more than `screen_margin` below the
+// k-th canonical score (no row outside the 64 can then reach it).  Queries for which it does not -- more than 64 - k
+// rows within the margin of the k-th, i.e. a large cluster of near-duplicates -- are appended to a second list and
+// re-run by the unscreened kernel.
+template <int METRIC_L2, int SCREEN>
 __global__ void __launch_bounds__(EXACT_THREADS, 1) exact_topk_kernel(const ExactParams p) {
   extern __shared__ uint8_t smem_raw[];
-  uint64_t* mkeys = reinterpret_cast<uint64_t*>(smem_raw);                  // [EXACT_MERGE]
-  float* qh = reinterpret_cast<float*>(mkeys + EXACT_MERGE);                // [d]
+  uint64_t* mkeys = reinterpret_cast<uint64_t*>(smem_raw);                  // [p.stage_keys]
+  float* qh = reinterpret_cast<float*>(mkeys + p.stage_keys);               // [d]
   __shared__ float s_den;
   __shared__ uint32_t s_last;
-  __shared__ uint64_t s_merge[EXACT_KEEP];
+  __shared__ uint64_t s_carry[2][EXACT_KEEP];
+  __shared__ uint64_t s_wout[16][EXACT_KEEP];   // EXACT_THREADS / 32 warps
   const int nfail = p.fail_count ? (int)min(__ldcg(p.fail_count), (uint32_t)p.nq) : p.nq;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
   for (int j = 0; j < nfail; ++j) {
@@ -899,7 +972,11 @@ __global__ void __launch_bounds__(EXACT_THREADS, 1) exact_topk_kernel(const Exac
       const uint32_t row0 = grp * 8;
       const int n_valid = (int)min(8u, p.n_rows - row0);
       float mine = 0.f;                       // lanes 4r .. 4r + 3: the score of row row0 + r
-      if (vec) {
+      if (SCREEN) {
+        mine = p.master_is_bf16
+                   ? screen_rows8(qh, reinterpret_cast<const __nv_bfloat16*>(p.master) + (size_t)row0 * p.d, p.d, lane, n_valid)
+                   : screen_rows8(qh, reinterpret_cast<const float*>(p.master) + (size_t)row0 * p.d, p.d, lane, n_valid);
+      } else if (vec) {
         mine = p.master_is_bf16
                    ? canon_rows8<METRIC_L2>(qh, reinterpret_cast<const __nv_bfloat16*>(p.master) + (size_t)row0 * p.d, p.d, lane, n_valid)
                    : canon_rows8<METRIC_L2>(qh, reinterpret_cast<const float*>(p.master) + (size_t)row0 * p.d, p.d, lane, n_valid);
@@ -952,61 +1029,69 @@ __global__ void __launch_bounds__(EXACT_THREADS, 1) exact_topk_kernel(const Exac
     __syncthreads();
     if (s_last) {
       __threadfence();
-      // Fold the per-CTA lists.  Each is sorted (better first) and only its first kk = min(k, 64) entries can reach
-      // the result, so up to 255 lists at a time are staged in shared memory and ONE warp merges them by their heads:
-      // every lane keeps the cursors of eight lists, a round is a warp arg-max and one cursor step (~150 clocks).
-      // The carry (best kk so far) is list 0 of the next batch.  (Sorting the gridDim.x * 64 keys with the bitonic
+      // Fold the per-CTA lists.  Each is sorted (better first) and only its first kk entries can reach the result.
+      // They are staged in shared memory (normally all at once); every warp then merges 32 of them by their heads,
+      // one list per lane (a round is a warp arg-max and one cursor step, ~100 clocks), and warp 0 merges the warps'
+      // outputs with the carry of the previous round the same way.  (Sorting the gridDim.x * 64 keys with the bitonic
       // network cost 0.2 ms per query -- more than streaming a million rows.)
-      const int kk = min(p.k, EXACT_KEEP);
-      const int per_round = min(EXACT_MERGE / kk - 1, 255);
-      for (int i = threadIdx.x; i < kk; i += blockDim.x) mkeys[i] = 0;
+      const int kk = SCREEN ? EXACT_KEEP : min(p.k, EXACT_KEEP);
+      const int per_round = min(p.stage_keys / kk, 32 * nwarp);
+      int cur = 0;
+      for (int i = threadIdx.x; i < kk; i += blockDim.x) s_carry[0][i] = 0;
       for (uint32_t c0 = 0; c0 < gridDim.x; c0 += per_round) {
         const int nl = (int)min((uint32_t)per_round, gridDim.x - c0);
         for (int i = threadIdx.x; i < nl * kk; i += blockDim.x) {
           const int l = i / kk, e = i - l * kk;
-          mkeys[kk + i] = __ldcg(part + (size_t)(c0 + l) * EXACT_KEEP + e);
+          mkeys[i] = __ldcg(part + (size_t)(c0 + l) * EXACT_KEEP + e);
         }
         __syncthreads();
-        if (warp == 0) {
-          uint64_t head[8];
-          int pos[8];
-#pragma unroll
-          for (int jj = 0; jj < 8; ++jj) {
-            const int l = lane + 32 * jj;                       // list 0 = the carry
-            pos[jj] = 0;
-            head[jj] = l <= nl ? mkeys[l * kk] : 0ull;
-          }
-          for (int t = 0; t < kk; ++t) {
-            uint64_t best = head[0];
-            int bj = 0;
-#pragma unroll
-            for (int jj = 1; jj < 8; ++jj)
-              if (head[jj] > best) { best = head[jj]; bj = jj; }
-            uint64_t wbest = best;
-#pragma unroll
-            for (int o = 16; o > 0; o >>= 1) {
-              const uint64_t other = shfl_xor_u64(wbest, o);
-              wbest = other > wbest ? other : wbest;
-            }
-            if (lane == 0) s_merge[t] = wbest;
-            if (wbest != 0 && best == wbest) {                  // keys are unique: exactly one lane owns the winner
-#pragma unroll
-              for (int jj = 0; jj < 8; ++jj) {
-                if (jj == bj) {
-                  ++pos[jj];
-                  head[jj] = pos[jj] < kk ? mkeys[(lane + 32 * jj) * kk + pos[jj]] : 0ull;
-                }
-              }
-            }
-          }
+        const int nw = (nl + 31) >> 5;
+        if (warp < nw) {
+          const int l = warp * 32 + lane;
+          warp_merge_heads(mkeys + (size_t)l * kk, l < nl ? kk : 0, kk, s_wout[warp], lane);
         }
         __syncthreads();
-        for (int i = threadIdx.x; i < kk; i += blockDim.x) mkeys[i] = s_merge[i];
+        if (warp == 0)
+          warp_merge_heads(lane == 0 ? s_carry[cur] : s_wout[(lane - 1) & 15], lane <= nw ? kk : 0, kk, s_carry[cur ^ 1], lane);
+        cur ^= 1;
         __syncthreads();
       }
-      for (int t = threadIdx.x; t < p.k; t += blockDim.x)
-        write_hit(p.out_ids, p.out_scores, p.out_packed, (size_t)q * p.k + t, t < kk ? mkeys[t] : 0ull, p.id_base,
-                  METRIC_L2 != 0);
+      for (int i = threadIdx.x; i < kk; i += blockDim.x) mkeys[i] = s_carry[cur][i];
+      __syncthreads();
+      bool settled = true;
+      if (SCREEN) {
+        // canonical scores of the 64 best rows by screen value; mkeys[0 .. 64) holds them in screen order
+        __shared__ uint64_t s_exact[EXACT_KEEP];
+        for (int c = warp; c < EXACT_KEEP; c += nwarp) {
+          const uint64_t key = mkeys[c];
+          uint64_t ek = 0;
+          if (key) {
+            const uint32_t id = ~(uint32_t)(key & 0xFFFFFFFFu);
+            const float sc = p.master_is_bf16
+                                 ? canon_score(qh, reinterpret_cast<const __nv_bfloat16*>(p.master) + (size_t)id * p.d, p.d, lane)
+                                 : canon_score(qh, reinterpret_cast<const float*>(p.master) + (size_t)id * p.d, p.d, lane);
+            ek = pack_key(sc, id);
+          }
+          if (lane == 0) s_exact[c] = ek;
+        }
+        __syncthreads();
+        const uint64_t last_screen = mkeys[EXACT_KEEP - 1];        // 0: fewer than 64 rows exist, all of them are in
+        bitonic_sort_desc(s_exact, EXACT_KEEP);
+        const uint64_t kth = s_exact[min(p.k, EXACT_KEEP) - 1];
+        if (last_screen != 0 && kth != 0) {
+          const float e_k = orderable_f32((uint32_t)(kth >> 32));
+          const float c_last = orderable_f32((uint32_t)(last_screen >> 32));
+          settled = (e_k - c_last) > p.screen_margin;
+        }
+        for (int i = threadIdx.x; i < EXACT_KEEP; i += blockDim.x) mkeys[i] = s_exact[i];
+        __syncthreads();
+        if (!settled && threadIdx.x == 0) p.fail2_idx[atomicAdd(p.fail2_count, 1u)] = q;
+      }
+      if (settled) {
+        for (int t = threadIdx.x; t < p.k; t += blockDim.x)
+          write_hit(p.out_ids, p.out_scores, p.out_packed, (size_t)q * p.k + t, t < min(p.k, EXACT_KEEP) ? mkeys[t] : 0ull,
+                    p.id_base, METRIC_L2 != 0);
+      }
       __syncthreads();
       if (threadIdx.x == 0) {
         __threadfence();

@@ -56,6 +56,61 @@ def test_near_duplicate_rows_are_exact(vs, k, n_dup, spread):
     ix.close()
 
 
+@pytest.mark.parametrize("screen", [1, 0])
+@pytest.mark.parametrize("k", [10, 48])
+def test_near_duplicates_packed_into_few_blocks(vs, k, screen):
+    """The exhaustive kernels merge one sorted candidate list per CTA: when several of the true top-k sit in
+    the rows of ONE CTA (runs of consecutive near-duplicates, at every position of the grid), every entry of
+    that list has to come through, not only its head.  Both passes: screened + full (search_screen=1) and
+    full alone (search_screen=0)."""
+    d, n_bg = 384, 60000
+    rng = np.random.default_rng(100 + k)
+    rows = rng.standard_normal((n_bg, d)).astype(np.float32)
+    dup = _near_duplicates(96, d, 11, 3e-5)
+    # runs of 3..9 consecutive rows scattered over the corpus: 96 rows in 16 runs
+    starts = np.sort(rng.choice(n_bg // 16 - 1, 16, replace=False)) * 16
+    at, pos = 0, []
+    for i, s0 in enumerate(starts):
+        n = 3 + (i % 7)
+        n = min(n, 96 - at)
+        pos.extend(range(int(s0), int(s0) + n)); at += n
+    pos.extend(range(n_bg - (96 - at), n_bg))            # whatever is left goes to the last rows
+    pos = np.array(pos[:96])
+    rows[pos] = dup
+    qs = np.concatenate([dup[:4] * 0.3, rng.standard_normal((1, d)).astype(np.float32)])
+    ix = vs.B200Index(d, device="cuda:0", master_dtype="float32")
+    ix.add(rows)
+    nat = pkg("_native")
+    with nat.options(search_screen=screen):
+        ids, sc = ix.search(qs, k)
+    oi, os_ = so.topk_canonical(qs, rows, k)
+    np.testing.assert_array_equal(ids, oi)
+    np.testing.assert_array_equal(_bits(sc), _bits(os_))
+    checked, redone = ix.certificate_stats()
+    assert checked == len(qs) and redone >= 4, (checked, redone)
+    ix.close()
+
+
+def test_screened_pass_settles_small_clusters(vs):
+    """A cluster smaller than 64 - k leaves the 64th screen value far below the k-th score: the screened pass
+    alone must give the oracle's answer (bit for bit), also with a bf16 master copy."""
+    d, n_bg, k = 384, 50000, 10
+    rng = np.random.default_rng(5)
+    rows = rng.standard_normal((n_bg, d)).astype(np.float32)
+    dup = _near_duplicates(30, d, 3, 2e-5)
+    rows[np.sort(rng.choice(n_bg, 30, replace=False))] = dup
+    rows = torch.from_numpy(rows).bfloat16().float().numpy()           # exactly representable in both master types
+    qs = np.concatenate([dup[:5] * 2.0, rng.standard_normal((3, d)).astype(np.float32)])
+    oi, os_ = so.topk_canonical(qs, rows, k)
+    for master in ("float32", "bfloat16"):
+        ix = vs.B200Index(d, device="cuda:0", master_dtype=master)
+        ix.add(rows)
+        ids, sc = ix.search(qs, k)
+        np.testing.assert_array_equal(ids, oi)
+        np.testing.assert_array_equal(_bits(sc), _bits(os_))
+        ix.close()
+
+
 def test_exact_duplicates_and_zero_rows(vs):
     """All-equal scores (every row identical; zero rows score 0 against everything): ties resolve to the lower row."""
     d = 384
