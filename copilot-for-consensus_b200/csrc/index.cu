@@ -185,12 +185,14 @@ static constexpr int kMaxQueryChunk = 8192;
 // 16-bit score are closer than the rounding bound eps (~7e-4): on random 384-d rows that is a sum of KP - k order-
 // statistic spacings, so its probability falls like eps^(KP - k): measured 2.4e-4 per query at KP = 16, none in
 // 10^5 queries at KP = 20.  A single query tile (<= 128 queries, the HBM-bound regime) has the issue slots to spare
-// for 20; the CTA-pair kernel (tensor-bound; the larger sets cost it one of its seven pipeline stages) slows down by
-// 5 % (10 M rows) to 27 % (1.25 M and fewer) with 20 -- more than the one exhaustive re-run per ~4000 queries costs it
-// on all but very large shards -- and stays at 16 below kPairKp20FromRows.
+// for 20; the CTA-pair kernel (tensor-bound; the larger sets cost it one of its seven pipeline stages) slows down with
+// 20 by 27 % at 1.25 M rows, 9 % at 5 M, 0 - 4 % at 10 - 25 M, 6 % at 50 M (4096 queries), while a re-run of a failing
+// query by the screened exhaustive pass costs 0.03 ms + 0.17 - 0.23 ms per million rows -- and the failure rate itself
+// grows with the shard (neighbours crowd together).  At 50 M rows one re-run per 4096 queries (11.6 ms) already costs
+// more than the slower drain (7.4 ms); below ~25 M it does not.  So 16 below kPairKp20FromRows.
 static constexpr int kKpSmall = 20;
 static constexpr int kKpPair = 16;
-static constexpr int64_t kPairKp20FromRows = 6000000;
+static constexpr int64_t kPairKp20FromRows = 32000000;
 static constexpr int kMaxCandPerQuery = 8192;
 
 static int index_reserve_locked(b200_index* ix, int64_t cap, cudaStream_t st) {
@@ -357,8 +359,8 @@ static int search_chunk(b200_index* ix, const void* q_dev, int q_dtype, int nq, 
   // CTA pairs (two query tiles per cluster) for k <= 10 once there are at least two query tiles; an odd
   // tile count is padded with an empty tile.  Option sim_pair=0 forces single-CTA tiles (A/B timing).
   const bool pair = kp == kKpSmall && nqt >= 2 && opt(OPT_SIM_PAIR) != 0;
-  // 16 candidates in the CTA-pair kernel unless the shard is so large that one exhaustive re-run per ~4000 queries
-  // (0.03 ms + ~0.17 ms per million rows) costs more than the 5 - 10 % the slower drain takes at that size
+  // 16 candidates in the CTA-pair kernel unless the shard is so large that the exhaustive re-runs cost more than the
+  // slower drain (see kPairKp20FromRows)
   if (pair && ix->count < kPairKp20FromRows) kp = kKpPair;
   if (pair && opt(OPT_SIM_PAIR_KP) == kKpPair) kp = kKpPair;      // A/B timing
   if (pair && opt(OPT_SIM_PAIR_KP) == kKpSmall) kp = kKpSmall;

@@ -110,10 +110,12 @@ int b200_index_get_rows(b200_index_t* idx, const int64_t* rows_host, int64_t n, 
  * candidates has a 16-bit score <= A (the KP-th best), its exact score can exceed that by at most
  * eps = r_v + r_q (1 + r_v) + slop (r_v: largest rounding distance of any stored row, tracked at insert;
  * r_q: this query's rounding distance; slop: fp32 evaluation error), and the k-th exact score must lie strictly
- * above A + eps.  A query that fails the test -- near-duplicate rows, ties -- is re-scored against every row by
- * a second kernel in the same call (no host round trip: the kernel is always launched and returns at once when
- * nothing failed).  So the ids, their order and the fp32 score bits are those of the exhaustive computation,
- * always; the cost of an uncertified query is one pass over the master copy. */
+ * above A + eps.  A query that fails the test -- near-duplicate rows, ties -- is re-scored against every row in
+ * the same call (no host round trip: the kernels are always launched and return at once when nothing failed):
+ * first by a screened pass (one cheap fp32 score per row, the reference's arithmetic for the best 64 rows, final
+ * when the 64th lies clearly below the k-th), then, for clusters of more than 64 - k near-equal rows, by the
+ * reference's arithmetic on every row.  So the ids, their order and the fp32 score bits are those of the
+ * exhaustive computation, always; the cost of an uncertified query is one or two passes over the master copy. */
 int b200_index_search(b200_index_t* idx, const void* queries, int q_dtype, int queries_on_device, int64_t nq,
                       int k, int64_t id_base, int64_t* ids, float* scores, int out_on_device, void* stream);
 

@@ -6,11 +6,11 @@ P = "copilot-for-consensus_b200"
 vs = importlib.import_module(P + ".vectorstore"); nat = importlib.import_module(P + "._native")
 dev = torch.device("cuda", 0)
 g = torch.Generator(device=dev).manual_seed(1)
-for n in (125_000, 1_250_000, 10_000_000):
+for n in (1_250_000, 5_000_000, 10_000_000, 25_000_000, 50_000_000):
     ix = vs.B200Index(384, device=0, master_dtype="bfloat16", capacity=n)
     for c0 in range(0, n, 1 << 20):
         ix.add(torch.randn((min(1 << 20, n - c0), 384), generator=g, device=dev).bfloat16().contiguous())
-    for nq in (512, 4096):
+    for nq in (4096,):
         q = torch.randn((nq, 384), generator=g, device=dev).bfloat16().contiguous()
         for kp in (16, 20):
             with nat.options(sim_pair_kp=kp):
@@ -25,5 +25,6 @@ for n in (125_000, 1_250_000, 10_000_000):
             print(json.dumps({"rows": n, "nq": nq, "kp": kp, "sim_ms": round(pr["sim_topk"]["ms"] / pr["sim_topk"]["launches"], 4),
                               "merge_ms": round(pr["merge_rescore"]["ms"] / pr["merge_rescore"]["launches"], 4),
                               "exact_ms": round(pr["exact_topk"]["ms"] / pr["exact_topk"]["launches"], 4),
+                              "full_ms": round(pr["exact_full"]["ms"] / pr["exact_full"]["launches"], 4),
                               "rescored_per_search": (r1_ - r0_) / 10}), flush=True)
     ix.close()
