@@ -102,6 +102,15 @@ __global__ void __launch_bounds__(256) att_norms_kernel(const __nv_bfloat16* __r
   }
 }
 
+// The same decision from maxima the QKV projection's epilogue has already folded (EPI_HEADNORM): one thread per
+// (sequence, head).
+__global__ void att_flag_kernel(const float* __restrict__ qmax2, const float* __restrict__ kmax2, int n, int32_t* __restrict__ flag) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const float gap_sq = 0.25f * ATT_BOUND_GAP * ATT_BOUND_GAP / (ATT_NORM_SLACK * ATT_NORM_SLACK);
+  if (!(qmax2[i] * kmax2[i] <= gap_sq)) atomicOr(flag, 1);
+}
+
 struct A64Item {
   int b, h, mt, len, nb, ns;   // sequence, head, query tile, valid keys, key blocks with a valid key, block steps
 };

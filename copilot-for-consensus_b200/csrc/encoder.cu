@@ -130,9 +130,9 @@ static int launch_gemm_t(const b200_encoder* e, const GemmIO& io, GemmParams p, 
   const int tiles = (p.M / (GEMM_BLOCK_M * CG)) * (p.N / BLOCK_N);
   const int grid = std::min(tiles, e->num_sms / CG) * CG;
   {
-    B200_PROF(EPI == EPI_BIAS ? "gemm_bias" : (EPI == EPI_BIAS_GELU ? "gemm_bias_gelu" : "gemm_bias_resid"),
+    B200_PROF((EPI & EPI_BIAS_RESID) ? "gemm_bias_resid" : ((EPI & EPI_BIAS_GELU) ? "gemm_bias_gelu" : "gemm_bias"),
               2.0 * p.M * (double)p.N * p.K,
-              2.0 * ((double)p.M * p.K + (double)p.N * p.K + (double)p.M * p.N * (EPI == EPI_BIAS_RESID ? 2 : 1)), st);
+              2.0 * ((double)p.M * p.K + (double)p.N * p.K + (double)p.M * p.N * ((EPI & EPI_BIAS_RESID) ? 2 : 1)), st);
     if (CG == 1) {
       kern<<<grid, gemm_threads(BLOCK_N), smem, st>>>(*io.a, *io.w, *io.out, *io.resid, p);
     } else {
@@ -270,7 +270,7 @@ static int ensure_activations(b200_encoder* e, int64_t m_rows, int batch, cudaSt
   const int H = e->cfg.hidden, I = e->cfg.intermediate;
   B200_TRY(e->lens.grow((size_t)std::max(batch, 1) * 4, 0, st));
   B200_TRY(e->out.grow((size_t)std::max(batch, 1) * H * 4, 0, st));
-  B200_TRY(e->att_kmax2.grow((size_t)std::max(batch, 1) * e->cfg.heads * 4, 0, st));
+  B200_TRY(e->att_kmax2.grow((size_t)2 * std::max(batch, 1) * e->cfg.heads * 4, 0, st));   // max |k|^2, then max |q|^2
   B200_TRY(e->att_flag.grow(64, 0, st));
   if (m_rows <= e->m_cap) return B200_OK;
   const int64_t m = (m_rows + 255) / 256 * 256;   // whole 256-row tiles for the CTA-pair GEMM
@@ -365,7 +365,18 @@ static int run_encoder(b200_encoder* e, const int32_t* d_ids, const int32_t* d_l
     GemmParams p{};
     // Q,K,V projections in one GEMM: qkv = x Wqkv^T + bqkv
     p.M = M; p.N = 3 * H; p.K = H; p.bias = L->bqkv.as<float>(); p.reverse = serp ? (kcount++ & 1) : 0;
-    B200_TRY(launch_gemm<EPI_BIAS>(e, GemmIO{&e->map_x, &L->map_wqkv, &L->map_wqkv_h, &e->map_qkv_st, &e->map_qkv_st}, p, st));
+    // 64-wide heads on whole CTA-pair tiles: the epilogue also folds the per-(sequence, head) maxima of |q|^2 and |k|^2
+    // that attention_tc64 takes its softmax reference from (option att_norms_fused=0: a separate pass over Q and K)
+    const bool fold_norms = use_att_tc64 && opt(OPT_ATT_NORMS_FUSED) != 0 && M % (2 * GEMM_BLOCK_M) == 0 &&
+                            pick_block_n(3 * H) == 192 && opt(OPT_GEMM_PAIR) != 0;
+    if (fold_norms) {
+      B200_CUDA(cudaMemsetAsync(e->att_kmax2.p, 0, (size_t)2 * batch * heads * 4, st));
+      p.hn_k2 = e->att_kmax2.as<float>(); p.hn_q2 = p.hn_k2 + (size_t)batch * heads;
+      p.hn_S = seq; p.hn_H = H; p.hn_heads = heads;
+      B200_TRY((launch_gemm_t<192, EPI_HEADNORM, 2>(e, GemmIO{&e->map_x, &L->map_wqkv, &L->map_wqkv_h, &e->map_qkv_st, &e->map_qkv_st}, p, st)));
+    } else {
+      B200_TRY(launch_gemm<EPI_BIAS>(e, GemmIO{&e->map_x, &L->map_wqkv, &L->map_wqkv_h, &e->map_qkv_st, &e->map_qkv_st}, p, st));
+    }
     if (use_att_tc) {
       AttParams ap;
       ap.S = seq; ap.H = H; ap.heads = heads; ap.n_mt = (seq + 127) / 128; ap.n_units = batch * heads * ap.n_mt;
@@ -382,8 +393,12 @@ static int run_encoder(b200_encoder* e, const int32_t* d_ids, const int32_t* d_l
       B200_CUDA(cudaLaunchKernelEx(&cfg, att_kernel, map_att_q, map_att_kv, map_att_out, ap));
     } else if (use_att_tc64) {
       B200_CUDA(cudaMemsetAsync(e->att_flag.p, 0, 4, st));
-      att_norms_kernel<A64_DH><<<dim3(heads, batch), 256, 0, st>>>(e->qkv.as<__nv_bfloat16>(), seq, H, heads,
-                                                                  e->att_kmax2.as<float>(), e->att_flag.as<int32_t>());
+      if (fold_norms)
+        att_flag_kernel<<<(batch * heads + 255) / 256, 256, 0, st>>>(e->att_kmax2.as<float>() + (size_t)batch * heads,
+                                                                    e->att_kmax2.as<float>(), batch * heads, e->att_flag.as<int32_t>());
+      else
+        att_norms_kernel<A64_DH><<<dim3(heads, batch), 256, 0, st>>>(e->qkv.as<__nv_bfloat16>(), seq, H, heads,
+                                                                    e->att_kmax2.as<float>(), e->att_flag.as<int32_t>());
       B200_CUDA(cudaGetLastError());
       Att64Params ap{};
       ap.S = seq; ap.H = H; ap.heads = heads; ap.n_mt = seq / 128; ap.n_units = batch * heads * ap.n_mt;

@@ -132,7 +132,15 @@ constexpr int GEMM_STAGING_BYTES = 32 * GEMM_OUT_CHUNK * 2;         // 32 rows x
 constexpr int gemm_epi_warps(int block_n) { return 4 * (block_n / GEMM_OUT_CHUNK); }
 constexpr int gemm_threads(int block_n) { return 128 + 32 * gemm_epi_warps(block_n); }
 
-enum { EPI_BIAS = 0, EPI_BIAS_GELU = 1, EPI_BIAS_RESID = 2 };
+// Epilogue of the GEMM kernels, a bit set: every epilogue adds the bias.
+//   EPI_BIAS_GELU   GELU on the result (FFN1)
+//   EPI_BIAS_RESID  + the residual tile (out-projection, FFN2)
+//   EPI_HEADNORM    the output is the QKV projection of 64-wide heads: besides storing it, fold max_r |q_r|^2 and
+//                   max_j |k_j|^2 of every (sequence, head) into GemmParams::hn_q2 / hn_k2 (what att_norms_kernel
+//                   would re-read the whole Q and K for).  An epilogue warp holds 32 rows x 64 columns = one head's slice of
+//                   32 tokens, one row per thread, so the squared norm is a thread-local sum and the maximum one warp
+//                   reduction + one atomicMax (non-negative floats order like their bit patterns).
+enum { EPI_BIAS = 0, EPI_BIAS_GELU = 1, EPI_BIAS_RESID = 2, EPI_HEADNORM = 4 };
 
 struct GemmParams {
   int M, N, K;         // M multiple of 128, N multiple of BLOCK_N, K multiple of 64
@@ -144,6 +152,10 @@ struct GemmParams {
   int reverse;         // 1: walk the row blocks from the last to the first.  Consecutive kernels of a layer
                        // alternate, so each starts with the rows its producer wrote LAST -- the part of a
                        // 300-400 MB activation that is still in the 126 MB L2.
+  // EPI_HEADNORM: [batch * heads] running maxima (zeroed before the launch), sequence length, hidden size, heads
+  float* hn_q2;
+  float* hn_k2;
+  int hn_S, hn_H, hn_heads;
 };
 
 // GELU(x) = x * Phi(x) (the exact-erf form BERT uses).  Phi is evaluated as
@@ -171,15 +183,17 @@ __device__ unsigned long long g_gemm_timing[8];
 // registers (one tcgen05.ld.x64), bias (+ GELU | + residual, which arrives by TMA in the staging box),
 // bf16, 128-byte-swizzled staging box, TMA store.
 template <int EPI, int CG>
-B200_DEVINL void gemm_epi_tile(const CUtensorMap& map_out, const CUtensorMap& map_resid, const float* bias, int m0, int n0,
+B200_DEVINL void gemm_epi_tile(const CUtensorMap& map_out, const CUtensorMap& map_resid, const GemmParams& p, int m0, int n0,
                                uint8_t* stg, float* sbias, uint64_t* rbar, uint8_t* my_row, int sw, int lane, uint32_t tacc,
                                uint64_t* acc_full_bar, uint32_t aph, uint64_t* acc_empty_bar, uint32_t it) {
+  const float* bias = p.bias;
+  float head_sq = 0.f;       // EPI_HEADNORM: |row slice|^2 of the values as stored (bf16)
   __syncwarp();
   sts32(smem_u32(sbias) + lane * 4, __float_as_uint(__ldg(bias + n0 + lane)));
   sts32(smem_u32(sbias) + (lane + 32) * 4, __float_as_uint(__ldg(bias + n0 + 32 + lane)));
   if (lane == 0) {
     tma_store_wait_read();   // the previous tile's store has finished reading this warp's box
-    if (EPI == EPI_BIAS_RESID) {
+    if (EPI & EPI_BIAS_RESID) {
       mbar_arrive_expect_tx(rbar, GEMM_STAGING_BYTES);
       tma_load_2d(stg, &map_resid, rbar, n0, m0);
     }
@@ -195,7 +209,7 @@ B200_DEVINL void gemm_epi_tile(const CUtensorMap& map_out, const CUtensorMap& ma
   if (lane == 0) {
     if (CG == 2) mbar_arrive_leader(acc_empty_bar); else mbar_arrive(acc_empty_bar);
   }
-  if (EPI == EPI_BIAS_RESID) mbar_wait(rbar, it & 1);
+  if (EPI & EPI_BIAS_RESID) mbar_wait(rbar, it & 1);
 #ifdef B200_GEMM_TIMING
   const unsigned long long dbg = g_gemm_timing[7];
   if (dbg == 1) return;   // experiment: accumulators drained, nothing computed or stored
@@ -209,12 +223,12 @@ B200_DEVINL void gemm_epi_tile(const CUtensorMap& map_out, const CUtensorMap& ma
     f[2] = __uint_as_float(v[j * 8 + 2]) + __uint_as_float(b0.z); f[3] = __uint_as_float(v[j * 8 + 3]) + __uint_as_float(b0.w);
     f[4] = __uint_as_float(v[j * 8 + 4]) + __uint_as_float(b1.x); f[5] = __uint_as_float(v[j * 8 + 5]) + __uint_as_float(b1.y);
     f[6] = __uint_as_float(v[j * 8 + 6]) + __uint_as_float(b1.z); f[7] = __uint_as_float(v[j * 8 + 7]) + __uint_as_float(b1.w);
-    if (EPI == EPI_BIAS_GELU) {
+    if (EPI & EPI_BIAS_GELU) {
 #pragma unroll
       for (int i = 0; i < 8; ++i) f[i] = gelu_erf(f[i]);
     }
     const uint32_t slot = s_row + ((j ^ sw) << 4);
-    if (EPI == EPI_BIAS_RESID) {
+    if (EPI & EPI_BIAS_RESID) {
       const uint4 r = lds128(slot);
       const __nv_bfloat162* r2 = reinterpret_cast<const __nv_bfloat162*>(&r);
 #pragma unroll
@@ -231,6 +245,24 @@ B200_DEVINL void gemm_epi_tile(const CUtensorMap& map_out, const CUtensorMap& ma
     o.x = *reinterpret_cast<uint32_t*>(&t0); o.y = *reinterpret_cast<uint32_t*>(&t1);
     o.z = *reinterpret_cast<uint32_t*>(&t2); o.w = *reinterpret_cast<uint32_t*>(&t3);
     sts128(slot, o);
+    if (EPI & EPI_HEADNORM) {
+      const __nv_bfloat162 tt[4] = {t0, t1, t2, t3};
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const float lo = __low2float(tt[i]), hi = __high2float(tt[i]);
+        head_sq = fmaf(lo, lo, fmaf(hi, hi, head_sq));
+      }
+    }
+  }
+  if (EPI & EPI_HEADNORM) {
+    if (n0 < 2 * p.hn_H) {       // Q and K columns (V needs no norm); warp-uniform
+      const float mx = warp_max(head_sq);
+      if (lane == 0) {
+        const int is_k = n0 >= p.hn_H;
+        const int h = (n0 - is_k * p.hn_H) / GEMM_OUT_CHUNK;
+        atomicMax(reinterpret_cast<unsigned int*>(is_k ? p.hn_k2 : p.hn_q2) + (m0 / p.hn_S) * p.hn_heads + h, __float_as_uint(mx));
+      }
+    }
   }
 #ifdef B200_GEMM_TIMING
   if (dbg == 3) return;      // experiment: no fence, no store
@@ -294,7 +326,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     tma_prefetch_desc(&map_a);
     tma_prefetch_desc(&map_b);
     tma_prefetch_desc(&map_out);
-    if (EPI == EPI_BIAS_RESID) tma_prefetch_desc(&map_resid);
+    if (EPI & EPI_BIAS_RESID) tma_prefetch_desc(&map_resid);
   }
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < p.nstage; ++i) {
@@ -422,7 +454,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
       const int mt = tile / n_tiles, mtr = p.reverse ? total_tiles / n_tiles - 1 - mt : mt;
       const int m0 = mtr * (GEMM_BLOCK_M * CG) + rank * GEMM_BLOCK_M + wq * 32;
       const int n0 = (tile % n_tiles) * BLOCK_N + chunk * GEMM_OUT_CHUNK;
-      gemm_epi_tile<EPI, CG>(map_out, map_resid, p.bias, m0, n0, stg, sbias, rbar, my_row, sw, lane,
+      gemm_epi_tile<EPI, CG>(map_out, map_resid, p, m0, n0, stg, sbias, rbar, my_row, sw, lane,
                              tmem_base + ((uint32_t)(wq * 32) << 16) + as * BLOCK_N + chunk * GEMM_OUT_CHUNK,
                              &acc_full[as], aph, &acc_empty[as], it);
     }
@@ -492,7 +524,7 @@ gemm_bf16_ast_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
     tma_prefetch_desc(&map_a);
     tma_prefetch_desc(&map_b);
     tma_prefetch_desc(&map_out);
-    if (EPI == EPI_BIAS_RESID) tma_prefetch_desc(&map_resid);
+    if (EPI & EPI_BIAS_RESID) tma_prefetch_desc(&map_resid);
   }
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < p.nstage; ++i) {
@@ -626,7 +658,7 @@ gemm_bf16_ast_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
         const uint32_t as = it & 1, aph = (it >> 1) & 1;
         const int m0 = (p.reverse ? m_blocks - 1 - mb : mb) * (GEMM_BLOCK_M * CG) + rank * GEMM_BLOCK_M + wq * 32;
         const int n0 = nt * BLOCK_N + chunk * GEMM_OUT_CHUNK;
-        gemm_epi_tile<EPI, CG>(map_out, map_resid, p.bias, m0, n0, stg, sbias, rbar, my_row, sw, lane,
+        gemm_epi_tile<EPI, CG>(map_out, map_resid, p, m0, n0, stg, sbias, rbar, my_row, sw, lane,
                                tmem_base + ((uint32_t)(wq * 32) << 16) + as * BLOCK_N + chunk * GEMM_OUT_CHUNK,
                                &acc_full[as], aph, &acc_empty[as], it);
       }

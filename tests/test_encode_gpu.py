@@ -175,12 +175,15 @@ def test_mpnet_base_class_matches_fp32_oracle():
     p.close()
 
 
-@pytest.mark.parametrize("S,qk_scale,exact_max", [(128, 1.0, 0), (256, 1.0, 0), (384, 1.0, 1), (384, 40.0, 0), (512, 1.0, 0)])
-def test_wide_head_attention_block_kernel(S, qk_scale, exact_max):
+@pytest.mark.parametrize("S,qk_scale,exact_max,B", [(128, 1.0, 0, 7), (256, 1.0, 0, 7), (384, 1.0, 1, 7), (384, 40.0, 0, 7),
+                                                    (512, 1.0, 0, 7), (384, 1.0, 0, 8), (384, 40.0, 0, 8), (128, 40.0, 0, 6)])
+def test_wide_head_attention_block_kernel(S, qk_scale, exact_max, B):
     """64-wide heads over whole 128-key blocks run on attention_tc64_kernel (key blocks accumulated under a fixed
     Cauchy-Schwarz reference).  Both of its scripts against the fp32 oracle: the bound script (random-init weights), the
     exact-maximum script forced by the option, and the exact script chosen by att_norms_kernel itself when query / key
-    weights are scaled until the bound is unusable; ragged lengths put padding inside and across key blocks."""
+    weights are scaled until the bound is unusable; ragged lengths put padding inside and across key blocks.
+    With whole 256-token tiles (B * S % 256 == 0) the key / query norms behind that decision come from the QKV
+    projection's epilogue instead of att_norms_kernel (same maxima up to the summation order), and both ways are checked."""
     from safetensors.torch import load_file, save_file
 
     mio, prov, nat = pkg("embedding.model_io"), pkg("embedding.provider"), pkg("_native")
@@ -192,7 +195,7 @@ def test_wide_head_attention_block_kernel(S, qk_scale, exact_max):
         save_file({k: v.contiguous() for k, v in _scale_qk(load_file(path), qk_scale).items()}, path)
         p = prov.B200SentenceTransformerProvider(model_name=td, device="cuda:0")
     w = _scale_qk(eo.make_weights(ocfg, seed=9), qk_scale)
-    ids, mask, lens = eo.synthetic_tokens(7, S, 3000, seed=S, ragged=True)
+    ids, mask, lens = eo.synthetic_tokens(B, S, 3000, seed=S, ragged=True)
     lens[0], mask[0] = S, 1                                   # one full-length row
     if S >= 256:
         lens[1] = 129                                         # one valid key in the second block
@@ -201,11 +204,15 @@ def test_wide_head_attention_block_kernel(S, qk_scale, exact_max):
         ids[1, 129:] = 0
     with nat.options(att_exact_max=exact_max):
         got = p.embed_tokens(ids.numpy(), lens.numpy())
+    with nat.options(att_exact_max=exact_max, att_norms_fused=0):
+        unfused = p.embed_tokens(ids.numpy(), lens.numpy())
+    np.testing.assert_allclose(np.asarray(got), np.asarray(unfused), atol=1e-3)     # the maxima agree to rounding
     with nat.options(attention_tc=0):
         legacy = p.embed_tokens(ids.numpy(), lens.numpy())    # the mma.sync kernel on the same input
     ref = eo.encode(ocfg, w, ids, mask).numpy()
     _check(legacy, ref)
     _check(got, ref)
+    _check(unfused, ref)
     p.close()
 
 
