@@ -32,6 +32,10 @@ struct LayerWeights {
   CUtensorMap map_wqkv, map_wo, map_w1, map_w2;           // box rows = BLOCK_N
   CUtensorMap map_wqkv_h, map_wo_h, map_w1_h, map_w2_h;   // box rows = BLOCK_N / 2 (one CTA's share in a CTA pair)
   CUtensorMap map_w1_f;                                   // box rows = 64: one CTA's share of a 128-column FFN slice (ffn_fused_kernel)
+  // deferred LayerNorm (EPI_ROWFOLD): weights with the preceding LayerNorm's gamma folded into their columns,
+  // their row sums c[n] (of the bf16 values), and biases with W beta added
+  DevBuf wqkv_g, w1_g, cqkv, c1, bqkv_g, b1_g;
+  CUtensorMap map_wqkv_gh, map_w1_gh;                     // box rows = BLOCK_N / 2
 };
 
 uint16_t f32_to_bf16_host(float f) {
@@ -68,6 +72,10 @@ struct b200_encoder {
   int64_t m_cap = 0;
   DevBuf x, qkv, ctx, y, ffn, ids, lens, out;
   DevBuf att_kmax2, att_flag;   // attention_tc64: max |k|^2 per (sequence, head); "take the exact-maximum script" flag
+  bool defer_capable = false;   // the folded weights of the deferred-LayerNorm path exist (finalize)
+  DevBuf ln_ones, ln_zeros;     // [hidden] gamma = 1 / beta = 0 for layer 0 of the deferred-LayerNorm path
+  DevBuf ln_stats0, ln_stats1;  // deferred LayerNorm: [m_cap][hidden / 64][2] (sum, sum of squares) of x-buffer / y-buffer rows
+  CUtensorMap map_y;                                        // y as an A operand (deferred LayerNorm: FFN1 reads it)
   CUtensorMap map_x, map_ctx, map_ffn;                      // A operands: box {64, 128}
   CUtensorMap map_qkv_st, map_y_st, map_ffn_st, map_x_res;  // epilogue boxes {64, 32}: stores and the residual load
   StreamOrder order;   // calls arriving on different streams share the activation buffers: see host_util.h
@@ -120,7 +128,8 @@ static int launch_gemm_t(const b200_encoder* e, const GemmIO& io, GemmParams p, 
   const size_t stage = (size_t)GEMM_A_STAGE_BYTES + (size_t)(BLOCK_N / CG) * GEMM_BLOCK_K * 2;
   const size_t max_smem = 232448;
   // staging boxes, barriers (2*nstage + 4 + NEPI, at most 8 stages), TMEM slot, per-warp bias slices
-  const size_t tail = (size_t)NEPI * GEMM_STAGING_BYTES + 8 * (2 * 8 + 4 + NEPI) + 16 + (size_t)NEPI * GEMM_OUT_CHUNK * 4;
+  const size_t tail = (size_t)NEPI * GEMM_STAGING_BYTES + 8 * (2 * 8 + 4 + NEPI) + 16 +
+                      (size_t)NEPI * GEMM_OUT_CHUNK * 4 * gemm_epi_consts(EPI);
   int nstage = (int)std::min<size_t>(8, (max_smem - 1024 - tail) / stage);
   if (nstage < 2) B200_FAIL(B200_ERR_UNSUPPORTED, "GEMM tile does not fit in shared memory");
   p.nstage = nstage;
@@ -287,6 +296,15 @@ static int ensure_activations(b200_encoder* e, int64_t m_rows, int batch, cudaSt
   B200_CUDA(cudaMemsetAsync(e->qkv.p, 0, (size_t)m * 3 * H * 2, st));
   B200_TRY(make_tma_2d_bf16(&e->map_x, e->x.p, (uint64_t)m, (uint64_t)H, GEMM_BLOCK_M, GEMM_BLOCK_K));
   B200_TRY(make_tma_2d_bf16(&e->map_ctx, e->ctx.p, (uint64_t)m, (uint64_t)H, GEMM_BLOCK_M, GEMM_BLOCK_K));
+  B200_TRY(make_tma_2d_bf16(&e->map_y, e->y.p, (uint64_t)m, (uint64_t)H, GEMM_BLOCK_M, GEMM_BLOCK_K));
+  if (e->defer_capable) {
+    const size_t sb = (size_t)m * (H / GEMM_OUT_CHUNK) * 2 * 4;
+    B200_TRY(e->ln_stats0.grow(sb, 0, st));
+    B200_TRY(e->ln_stats1.grow(sb, 0, st));
+    B200_CUDA(cudaMemsetAsync(e->ln_stats0.p, 0, sb, st));
+    B200_CUDA(cudaMemsetAsync(e->ln_stats1.p, 0, sb, st));
+    B200_CUDA(cudaMemsetAsync(e->y.p, 0, (size_t)m * H * 2, st));
+  }
   B200_TRY(make_tma_2d_bf16(&e->map_ffn, e->ffn.p, (uint64_t)m, (uint64_t)I, GEMM_BLOCK_M, GEMM_BLOCK_K));
   B200_TRY(make_tma_2d_bf16(&e->map_qkv_st, e->qkv.p, (uint64_t)m, (uint64_t)(3 * H), 32, GEMM_OUT_CHUNK));
   B200_TRY(make_tma_2d_bf16(&e->map_y_st, e->y.p, (uint64_t)m, (uint64_t)H, 32, GEMM_OUT_CHUNK));
@@ -314,9 +332,18 @@ static int run_encoder(b200_encoder* e, const int32_t* d_ids, const int32_t* d_l
   const int wpb = 8;
   __nv_bfloat16* x = e->x.as<__nv_bfloat16>();
   __nv_bfloat16* y = e->y.as<__nv_bfloat16>();
+  // Deferred LayerNorm (hidden sizes without the fused GEMM + LayerNorm kernel; option defer_ln=0 disables): no
+  // LayerNorm output is ever written -- see EPI_ROWFOLD in encoder_kernels.cuh.  The x buffer then holds the
+  // un-normalised input / output of a layer, the y buffer the one between its two blocks, each with its statistic slots.
+  const bool defer = e->defer_capable && opt(OPT_DEFER_LN) != 0 && opt(OPT_GEMM_PAIR) != 0;
+  const int ln_parts = H / GEMM_OUT_CHUNK;
+  float* stats_x = e->ln_stats0.as<float>();
+  float* stats_y = e->ln_stats1.as<float>();
   embed_ln_kernel<NV><<<(n_tok + wpb - 1) / wpb, wpb * 32, 0, st>>>(
       d_ids, n_tok, seq, e->cfg.vocab_size, e->word.as<__nv_bfloat16>(), e->pos.as<__nv_bfloat16>(),
       e->type0.as<__nv_bfloat16>(), e->emb_g.as<float>(), e->emb_b.as<float>(), e->cfg.ln_eps, x);
+  if (defer)   // layer 0 reads the normalised embedding rows through "identity" statistics
+    ln_identity_stats_kernel<<<(unsigned)(((int64_t)M * ln_parts + 255) / 256), 256, 0, st>>>(stats_x, M, ln_parts, (float)H);
   B200_CUDA(cudaGetLastError());
 
   const size_t att_smem = 2 * (size_t)seq * (dh + 8) * 2;   // K and V tiles, rows padded by 16 bytes
@@ -369,10 +396,22 @@ static int run_encoder(b200_encoder* e, const int32_t* d_ids, const int32_t* d_l
     // that attention_tc64 takes its softmax reference from (option att_norms_fused=0: a separate pass over Q and K)
     const bool fold_norms = use_att_tc64 && opt(OPT_ATT_NORMS_FUSED) != 0 && M % (2 * GEMM_BLOCK_M) == 0 &&
                             pick_block_n(3 * H) == 192 && opt(OPT_GEMM_PAIR) != 0;
+    // the LayerNorm in front of this layer (deferred form): none for layer 0 (the embedding's has been applied), else the
+    // previous layer's second one
+    const float* in_g = l == 0 ? e->ln_ones.as<float>() : e->layers[l - 1]->ln2_g.as<float>();
+    const float* in_b = l == 0 ? e->ln_zeros.as<float>() : e->layers[l - 1]->ln2_b.as<float>();
     if (fold_norms) {
       B200_CUDA(cudaMemsetAsync(e->att_kmax2.p, 0, (size_t)2 * batch * heads * 4, st));
       p.hn_k2 = e->att_kmax2.as<float>(); p.hn_q2 = p.hn_k2 + (size_t)batch * heads;
       p.hn_S = seq; p.hn_H = H; p.hn_heads = heads;
+    }
+    if (defer) {
+      p.bias = l == 0 ? L->bqkv.as<float>() : L->bqkv_g.as<float>(); p.fold_c = L->cqkv.as<float>(); p.eps = e->cfg.ln_eps;
+      p.ln_stats_in = stats_x; p.ln_parts = ln_parts; p.ln_inv_n = 1.0f / (float)H;
+      const GemmIO io{&e->map_x, &L->map_wqkv, l == 0 ? &L->map_wqkv_h : &L->map_wqkv_gh, &e->map_qkv_st, &e->map_qkv_st};
+      if (fold_norms) B200_TRY((launch_gemm_t<192, EPI_ROWFOLD | EPI_HEADNORM, 2>(e, io, p, st)));
+      else B200_TRY((launch_gemm_t<192, EPI_ROWFOLD, 2>(e, io, p, st)));
+    } else if (fold_norms) {
       B200_TRY((launch_gemm_t<192, EPI_HEADNORM, 2>(e, GemmIO{&e->map_x, &L->map_wqkv, &L->map_wqkv_h, &e->map_qkv_st, &e->map_qkv_st}, p, st)));
     } else {
       B200_TRY(launch_gemm<EPI_BIAS>(e, GemmIO{&e->map_x, &L->map_wqkv, &L->map_wqkv_h, &e->map_qkv_st, &e->map_qkv_st}, p, st));
@@ -425,7 +464,13 @@ static int run_encoder(b200_encoder* e, const int32_t* d_ids, const int32_t* d_l
     B200_CUDA(cudaGetLastError());
     // y = ctx Wo^T + bo + x ; x = LN(y)
     p.N = H; p.K = H; p.bias = L->bo.as<float>(); p.reverse = serp ? (kcount++ & 1) : 0;
-    if (fuse_ln) {
+    if (defer) {
+      // y = ctx Wo^T + bo + LN_in(x buffer): the residual is rebuilt from the un-normalised rows; statistics of y go out
+      p.gamma = in_g; p.beta = in_b; p.eps = e->cfg.ln_eps;
+      p.ln_stats_in = stats_x; p.ln_parts = ln_parts; p.ln_inv_n = 1.0f / (float)H; p.ln_stats_out = stats_y;
+      B200_TRY((launch_gemm_t<192, EPI_BIAS_RESID | EPI_RESID_LN | EPI_STATS, 2>(
+          e, GemmIO{&e->map_ctx, &L->map_wo, &L->map_wo_h, &e->map_y_st, &e->map_x_res}, p, st)));
+    } else if (fuse_ln) {
       p.gamma = L->ln1_g.as<float>(); p.beta = L->ln1_b.as<float>(); p.eps = e->cfg.ln_eps;
       B200_TRY(launch_gemm_ln(e, GemmIO{&e->map_ctx, &L->map_wo, &L->map_wo_h, &e->map_x_res, &e->map_x_res}, p, st));
     } else {
@@ -437,6 +482,21 @@ static int run_encoder(b200_encoder* e, const int32_t* d_ids, const int32_t* d_l
     // ffn = gelu(x W1^T + b1) ; y = ffn W2^T + b2 + x ; x = LN(y)
     if (fuse_ffn) {
       B200_TRY(launch_ffn_fused(e, L, M, I, serp ? (kcount++ & 1) : 0, st));
+      continue;
+    }
+    if (defer) {
+      // ffn = gelu(LN1(y) W1^T + b1) from the un-normalised y; then x buffer = ffn W2^T + b2 + LN1(y), with its statistics
+      p = GemmParams{};
+      p.M = M; p.N = I; p.K = H; p.bias = L->b1_g.as<float>(); p.fold_c = L->c1.as<float>(); p.eps = e->cfg.ln_eps;
+      p.ln_stats_in = stats_y; p.ln_parts = ln_parts; p.ln_inv_n = 1.0f / (float)H; p.reverse = serp ? (kcount++ & 1) : 0;
+      B200_TRY((launch_gemm_t<192, EPI_ROWFOLD | EPI_BIAS_GELU, 2>(
+          e, GemmIO{&e->map_y, &L->map_w1, &L->map_w1_gh, &e->map_ffn_st, &e->map_ffn_st}, p, st)));
+      p = GemmParams{};
+      p.M = M; p.N = H; p.K = I; p.bias = L->b2.as<float>(); p.reverse = serp ? (kcount++ & 1) : 0;
+      p.gamma = L->ln1_g.as<float>(); p.beta = L->ln1_b.as<float>(); p.eps = e->cfg.ln_eps;
+      p.ln_stats_in = stats_y; p.ln_parts = ln_parts; p.ln_inv_n = 1.0f / (float)H; p.ln_stats_out = stats_x;
+      B200_TRY((launch_gemm_t<192, EPI_BIAS_RESID | EPI_RESID_LN | EPI_STATS, 2>(
+          e, GemmIO{&e->map_ffn, &L->map_w2, &L->map_w2_h, &e->map_x_res, &e->map_y_st}, p, st)));
       continue;
     }
     p.N = I; p.K = H; p.bias = L->b1.as<float>(); p.reverse = serp ? (kcount++ & 1) : 0;
@@ -451,6 +511,12 @@ static int run_encoder(b200_encoder* e, const int32_t* d_ids, const int32_t* d_l
                                                                         e->cfg.ln_eps, x);
       B200_CUDA(cudaGetLastError());
     }
+  }
+  if (defer) {   // the last layer's second LayerNorm, in place (a row is read whole before it is written)
+    const LayerWeights* L = e->layers.back();
+    layernorm_kernel<NV><<<(n_tok + wpb - 1) / wpb, wpb * 32, 0, st>>>(x, n_tok, L->ln2_g.as<float>(), L->ln2_b.as<float>(),
+                                                                      e->cfg.ln_eps, x);
+    B200_CUDA(cudaGetLastError());
   }
   pool_normalize_kernel<<<batch, 256, 0, st>>>(x, d_lens, seq, H, d_out);
   B200_CUDA(cudaGetLastError());
@@ -526,6 +592,40 @@ int b200_encoder_finalize(b200_encoder_t* e) {
   B200_TRY(upload_f32(e->emb_g, t->data(), H));
   B200_TRY(take(e, "embeddings.LayerNorm.bias", H, &t));
   B200_TRY(upload_f32(e->emb_b, t->data(), H));
+  // deferred LayerNorm needs whole 192-column tiles everywhere and an even number of 64-column statistic slots;
+  // hidden 384 has the fused GEMM + LayerNorm kernel instead
+  e->defer_capable = H != 384 && H % 192 == 0 && (H / 64) % 2 == 0 && I % 192 == 0;
+  // the LayerNorm in front of the layer being loaded; none for layer 0 (the embedding's is applied by embed_ln_kernel)
+  std::vector<float> prev_g(H, 1.0f), prev_b(H, 0.0f);
+  if (e->defer_capable) {
+    B200_TRY(upload_f32(e->ln_ones, prev_g.data(), H));
+    B200_TRY(upload_f32(e->ln_zeros, prev_b.data(), H));
+  }
+  // W (.) gamma as bf16, its row sums, b + W beta
+  auto fold = [&](const float* w, const float* b, size_t N, const std::vector<float>& g, const std::vector<float>& be,
+                  DevBuf& wg, DevBuf& c, DevBuf& bg) -> int {
+    std::vector<uint16_t> wq(N * H);
+    std::vector<float> cs(N), bf(N);
+    for (size_t n = 0; n < N; ++n) {
+      double csum = 0.0, bsum = 0.0;
+      for (size_t k = 0; k < H; ++k) {
+        const uint16_t q = f32_to_bf16_host(w[n * H + k] * g[k]);
+        wq[n * H + k] = q;
+        const uint32_t u = (uint32_t)q << 16;
+        float back;
+        memcpy(&back, &u, 4);
+        csum += back;
+        bsum += (double)w[n * H + k] * be[k];
+      }
+      cs[n] = (float)csum;
+      bf[n] = b[n] + (float)bsum;
+    }
+    B200_TRY(wg.alloc(N * H * 2));
+    B200_CUDA(cudaMemcpy(wg.p, wq.data(), N * H * 2, cudaMemcpyHostToDevice));
+    B200_TRY(upload_f32(c, cs.data(), N));
+    B200_TRY(upload_f32(bg, bf.data(), N));
+    return B200_OK;
+  };
   for (int l = 0; l < e->cfg.layers; ++l) {
     const std::string p = "encoder.layer." + std::to_string(l) + ".";
     LayerWeights* L = new LayerWeights();
@@ -547,6 +647,10 @@ int b200_encoder_finalize(b200_encoder_t* e) {
     }
     B200_TRY(upload_bf16(L->wqkv, wqkv.data(), wqkv.size()));
     B200_TRY(upload_f32(L->bqkv, bqkv.data(), bqkv.size()));
+    if (e->defer_capable) {
+      B200_TRY(fold(wqkv.data(), bqkv.data(), 3 * H, prev_g, prev_b, L->wqkv_g, L->cqkv, L->bqkv_g));
+      B200_TRY(weight_map(&L->map_wqkv_gh, L->wqkv_g, (int)(3 * H), (int)H, 2));
+    }
     B200_TRY(take(e, p + "attention.output.dense.weight", H * H, &t));
     B200_TRY(upload_bf16(L->wo, t->data(), t->size()));
     B200_TRY(take(e, p + "attention.output.dense.bias", H, &t));
@@ -557,16 +661,26 @@ int b200_encoder_finalize(b200_encoder_t* e) {
     B200_TRY(upload_f32(L->ln1_b, t->data(), H));
     B200_TRY(take(e, p + "intermediate.dense.weight", I * H, &t));
     B200_TRY(upload_bf16(L->w1, t->data(), t->size()));
-    B200_TRY(take(e, p + "intermediate.dense.bias", I, &t));
-    B200_TRY(upload_f32(L->b1, t->data(), I));
+    const std::vector<float>* tb1 = nullptr;
+    B200_TRY(take(e, p + "intermediate.dense.bias", I, &tb1));
+    B200_TRY(upload_f32(L->b1, tb1->data(), I));
+    if (e->defer_capable) {
+      const std::vector<float>*g1 = nullptr, *be1 = nullptr;
+      B200_TRY(take(e, p + "attention.output.LayerNorm.weight", H, &g1));
+      B200_TRY(take(e, p + "attention.output.LayerNorm.bias", H, &be1));
+      B200_TRY(fold(t->data(), tb1->data(), I, *g1, *be1, L->w1_g, L->c1, L->b1_g));
+      B200_TRY(weight_map(&L->map_w1_gh, L->w1_g, (int)I, (int)H, 2));
+    }
     B200_TRY(take(e, p + "output.dense.weight", H * I, &t));
     B200_TRY(upload_bf16(L->w2, t->data(), t->size()));
     B200_TRY(take(e, p + "output.dense.bias", H, &t));
     B200_TRY(upload_f32(L->b2, t->data(), H));
     B200_TRY(take(e, p + "output.LayerNorm.weight", H, &t));
     B200_TRY(upload_f32(L->ln2_g, t->data(), H));
+    prev_g = *t;
     B200_TRY(take(e, p + "output.LayerNorm.bias", H, &t));
     B200_TRY(upload_f32(L->ln2_b, t->data(), H));
+    prev_b = *t;
     B200_TRY(weight_map(&L->map_wqkv, L->wqkv, (int)(3 * H), (int)H));
     B200_TRY(weight_map(&L->map_wo, L->wo, (int)H, (int)H));
     B200_TRY(weight_map(&L->map_w1, L->w1, (int)I, (int)H));

@@ -94,6 +94,16 @@ __global__ void __launch_bounds__(256) embed_ln_kernel(const int32_t* __restrict
   warp_layernorm_store<NV>(v, H, eps, gamma, beta, x + (size_t)tok * H, lane);
 }
 
+// Deferred LayerNorm (see EPI_ROWFOLD): statistic slots that make a row read as "already normalised" -- sum 0, sum of
+// squares = width, so mean = 0 and rstd = 1 (to 1e-12).  The embedding LayerNorm is NOT deferred: the raw embedding sum
+// of a model with a large common offset would lose its signal in bf16, so layer 0 reads embed_ln_kernel's output through
+// these slots with unfolded weights and gamma = 1, beta = 0.
+__global__ void ln_identity_stats_kernel(float* __restrict__ stats, int64_t n_rows, int parts, float width) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_rows * parts) return;
+  reinterpret_cast<float2*>(stats)[i] = (i % parts) == 0 ? make_float2(0.f, width) : make_float2(0.f, 0.f);
+}
+
 template <int NV>
 __global__ void __launch_bounds__(256) layernorm_kernel(const __nv_bfloat16* __restrict__ y, int n_rows,
                                                         const float* __restrict__ gamma, const float* __restrict__ beta,
@@ -140,7 +150,17 @@ constexpr int gemm_threads(int block_n) { return 128 + 32 * gemm_epi_warps(block
 //                   would re-read the whole Q and K for).  An epilogue warp holds 32 rows x 64 columns = one head's slice of
 //                   32 tokens, one row per thread, so the squared norm is a thread-local sum and the maximum one warp
 //                   reduction + one atomicMax (non-negative floats order like their bit patterns).
-enum { EPI_BIAS = 0, EPI_BIAS_GELU = 1, EPI_BIAS_RESID = 2, EPI_HEADNORM = 4 };
+//
+// Deferred LayerNorm (hidden sizes without the fused GEMM + LayerNorm kernel, e.g. 768): x = LN(y) is never
+// written.  A producer stores y (bf16) and, per row and 64-column chunk, (sum, sum of squares) of what it stored
+// (EPI_STATS: plain stores into the row's slot for that chunk -- no atomics, deterministic).  Consumers rebuild
+// what they need from y and those sums:
+//   EPI_ROWFOLD   the A operand is y, the weights are W' = W (.) gamma (column k scaled by gamma_k), and
+//                   x W^T = rstd (y W'^T - mean c) + W beta,   c_n = sum_k W'_nk
+//                 so the epilogue computes rstd_r (acc - mean_r c_n) + b'_n with b' = b + W beta folded on the host.
+//   EPI_RESID_LN  the residual tile holds y: x = (y - mean) rstd gamma + beta is formed on the fly (implies RESID).
+enum { EPI_BIAS = 0, EPI_BIAS_GELU = 1, EPI_BIAS_RESID = 2, EPI_HEADNORM = 4, EPI_ROWFOLD = 8, EPI_RESID_LN = 16, EPI_STATS = 32 };
+constexpr int gemm_epi_consts(int epi) { return (epi & (EPI_ROWFOLD | EPI_RESID_LN)) ? 3 : 1; }   // 64-float slices staged per warp
 
 struct GemmParams {
   int M, N, K;         // M multiple of 128, N multiple of BLOCK_N, K multiple of 64
@@ -156,6 +176,14 @@ struct GemmParams {
   float* hn_q2;
   float* hn_k2;
   int hn_S, hn_H, hn_heads;
+  // deferred LayerNorm: statistic slots [M][ln_parts][2] of the tensor being normalised (ROWFOLD: the A operand,
+  // RESID_LN: the residual), 1 / its width, the folded column sums c[N] (ROWFOLD), gamma / beta above (RESID_LN);
+  // EPI_STATS: the slots of the tensor being produced ([M][N / 64][2])
+  const float* ln_stats_in;
+  int ln_parts;
+  float ln_inv_n;
+  const float* fold_c;
+  float* ln_stats_out;
 };
 
 // GELU(x) = x * Phi(x) (the exact-erf form BERT uses).  Phi is evaluated as
@@ -191,6 +219,26 @@ B200_DEVINL void gemm_epi_tile(const CUtensorMap& map_out, const CUtensorMap& ma
   __syncwarp();
   sts32(smem_u32(sbias) + lane * 4, __float_as_uint(__ldg(bias + n0 + lane)));
   sts32(smem_u32(sbias) + (lane + 32) * 4, __float_as_uint(__ldg(bias + n0 + 32 + lane)));
+  float r_mean = 0.f, r_rstd = 1.f;   // deferred LayerNorm: this thread's row
+  if (EPI & (EPI_ROWFOLD | EPI_RESID_LN)) {
+    const float* c1 = (EPI & EPI_ROWFOLD) ? p.fold_c : p.gamma;
+    sts32(smem_u32(sbias) + (64 + lane) * 4, __float_as_uint(__ldg(c1 + n0 + lane)));
+    sts32(smem_u32(sbias) + (96 + lane) * 4, __float_as_uint(__ldg(c1 + n0 + 32 + lane)));
+    if (EPI & EPI_RESID_LN) {
+      sts32(smem_u32(sbias) + (128 + lane) * 4, __float_as_uint(__ldg(p.beta + n0 + lane)));
+      sts32(smem_u32(sbias) + (160 + lane) * 4, __float_as_uint(__ldg(p.beta + n0 + 32 + lane)));
+    }
+    const float4* sp = reinterpret_cast<const float4*>(p.ln_stats_in + (size_t)(m0 + lane) * 2 * p.ln_parts);
+    float s1 = 0.f, s2 = 0.f;
+    for (int i = 0; i < p.ln_parts / 2; ++i) {
+      const float4 t = __ldg(sp + i);
+      s1 += t.x + t.z;
+      s2 += t.y + t.w;
+    }
+    r_mean = s1 * p.ln_inv_n;
+    r_rstd = rsqrtf(fmaxf(fmaf(-r_mean, r_mean, s2 * p.ln_inv_n), 0.f) + p.eps);
+  }
+  float st1 = 0.f, st2 = 0.f;         // EPI_STATS: sums of this thread's 64 stored values
   if (lane == 0) {
     tma_store_wait_read();   // the previous tile's store has finished reading this warp's box
     if (EPI & EPI_BIAS_RESID) {
@@ -218,11 +266,18 @@ B200_DEVINL void gemm_epi_tile(const CUtensorMap& map_out, const CUtensorMap& ma
 #pragma unroll
   for (int j = 0; j < 8; ++j) {   // 8 columns = one 16-byte piece of this thread's row
     const uint4 b0 = lds128(s_bias + j * 32), b1 = lds128(s_bias + j * 32 + 16);
+    const uint32_t bw[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
     float f[8];
-    f[0] = __uint_as_float(v[j * 8 + 0]) + __uint_as_float(b0.x); f[1] = __uint_as_float(v[j * 8 + 1]) + __uint_as_float(b0.y);
-    f[2] = __uint_as_float(v[j * 8 + 2]) + __uint_as_float(b0.z); f[3] = __uint_as_float(v[j * 8 + 3]) + __uint_as_float(b0.w);
-    f[4] = __uint_as_float(v[j * 8 + 4]) + __uint_as_float(b1.x); f[5] = __uint_as_float(v[j * 8 + 5]) + __uint_as_float(b1.y);
-    f[6] = __uint_as_float(v[j * 8 + 6]) + __uint_as_float(b1.z); f[7] = __uint_as_float(v[j * 8 + 7]) + __uint_as_float(b1.w);
+    if (EPI & EPI_ROWFOLD) {
+      const uint4 c0 = lds128(s_bias + 256 + j * 32), c1 = lds128(s_bias + 256 + j * 32 + 16);
+      const uint32_t cw[8] = {c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z, c1.w};
+#pragma unroll
+      for (int i = 0; i < 8; ++i)
+        f[i] = fmaf(r_rstd, fmaf(-r_mean, __uint_as_float(cw[i]), __uint_as_float(v[j * 8 + i])), __uint_as_float(bw[i]));
+    } else {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) f[i] = __uint_as_float(v[j * 8 + i]) + __uint_as_float(bw[i]);
+    }
     if (EPI & EPI_BIAS_GELU) {
 #pragma unroll
       for (int i = 0; i < 8; ++i) f[i] = gelu_erf(f[i]);
@@ -231,10 +286,23 @@ B200_DEVINL void gemm_epi_tile(const CUtensorMap& map_out, const CUtensorMap& ma
     if (EPI & EPI_BIAS_RESID) {
       const uint4 r = lds128(slot);
       const __nv_bfloat162* r2 = reinterpret_cast<const __nv_bfloat162*>(&r);
+      if (EPI & EPI_RESID_LN) {
+        const uint4 g0 = lds128(s_bias + 256 + j * 32), g1 = lds128(s_bias + 256 + j * 32 + 16);
+        const uint4 e0 = lds128(s_bias + 512 + j * 32), e1 = lds128(s_bias + 512 + j * 32 + 16);
+        const uint32_t gw[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
+        const uint32_t ew[8] = {e0.x, e0.y, e0.z, e0.w, e1.x, e1.y, e1.z, e1.w};
 #pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        f[2 * i] += __low2float(r2[i]);
-        f[2 * i + 1] += __high2float(r2[i]);
+        for (int i = 0; i < 4; ++i) {
+          const float a0 = r_rstd * __uint_as_float(gw[2 * i]), a1 = r_rstd * __uint_as_float(gw[2 * i + 1]);
+          f[2 * i] += fmaf(__low2float(r2[i]) - r_mean, a0, __uint_as_float(ew[2 * i]));
+          f[2 * i + 1] += fmaf(__high2float(r2[i]) - r_mean, a1, __uint_as_float(ew[2 * i + 1]));
+        }
+      } else {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          f[2 * i] += __low2float(r2[i]);
+          f[2 * i + 1] += __high2float(r2[i]);
+        }
       }
     }
     uint4 o;
@@ -245,15 +313,22 @@ B200_DEVINL void gemm_epi_tile(const CUtensorMap& map_out, const CUtensorMap& ma
     o.x = *reinterpret_cast<uint32_t*>(&t0); o.y = *reinterpret_cast<uint32_t*>(&t1);
     o.z = *reinterpret_cast<uint32_t*>(&t2); o.w = *reinterpret_cast<uint32_t*>(&t3);
     sts128(slot, o);
-    if (EPI & EPI_HEADNORM) {
+    if (EPI & (EPI_HEADNORM | EPI_STATS)) {
       const __nv_bfloat162 tt[4] = {t0, t1, t2, t3};
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
         const float lo = __low2float(tt[i]), hi = __high2float(tt[i]);
-        head_sq = fmaf(lo, lo, fmaf(hi, hi, head_sq));
+        if (EPI & EPI_HEADNORM) head_sq = fmaf(lo, lo, fmaf(hi, hi, head_sq));
+        if (EPI & EPI_STATS) {
+          st1 += lo + hi;
+          st2 = fmaf(lo, lo, fmaf(hi, hi, st2));
+        }
       }
     }
   }
+  if (EPI & EPI_STATS)
+    *reinterpret_cast<float2*>(p.ln_stats_out + ((size_t)(m0 + lane) * (p.N / GEMM_OUT_CHUNK) + n0 / GEMM_OUT_CHUNK) * 2) =
+        make_float2(st1, st2);
   if (EPI & EPI_HEADNORM) {
     if (n0 < 2 * p.hn_H) {       // Q and K columns (V needs no norm); warp-uniform
       const float mx = warp_max(head_sq);
@@ -311,7 +386,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
   uint64_t* acc_empty = acc_full + 2;          // [2]       epilogue -> MMA     (leader's copy is the one used)
   uint64_t* resid_bar = acc_empty + 2;         // [NEPI]    residual box landed (one per epilogue warp)
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(resid_bar + NEPI);
-  float* bias_smem = reinterpret_cast<float*>(tmem_slot + 4);               // [NEPI][64]
+  float* bias_smem = reinterpret_cast<float*>(tmem_slot + 4);               // [NEPI][gemm_epi_consts(EPI)][64]
 
   const int warp = uniform_warp_idx();
   const int lane = threadIdx.x & 31;
@@ -444,7 +519,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     const int wq = e & 3;         // == warp % 4: the TMEM lane group this warp may read
     const int chunk = e >> 2;
     uint8_t* stg = staging + (size_t)e * GEMM_STAGING_BYTES;
-    float* sbias = bias_smem + e * GEMM_OUT_CHUNK;
+    float* sbias = bias_smem + e * GEMM_OUT_CHUNK * gemm_epi_consts(EPI);
     uint64_t* rbar = &resid_bar[e];
     uint8_t* my_row = stg + lane * 128;
     const int sw = lane & 7;       // 128-byte swizzle: 16-byte chunk j of row r lives at chunk j ^ (r % 8)

@@ -159,6 +159,7 @@ enum Option {
   OPT_SIM_NSPLIT,         // > 0: force the number of corpus slices of the similarity kernel (A/B timing)             (default 0)
   OPT_SEARCH_SCREEN,      // 0: queries the certificate turns down go straight to the full exhaustive pass (no screened pass) (default 1)
   OPT_ATT_NORMS_FUSED,    // 0: a separate kernel re-reads Q and K for the softmax reference of 64-wide heads instead of the QKV epilogue (default 1)
+  OPT_DEFER_LN,           // 0: hidden sizes without the fused GEMM + LayerNorm kernel run a separate LayerNorm pass instead of the deferred form (default 1)
   OPT_COUNT
 };
 int opt(Option o);

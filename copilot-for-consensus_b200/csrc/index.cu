@@ -121,7 +121,7 @@ static const OptDef kOptDefs[OPT_COUNT] = {
     {"att_exact_max", 0, 0, 1}, {"att_turns", 1, 0, 1},      {"att_poly", 1, 0, 4},   {"fuse_ln", 1, 0, 1},
     {"fuse_ffn", 1, 0, 1},      {"serpentine", 1, 0, 1},     {"sim_pair", 1, 0, 1},   {"sim_bound", 3, 0, 3},
     {"sim_refresh_mask", 0, 0, 1023}, {"search_certify", 1, 0, 1}, {"sim_pair_kp", 0, 0, 20}, {"sim_nsplit", 0, 0, 4096},
-    {"search_screen", 1, 0, 1}, {"att_norms_fused", 1, 0, 1},
+    {"search_screen", 1, 0, 1}, {"att_norms_fused", 1, 0, 1}, {"defer_ln", 1, 0, 1},
 };
 static std::atomic<int> g_opts[OPT_COUNT];
 static std::once_flag g_opts_once;

@@ -165,6 +165,42 @@ def test_small_architectures_head_dims():
         p.close()
 
 
+@pytest.mark.parametrize("B,S,mean_shift", [(5, 128, 0.0), (3, 48, 0.0), (4, 256, 3.0)])
+def test_deferred_layernorm_path_768(B, S, mean_shift):
+    """Hidden 768 never writes a LayerNorm output: the GEMMs read the un-normalised rows with gamma folded into the
+    weights and rebuild the residual from per-row statistics (EPI_ROWFOLD / EPI_RESID_LN / EPI_STATS).  Against the
+    fp32 oracle, next to the separate-LayerNorm path (defer_ln=0) on the same input; `mean_shift` adds a constant to
+    the attention output bias of every layer so that the rows being normalised have mean^2 ~ 10x their variance (the
+    statistics are plain sums of y and y^2)."""
+    from safetensors.torch import load_file, save_file
+
+    mio, prov, nat = pkg("embedding.model_io"), pkg("embedding.provider"), pkg("_native")
+    cfg = mio.EncoderConfig(vocab_size=3000, hidden=768, layers=2, heads=12, intermediate=1536, max_pos=512, max_seq_length=512)
+    ocfg = eo.EncoderConfig(vocab_size=3000, hidden=768, layers=2, heads=12, intermediate=1536, max_pos=512)
+    w = eo.make_weights(ocfg, seed=21)
+    with tempfile.TemporaryDirectory() as td:
+        mio.write_random_model(td, cfg, seed=21)
+        if mean_shift:
+            path = td + "/model.safetensors"
+            t = load_file(path)
+            for l in range(2):
+                k = f"encoder.layer.{l}.attention.output.dense.bias"
+                t[k] = t[k] + mean_shift
+                w[k] = w[k] + mean_shift
+            save_file({k: v.contiguous() for k, v in t.items()}, path)
+        p = prov.B200SentenceTransformerProvider(model_name=td, device="cuda:0")
+    ids, mask, lens = eo.synthetic_tokens(B, S, 3000, seed=S + B, ragged=True)
+    ref = eo.encode(ocfg, w, ids, mask).numpy()
+    got = p.embed_tokens(ids.numpy(), lens.numpy())
+    with nat.options(defer_ln=0):
+        plain = p.embed_tokens(ids.numpy(), lens.numpy())
+    _check(plain, ref)
+    _check(got, ref)
+    again = p.embed_tokens(ids.numpy(), lens.numpy())
+    np.testing.assert_array_equal(np.asarray(got), np.asarray(again))      # no atomics in the statistics: run-to-run identical
+    p.close()
+
+
 @pytest.mark.slow
 def test_mpnet_base_class_matches_fp32_oracle():
     """BASELINE.json configs[3] architecture: 768-d, 12 layers, 12 heads x 64, seq 384."""
