@@ -421,8 +421,8 @@ def run_b200(a) -> None:
     roofline["certificate"] = {"queries_checked": chk, "queries_rescored_exhaustively": redo}
 
     # launches of OUR kernels per step: embed+LN, 6 x (QKV GEMM, attention, out-proj GEMM + LayerNorm, fused
-    # feed-forward block + LayerNorm), pool, prep_queries, sim, merge+rescore, the (predicated) exhaustive kernel, K10 merge
-    launches_step = 1 + 6 * 4 + 1 + 4 + (1 if world > 1 else 0)
+    # feed-forward block + LayerNorm), pool, prep_queries, sim, merge+rescore, the two (predicated) exhaustive passes, K10 merge
+    launches_step = 1 + 6 * 4 + 1 + 5 + (1 if world > 1 else 0)
     gpu_launches = launches_step * a.steps
 
     # --- N > 1: the sharded result against ONE index holding every row, outside the timed region ---

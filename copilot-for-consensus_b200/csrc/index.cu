@@ -186,13 +186,13 @@ static constexpr int kMaxQueryChunk = 8192;
 // statistic spacings, so its probability falls like eps^(KP - k): measured 2.4e-4 per query at KP = 16, none in
 // 10^5 queries at KP = 20.  A single query tile (<= 128 queries, the HBM-bound regime) has the issue slots to spare
 // for 20; the CTA-pair kernel (tensor-bound; the larger sets cost it one of its seven pipeline stages) slows down with
-// 20 by 27 % at 1.25 M rows, 9 % at 5 M, 0 - 4 % at 10 - 25 M, 6 % at 50 M (4096 queries), while a re-run of a failing
-// query by the screened exhaustive pass costs 0.03 ms + 0.17 - 0.23 ms per million rows -- and the failure rate itself
-// grows with the shard (neighbours crowd together).  At 50 M rows one re-run per 4096 queries (11.6 ms) already costs
-// more than the slower drain (7.4 ms); below ~25 M it does not.  So 16 below kPairKp20FromRows.
+// 20 by 1.0 ms at 1.25 M rows (27 %), 1.1 ms at 5 M (9 %), ~0 at 10 M, 2.1 ms at 25 M, 7.4 ms at 50 M (4096 queries),
+// while 16 sends 1 - 2 queries of every 4096 to the screened exhaustive pass (0.03 ms + 0.17 - 0.23 ms per million rows
+// each: 0.3 ms at 1.25 M, 1.7 ms at 10 M, 11.6 ms at 50 M) -- measured in bench.py's 10 M-row leg: 2 re-runs per batch,
+// 27.9 ms against 24.2.  The two costs cross near 5 M rows per shard: 16 below kPairKp20FromRows, 20 from there on.
 static constexpr int kKpSmall = 20;
 static constexpr int kKpPair = 16;
-static constexpr int64_t kPairKp20FromRows = 32000000;
+static constexpr int64_t kPairKp20FromRows = 5000000;
 static constexpr int kMaxCandPerQuery = 8192;
 
 static int index_reserve_locked(b200_index* ix, int64_t cap, cudaStream_t st) {
