@@ -601,10 +601,18 @@ def traffic_per_launch(*prefixes: str):
 
 def main():
     a = parse()
+    # The contract is ONE JSON line on stdout.  Libraries write there too (NCCL prints its version banner on fd 1 when
+    # NCCL_DEBUG is set in the environment), so for the duration of the run fd 1 points at stderr and the line goes to
+    # the saved descriptor at the end.
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+    sys.stdout = os.fdopen(real_stdout, "w", buffering=1)
     if a.impl == "reference":
         run_reference(a)
     else:
         run_b200(a)
+    sys.stdout.flush()
 
 
 if __name__ == "__main__":
