@@ -506,6 +506,10 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
         if (blockIdx.x == 0 && lane == 0) {
           const long long g2 = clock64();
           atomicAdd(&g_gemm_timing[1], (unsigned long long)gw);
+          if (tile % n_tiles == 0) {      // first column tile of a row block: its A rows come from HBM
+            atomicAdd(&g_gemm_timing[5], (unsigned long long)gw);
+            atomicAdd(&g_gemm_timing[6], 1ull);
+          }
           atomicAdd(&g_gemm_timing[2], (unsigned long long)(g2 - g1 - gw));
           atomicAdd(&g_gemm_timing[3], 1ull);
           atomicAdd(&g_gemm_timing[4], (unsigned long long)(g2 - g0));

@@ -34,4 +34,6 @@ for defer in (1, 0):
         L.b200_debug_gemm_timing(buf)
         n = max(1, buf[3])
         print("defer_ln=%d flag %d (%s): encode %.3f ms | per tile: wait accumulator %.0f  wait operands %.0f  issue %.0f  total %.0f clk"
-              % (defer, flag, names[flag], e0.elapsed_time(e1) / 5, buf[0] / n, buf[1] / n, buf[2] / n, buf[4] / n), flush=True)
+              " | first column tiles: %d of %d tiles, wait operands %.0f per tile"
+              % (defer, flag, names[flag], e0.elapsed_time(e1) / 5, buf[0] / n, buf[1] / n, buf[2] / n, buf[4] / n,
+                 buf[6], buf[3], buf[5] / max(1, buf[6])), flush=True)
