@@ -403,7 +403,7 @@ static int run_encoder(b200_encoder* e, const int32_t* d_ids, const int32_t* d_l
     if (fold_norms) {
       B200_CUDA(cudaMemsetAsync(e->att_kmax2.p, 0, (size_t)2 * batch * heads * 4, st));
       p.hn_k2 = e->att_kmax2.as<float>(); p.hn_q2 = p.hn_k2 + (size_t)batch * heads;
-      p.hn_S = seq; p.hn_H = H; p.hn_heads = heads;
+      p.hn_S = seq; p.hn_H = H; p.hn_heads = heads; p.hn_rows = n_tok;
     }
     if (defer) {
       p.bias = l == 0 ? L->bqkv.as<float>() : L->bqkv_g.as<float>(); p.fold_c = L->cqkv.as<float>(); p.eps = e->cfg.ln_eps;

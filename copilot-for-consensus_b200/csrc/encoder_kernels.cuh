@@ -175,7 +175,7 @@ struct GemmParams {
   // EPI_HEADNORM: [batch * heads] running maxima (zeroed before the launch), sequence length, hidden size, heads
   float* hn_q2;
   float* hn_k2;
-  int hn_S, hn_H, hn_heads;
+  int hn_S, hn_H, hn_heads, hn_rows;   // hn_rows = batch * S: rows that belong to a sequence
   // deferred LayerNorm: statistic slots [M][ln_parts][2] of the tensor being normalised (ROWFOLD: the A operand,
   // RESID_LN: the residual), 1 / its width, the folded column sums c[N] (ROWFOLD), gamma / beta above (RESID_LN);
   // EPI_STATS: the slots of the tensor being produced ([M][N / 64][2])
@@ -330,7 +330,8 @@ B200_DEVINL void gemm_epi_tile(const CUtensorMap& map_out, const CUtensorMap& ma
     *reinterpret_cast<float2*>(p.ln_stats_out + ((size_t)(m0 + lane) * (p.N / GEMM_OUT_CHUNK) + n0 / GEMM_OUT_CHUNK) * 2) =
         make_float2(st1, st2);
   if (EPI & EPI_HEADNORM) {
-    if (n0 < 2 * p.hn_H) {       // Q and K columns (V needs no norm); warp-uniform
+    if (n0 < 2 * p.hn_H && m0 < p.hn_rows) {   // Q and K columns (V needs no norm) of real tokens (rows past the batch pad the
+                                               // last tile and belong to no sequence); warp-uniform
       const float mx = warp_max(head_sq);
       if (lane == 0) {
         const int is_k = n0 >= p.hn_H;

@@ -218,8 +218,9 @@ def test_wide_head_attention_block_kernel(S, qk_scale, exact_max, B):
     Cauchy-Schwarz reference).  Both of its scripts against the fp32 oracle: the bound script (random-init weights), the
     exact-maximum script forced by the option, and the exact script chosen by att_norms_kernel itself when query / key
     weights are scaled until the bound is unusable; ragged lengths put padding inside and across key blocks.
-    With whole 256-token tiles (B * S % 256 == 0) the key / query norms behind that decision come from the QKV
-    projection's epilogue instead of att_norms_kernel (same maxima up to the summation order), and both ways are checked."""
+    The key / query norms behind that decision come from the QKV projection's epilogue instead of att_norms_kernel (same
+    maxima up to the summation order; rows that pad the last 256-token tile -- B * S not a multiple of 256 -- must stay out
+    of them), and both ways are checked."""
     from safetensors.torch import load_file, save_file
 
     mio, prov, nat = pkg("embedding.model_io"), pkg("embedding.provider"), pkg("_native")
