@@ -186,13 +186,13 @@ static constexpr int kMaxQueryChunk = 8192;
 // statistic spacings, so its probability falls like eps^(KP - k): measured 2.4e-4 per query at KP = 16, none in
 // 10^5 queries at KP = 20.  A single query tile (<= 128 queries, the HBM-bound regime) has the issue slots to spare
 // for 20; the CTA-pair kernel (tensor-bound; the larger sets cost it one of its seven pipeline stages) slows down with
-// 20 by 1.0 ms at 1.25 M rows (27 %), 1.1 ms at 5 M (9 %), ~0 at 10 M, 2.1 ms at 25 M, 7.4 ms at 50 M (4096 queries),
+// 20 by 0.54 ms at 1.25 M rows (19 %), 0.2 ms at 5 - 10 M (1 - 2 %), 0.4 ms at 25 M, 3.2 ms at 50 M (4096 queries),
 // while 16 sends 1 - 2 queries of every 4096 to the screened exhaustive pass (0.03 ms + 0.17 - 0.23 ms per million rows
-// each: 0.3 ms at 1.25 M, 1.7 ms at 10 M, 11.6 ms at 50 M) -- measured in bench.py's 10 M-row leg: 2 re-runs per batch,
-// 27.9 ms against 24.2.  The two costs cross near 5 M rows per shard: 16 below kPairKp20FromRows, 20 from there on.
+// each: 0.3 ms at 1.25 M, 1.7 ms at 10 M, 11.3 ms at 50 M) -- measured in bench.py's 10 M-row leg: 2 re-runs per batch,
+// 27.9 ms against 24.2.  The two costs cross near 2 M rows per shard: 16 below kPairKp20FromRows, 20 from there on.
 static constexpr int kKpSmall = 20;
 static constexpr int kKpPair = 16;
-static constexpr int64_t kPairKp20FromRows = 5000000;
+static constexpr int64_t kPairKp20FromRows = 2500000;
 static constexpr int kMaxCandPerQuery = 8192;
 
 static int index_reserve_locked(b200_index* ix, int64_t cap, cudaStream_t st) {
@@ -1124,3 +1124,11 @@ extern "C" int b200_index_search_static(b200_index_t* ix, const void* queries_de
                            std::min(ix->num_sms, kStaticExactGrid)));
   return B200_OK;
 }
+
+#ifdef B200_K8_TIMING
+extern "C" int b200_debug_k8_timing(unsigned long long* out) {
+  cudaDeviceSynchronize();
+  cudaMemcpyFromSymbol(out, b200::g_k8_timing, 128 * sizeof(unsigned long long));
+  return 0;
+}
+#endif

@@ -249,26 +249,74 @@ B200_DEVINL uint64_t pack_key(float s, uint32_t id) {
   return ((uint64_t)f32_orderable(s) << 32) | (uint64_t)(~id);
 }
 
+// v[j] for a run-time j without sending the array to local memory: a binary tree of selects (31 of them)
+B200_DEVINL float pick32(const uint32_t (&v)[32], int j) {
+  uint32_t a[16], b[8], c[4], d[2];
+#pragma unroll
+  for (int i = 0; i < 16; ++i) a[i] = (j & 16) ? v[16 + i] : v[i];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) b[i] = (j & 8) ? a[8 + i] : a[i];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) c[i] = (j & 4) ? b[4 + i] : b[i];
+#pragma unroll
+  for (int i = 0; i < 2; ++i) d[i] = (j & 2) ? c[2 + i] : c[i];
+  return __uint_as_float((j & 1) ? d[1] : d[0]);
+}
+
 // One query's candidate set: KP unsorted keys in shared memory (a thread-private row) plus the
 // position of the current worst one.  A new candidate overwrites the worst, then the worst is
-// found again with KP independent loads -- no shifting, so an insert costs ~4*KP instructions
-// whatever its rank (a sorted list made inserts the bottleneck once every TMEM lane carries a live
-// query).  Rows arrive in ascending order and the caller only inserts when score > worst score, so
-// among equal scores the earlier row stays: the reference's stable-sort tie rule (inmemory.py:118).
+// found again -- no shifting, so an insert costs the same whatever its rank (a sorted list made
+// inserts the bottleneck once every TMEM lane carries a live query).  Rows arrive in ascending order
+// and the caller only inserts when score > worst score, so among equal scores the earlier row stays:
+// the reference's stable-sort tie rule (inmemory.py:118).
+// The worst key is the lowest score, then the highest row.  Scores decide it almost always, so only the keys'
+// HIGH words are loaded (shared-space loads: through a generic pointer the compiler emitted generic LD / ST), their
+// minimum comes from a tree of 32-bit min (one instruction per node; the 64-bit compare-and-select with index tracking
+// was nine), and the low words are looked at only when two kept rows share the lowest score.  ~90 instructions per
+// insert instead of 175 -- the drain warp is alone on its SM sub-partition, so instructions are what an insert costs.
+// `keys_s` = shared-space byte address of the KP keys.
 // Returns (float bits of the worst score, -inf while the set is not full) << 32 | worst position.
 template <int KP>
-__device__ __noinline__ uint64_t topk_replace_worst(uint64_t* keys, int wpos, float s, uint32_t id) {
-  keys[wpos] = pack_key(s, id);
-  uint64_t w = keys[0];
-  int wp = 0;
+__device__ __noinline__ uint64_t topk_replace_worst(uint32_t keys_s, int wpos, float s, uint32_t id) {
+  asm volatile("st.shared.v2.u32 [%0], {%1, %2};" ::"r"(keys_s + (uint32_t)wpos * 8u), "r"(~id), "r"(f32_orderable(s)) : "memory");
+  uint32_t h[KP], m[KP];
 #pragma unroll
-  for (int i = 1; i < KP; ++i) {
-    const uint64_t k = keys[i];
-    if (k < w) { w = k; wp = i; }
+  for (int i = 0; i < KP; ++i) {
+    h[i] = lds32(keys_s + (uint32_t)i * 8u + 4u);
+    m[i] = h[i];
   }
-  const float thr = w ? orderable_f32((uint32_t)(w >> 32)) : -INFINITY;
+#pragma unroll
+  for (int stride = 1; stride < KP; stride <<= 1) {
+#pragma unroll
+    for (int i = 0; i + stride < KP; i += 2 * stride) m[i] = min(m[i], m[i + stride]);
+  }
+  const uint32_t whi = m[0];
+  // positions that hold the minimum, as a bit mask (two words: KP goes up to 64), built from independent partial masks
+  uint32_t eq4[4] = {0u, 0u, 0u, 0u};
+#pragma unroll
+  for (int i = 0; i < KP; ++i) eq4[(i >> 5) * 2 + (i & 1)] |= (h[i] == whi ? 1u : 0u) << (i & 31);
+  const uint64_t eq = ((uint64_t)(eq4[2] | eq4[3]) << 32) | (eq4[0] | eq4[1]);
+  int wp = __ffsll((long long)eq) - 1;
+  if (whi != 0 && (eq & (eq - 1ull)) != 0) {    // several kept rows with this score (not empty slots: any of those will do)
+    uint32_t wlo = 0xFFFFFFFFu;
+    for (uint64_t e = eq; e; e &= e - 1ull) {
+      const int i = __ffsll((long long)e) - 1;
+      const uint32_t lo = lds32(keys_s + (uint32_t)i * 8u);
+      if (lo <= wlo) {                           // low word = ~row: the highest row is the worst
+        wlo = lo;
+        wp = i;
+      }
+    }
+  }
+  const float thr = whi ? orderable_f32(whi) : -INFINITY;
   return ((uint64_t)__float_as_uint(thr) << 32) | (uint32_t)wp;
 }
+
+#ifdef B200_K8_TIMING
+// Development aid (not compiled into the shipped library): per corpus tile of CTA 0, the clocks its first drain warp
+// spends scanning the accumulators ([t], t < 48) and waiting for them ([64 + t]).
+__device__ unsigned long long g_k8_timing[128];
+#endif
 
 // CG = 1: one CTA per (query tile, corpus slice).  CG = 2: a CTA pair (cluster of 2, cta_group::2)
 // per (two query tiles, corpus slice): each CTA keeps its own 128 queries resident and loads only
@@ -427,6 +475,7 @@ sim_topk_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant
     const int row = wq * 32 + lane;
     const int qg = qtile * SIM_BLOCK_M + row;
     uint64_t* my_keys = ckeys + row * (KP + 1);      // odd stride in 8-byte words: conflict-free
+    const uint32_t my_keys_s = smem_u32(my_keys);
     int wpos = 0;
     const bool live = qg < p.nq;
     // thr = max(score of this CTA's own worst kept candidate, just below the cross-CTA bound).
@@ -469,8 +518,14 @@ sim_topk_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant
           thr = fmaxf(thr, below);
         }
       }
+#ifdef B200_K8_TIMING
+      const long long kt0 = clock64();
+#endif
       mbar_wait(&acc_full[as], aph);
       tc_fence_after();
+#ifdef B200_K8_TIMING
+      const long long kt1 = clock64();
+#endif
       const uint32_t taddr = tmem_base + ((uint32_t)(wq * 32) << 16) + as * BLOCK_N;
       const uint32_t col0 = (tile0 + t) * BLOCK_N;
       // Software-pipelined drain: the tcgen05.ld of chunk c+1 is in flight while chunk c is
@@ -494,9 +549,8 @@ sim_topk_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant
               if (CG == 2) mbar_arrive_leader(&acc_empty[as]); else mbar_arrive(&acc_empty[as]);
             }
           }
-          // maxima of the chunk's four 8-column groups (independent chains: the one drain warp of an
-          // SM sub-partition has nobody to hide a 31-deep FMNMX chain behind); the insert path below
-          // only walks the groups that actually hold a candidate
+          // maximum of the chunk by four independent chains (the one drain warp of an SM sub-partition has nobody to hide
+          // a 31-deep FMNMX chain behind)
           float g[4];
 #pragma unroll
           for (int q4 = 0; q4 < 4; ++q4) {
@@ -508,32 +562,42 @@ sim_topk_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant
           }
           const float m = fmaxf(fmaxf(g[0], g[1]), fmaxf(g[2], g[3]));
           if (m > thr) {
+            // Insert path.  Every lane makes the bit mask of ITS columns above the threshold and then pops them in
+            // ascending order, so the warp runs max-over-lanes(popcount) rounds of ONE compact loop body.  (The first
+            // version walked the 32 columns in straight-line code, one predicated insert per column: while a CTA's sets
+            // warm up nearly every column has some lane above its threshold, and 32 call sites per chunk did not fit the
+            // instruction cache -- the first tile of every CTA took 150 k clocks, ~600 per column.)
             const uint32_t base = col0 + c * 32;
+            uint32_t mask = 0;
 #pragma unroll
-            for (int q4 = 0; q4 < 4; ++q4) {
-              if (g[q4] > thr) {
-#pragma unroll
-                for (int jj = 0; jj < 8; ++jj) {
-                  const int j = q4 * 8 + jj;
-                  const float s = __uint_as_float(v[u][j]);
-                  if (s > thr && base + j < p.n_rows) {
-                    const uint64_t r = topk_replace_worst<KP>(my_keys, wpos, s, base + j);
-                    thr_own = __uint_as_float((uint32_t)(r >> 32));
-                    wpos = (int)(uint32_t)r;
-                    thr = fmaxf(thr, thr_own);
-                    if (p.use_gthr && thr_own > -INFINITY) atomicMax(p.gthr + qg, f32_orderable(thr_own));   // set is full
-                    const uint32_t os = f32_orderable(s);
-                    if (os > bkt_best) {
-                      bkt_best = os;
-                      atomicMax(my_bkt + bkt, os);
-                    }
-                  }
+            for (int j = 0; j < 32; ++j) mask |= (__uint_as_float(v[u][j]) > thr ? 1u : 0u) << j;
+            if (base + 32 > p.n_rows) mask &= base < p.n_rows ? (1u << (p.n_rows - base)) - 1u : 0u;   // rows past the end
+            while (mask) {
+              const int j = __ffs(mask) - 1;
+              mask &= mask - 1;
+              const float s = pick32(v[u], j);
+              if (s > thr) {                      // the threshold has moved since the mask was made
+                const uint64_t r = topk_replace_worst<KP>(my_keys_s, wpos, s, base + j);
+                thr_own = __uint_as_float((uint32_t)(r >> 32));
+                wpos = (int)(uint32_t)r;
+                thr = fmaxf(thr, thr_own);
+                if (p.use_gthr && thr_own > -INFINITY) atomicMax(p.gthr + qg, f32_orderable(thr_own));   // set is full
+                const uint32_t os = f32_orderable(s);
+                if (os > bkt_best) {
+                  bkt_best = os;
+                  atomicMax(my_bkt + bkt, os);
                 }
               }
             }
           }
         }
       }
+#ifdef B200_K8_TIMING
+      if (blockIdx.x == 0 && warp == 4 && lane == 0 && t < 48) {
+        g_k8_timing[t] = (unsigned long long)(clock64() - kt1);
+        g_k8_timing[64 + t] = (unsigned long long)(kt1 - kt0);
+      }
+#endif
     }
     // this split's candidates for this query
     if (qg < p.nq) {
