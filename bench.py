@@ -406,7 +406,7 @@ def run_b200(a) -> None:
                     "frac_burst": ach / pk["tf_burst"], "frac_sustained": ach / pk["tf_sustained"],
                     "peak_source": pk["source"] + (" (burst bf16 GEMM: the timed region is %.2f s)" % timed_region_s if use_burst
                                                    else " (sustained bf16 GEMM: kernels timed inside a long run)"),
-                    "flop_per_launch": g_fl / g_n, "ms_per_launch": g_ms / g_n, "traffic": traffic_per_launch("gemm_", "ffn_"),
+                    "flop_per_launch": g_fl / g_n, "ms_per_launch": g_ms / g_n, "traffic": traffic_per_launch("gemm_bf16_ast_kernel", "gemm_ln_kernel", "ffn_fused_kernel"),
                     "profiled_ms_per_step": tot_ms / 3, "timed_ms_per_step": ms_step}
     sim = prof.get("sim_topk")
     if sim and sim["ms"] > 0:
@@ -465,7 +465,7 @@ def run_b200(a) -> None:
             rows_rank = len(big)
             s10 = {"rows_global": n_big, "rows_per_gpu": rows_rank, "algorithmic_bytes_per_pass_per_gpu": rows_rank * 768,
                    "traffic": {"single_tile_kernel_128_queries": traffic_per_launch("sim_topk_kernel<256, 20, 1>"),
-                               "cta_pair_kernel_4096_queries": traffic_per_launch("sim_topk_kernel<256, 16, 2>"),
+                               "cta_pair_kernel_4096_queries": traffic_per_launch("sim_topk_kernel<256, 20, 2>"),
                                "note": "dram bytes per launch over ALL 10 M rows on one GPU (profiles/r02_ncu_search.md); algorithmic = 7.68e9"},
                    "exchange": bs.exchange,
                    "api": "ShardedSearch.search_replicated: b200_index_search_exchange (hit records stored into NVLink peer memory) -> "

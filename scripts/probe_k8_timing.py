@@ -7,12 +7,12 @@ vs = importlib.import_module(P + ".vectorstore"); nat = importlib.import_module(
 L = nat.lib()
 dev = torch.device("cuda", 0)
 g = torch.Generator(device=dev).manual_seed(1)
-n = 1_250_000
+n = int(sys.argv[1]) if len(sys.argv) > 1 else 1_250_000
 ix = vs.B200Index(384, device=0, master_dtype="bfloat16", capacity=n)
 for c0 in range(0, n, 1 << 20):
     ix.add(torch.randn((min(1 << 20, n - c0), 384), generator=g, device=dev).bfloat16().contiguous())
 buf = (ctypes.c_ulonglong * 128)()
-for nq in (1, 32, 128):
+for nq in ([int(x) for x in sys.argv[2].split(',')] if len(sys.argv) > 2 else (1, 32, 128)):
     q = torch.randn((nq, 384), generator=g, device=dev).bfloat16().contiguous()
     for _ in range(3): ix.search(q, 10)
     L.b200_debug_k8_timing(buf)

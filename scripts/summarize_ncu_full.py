@@ -54,6 +54,8 @@ def main():
                 u = units[col[m]]
                 if "MB" in lbl:
                     f = f * {"Kbyte": 1e-3, "Mbyte": 1.0, "Gbyte": 1e3, "byte": 1e-6}.get(u, 1.0)
+                if lbl == "us":      # ncu picks one unit per column (ms when a long kernel is in the report)
+                    f = f * {"ns": 1e-3, "nsecond": 1e-3, "us": 1.0, "usecond": 1.0, "ms": 1e3, "msecond": 1e3, "s": 1e6, "second": 1e6}.get(u, 1.0)
                 cells.append("%.1f" % f if abs(f) < 1e5 and f != int(f) else "%d" % f)
             except ValueError:
                 cells.append(v)
