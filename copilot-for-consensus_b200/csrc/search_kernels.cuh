@@ -637,6 +637,31 @@ B200_DEVINL void bitonic_sort_desc(uint64_t* keys, int n) {
   }
 }
 
+// The same network for exactly 64 keys, run by ONE warp (32 compare-exchanges per stage = one per lane): the CTA-wide
+// version spends eight warps' worth of loop and barrier instructions on it, and K9 -- 13 k warp instructions per
+// query -- is bound by instruction issue.  Every thread of the CTA calls it; ends with __syncthreads.
+B200_DEVINL void bitonic_sort_desc64_one_warp(uint64_t* keys) {
+  if (threadIdx.x < 32) {
+    const int lane = threadIdx.x;
+#pragma unroll
+    for (int k = 2; k <= 64; k <<= 1) {
+#pragma unroll
+      for (int j = k >> 1; j > 0; j >>= 1) {
+        const int i = ((lane & ~(j - 1)) << 1) | (lane & (j - 1));
+        const int l = i | j;
+        const uint64_t a = keys[i], b = keys[l];
+        const bool desc = (i & k) == 0;
+        if (desc ? (a < b) : (a > b)) {
+          keys[i] = b;
+          keys[l] = a;
+        }
+        __syncwarp();
+      }
+    }
+  }
+  __syncthreads();
+}
+
 // ---------------------------------------------------------------------------------------------
 // K9: one CTA per query.
 //   1. gather nsplit*KP (approx score, row) candidates as 64-bit keys (score desc, row asc),
@@ -719,7 +744,9 @@ __global__ void __launch_bounds__(256) merge_rescore_kernel(const MergeParams p)
   __syncthreads();
   for (int i = threadIdx.x; i < p.d; i += blockDim.x) qh[i] = __fdiv_rn(qraw[i], s_den);
   for (int i = threadIdx.x; i < 64; i += blockDim.x) fin[i] = 0;
-  bitonic_sort_desc(keys, npow2);  // ends with __syncthreads
+  __syncthreads();                 // keys[], qh[] and fin[] are written
+  if (npow2 == 64) bitonic_sort_desc64_one_warp(keys);
+  else bitonic_sort_desc(keys, npow2);  // both end with __syncthreads
 
   for (int c = warp; c < p.kp; c += nwarp) {
     const uint64_t key = keys[c];
@@ -733,7 +760,7 @@ __global__ void __launch_bounds__(256) merge_rescore_kernel(const MergeParams p)
     if (lane == 0) fin[c] = pack_key(s, id);
   }
   __syncthreads();
-  bitonic_sort_desc(fin, 64);
+  bitonic_sort_desc64_one_warp(fin);
   // Certificate.  K8 ranked rows by s16(v) = q16 . v16 (tensor cores, fp32 accumulate) and every row
   // outside the KP survivors has s16 <= A, the KP-th best.  In cosine units (x inv_scale), for any row v
   //   exact(v) - s16(v) = q_hat.(v_hat - v16) + (q_hat - q16').v16 + (evaluation error of both sides)
