@@ -132,6 +132,31 @@ def current_stream_ptr(device_ordinal: int) -> int:
     return 0
 
 
+_PINNED_MAX_BYTES = 64 << 20
+
+
+def host_out(shape, dtype):
+    """A numpy array for a result the library copies back from the GPU.  Page-locked when torch can provide it (its
+    caching host allocator recycles the blocks of arrays that have been dropped, so after the first calls this costs
+    microseconds): the device-to-host copy then runs at the DMA rate instead of being staged through the driver's bounce
+    buffer, and so does the host-to-device copy when the caller hands the same array back (embeddings -> query).  A
+    fresh array per call, like ``np.empty``; plain pageable memory for results over 64 MB or without torch."""
+    import numpy as np
+
+    nbytes = int(np.prod(shape)) * np.dtype(dtype).itemsize
+    if 0 < nbytes <= _PINNED_MAX_BYTES:
+        try:
+            import torch
+
+            if torch.cuda.is_available():
+                tdt = {"float32": torch.float32, "int64": torch.int64, "int32": torch.int32}.get(np.dtype(dtype).name)
+                if tdt is not None:
+                    return torch.empty(tuple(int(x) for x in shape), dtype=tdt, pin_memory=True).numpy()
+        except Exception:
+            pass
+    return np.empty(shape, dtype=dtype)
+
+
 def set_option(name: str, value: int) -> None:
     """Process-wide kernel-variant switch (``b200_set_option``); see the header for names and defaults."""
     check(lib().b200_set_option(name.encode(), int(value)))
