@@ -184,7 +184,7 @@ class WordPieceTokenizer:
         n = len(texts)
         ids = np.full((n, max_length), self.pad_id, dtype=np.int32)
         lens = np.zeros(n, dtype=np.int32)
-        nat_h = self._native_handle() if n >= 4 and max_length >= 2 and self.max_chars_per_word == 100 else None
+        nat_h = self._native_handle() if n >= 1 and max_length >= 2 and self.max_chars_per_word == 100 else None
         if nat_h is None:
             todo = range(n)
         else:
