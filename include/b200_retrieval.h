@@ -105,7 +105,7 @@ int b200_index_get_rows(b200_index_t* idx, const int64_t* rows_host, int64_t n, 
  * query at a time -- same ids, order and scores, HBM-bound on the master copy.
  *
  * Exactness.  The reference scores EVERY row exactly (inmemory.py:111-119).  The fused path ranks rows by a
- * 16-bit tensor-core score, keeps KP = 20 (16 in batches of more than 128 queries) / 32 / 64 candidates per query (k <= 10 / 24 / 48) and rescores those
+ * 16-bit tensor-core score, keeps KP = 20 (16 in batches of more than 128 queries over fewer than 2.5 M rows) / 32 / 64 candidates per query (k <= 10 / 24 / 48) and rescores those
  * exactly.  It then proves, per query, that no other row can belong to the exact top-k: every row outside the
  * candidates has a 16-bit score <= A (the KP-th best), its exact score can exceed that by at most
  * eps = r_v + r_q (1 + r_v) + slop (r_v: largest rounding distance of any stored row, tracked at insert;
