@@ -416,6 +416,29 @@ def run_b200(a) -> None:
         roofline["search_step"] = {"queries_per_pass": q_per_pass, "rows_per_shard": len(index), "ms_per_launch": sim["ms"] / sim["launches"],
                                    "tflops": tf, "frac_tensor_burst": tf / pk["tf_burst"], "frac_tensor_sustained": tf / pk["tf_sustained"],
                                    "gbs": gbs, "frac_hbm": gbs / pk["hbm_gbs"], "bound": "tensor" if q_per_pass > 212 else "hbm"}
+        # The step searches the embeddings a RANDOM-INIT encoder produces, and those are nearly parallel to one another:
+        # the 32 queries a drain warp serves then pass their thresholds at the same corpus columns, which is the cheapest
+        # case for the fused select.  The same launch with independent random unit queries (what a trained model's
+        # embeddings of different texts look like to this kernel) is reported beside it.
+        try:
+            gq = torch.Generator(device=dev).manual_seed(4242 + rank)
+            q_ind = torch.randn((q_per_pass, 384), generator=gq, device=dev, dtype=torch.float32)
+            q_ind = (q_ind / q_ind.norm(dim=1, keepdim=True)).contiguous()
+            for _ in range(2):
+                index.search(q_ind, a.top_k, id_base=r0)
+            torch.cuda.synchronize()
+            nat.profile(True)
+            for _ in range(5):
+                index.search(q_ind, a.top_k, id_base=r0)
+            torch.cuda.synchronize()
+            p2 = nat.profile_read()
+            nat.profile(False)
+            roofline["search_step"]["ms_per_launch_independent_queries"] = p2["sim_topk"]["ms"] / p2["sim_topk"]["launches"]
+            roofline["search_step"]["note"] = ("ms_per_launch is for the step's own queries (embeddings of a random-init encoder, nearly "
+                                               "parallel); ms_per_launch_independent_queries is the same launch with independent random unit queries")
+        except Exception as exc:  # noqa: BLE001
+            roofline["search_step"]["ms_per_launch_independent_queries"] = None
+            roofline["search_step"]["note"] = str(exc)[:200]
     roofline["whole_encode_tflops"] = FLOP_PER_CHUNK * a.batch / (ms_step * 1e-3) / 1e12
     chk, redo = index.certificate_stats()
     roofline["certificate"] = {"queries_checked": chk, "queries_rescored_exhaustively": redo}

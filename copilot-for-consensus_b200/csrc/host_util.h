@@ -160,6 +160,7 @@ enum Option {
   OPT_SEARCH_SCREEN,      // 0: queries the certificate turns down go straight to the full exhaustive pass (no screened pass) (default 1)
   OPT_ATT_NORMS_FUSED,    // 0: a separate kernel re-reads Q and K for the softmax reference of 64-wide heads instead of the QKV epilogue (default 1)
   OPT_DEFER_LN,           // 0: hidden sizes without the fused GEMM + LayerNorm kernel run a separate LayerNorm pass instead of the deferred form (default 1)
+  OPT_SIM_DRAIN,          // drain groups of the CTA-pair similarity kernel: 1 / 2 force, 0 = by shard size (default 0)
   OPT_COUNT
 };
 int opt(Option o);

@@ -121,7 +121,7 @@ static const OptDef kOptDefs[OPT_COUNT] = {
     {"att_exact_max", 0, 0, 1}, {"att_turns", 1, 0, 1},      {"att_poly", 1, 0, 4},   {"fuse_ln", 1, 0, 1},
     {"fuse_ffn", 1, 0, 1},      {"serpentine", 1, 0, 1},     {"sim_pair", 1, 0, 1},   {"sim_bound", 3, 0, 3},
     {"sim_refresh_mask", 0, 0, 1023}, {"search_certify", 1, 0, 1}, {"sim_pair_kp", 0, 0, 20}, {"sim_nsplit", 0, 0, 4096},
-    {"search_screen", 1, 0, 1}, {"att_norms_fused", 1, 0, 1}, {"defer_ln", 1, 0, 1},
+    {"search_screen", 1, 0, 1}, {"att_norms_fused", 1, 0, 1}, {"defer_ln", 1, 0, 1}, {"sim_drain", 0, 0, 2},
 };
 static std::atomic<int> g_opts[OPT_COUNT];
 static std::once_flag g_opts_once;
@@ -194,6 +194,8 @@ static constexpr int kKpSmall = 20;
 static constexpr int kKpPair = 16;
 static constexpr int64_t kPairKp20FromRows = 2500000;
 static constexpr int kMaxCandPerQuery = 8192;
+// shards below this many rows run the CTA-pair similarity kernel with two drain groups (see sim_topk_kernel, DR)
+static constexpr int64_t kDualDrainBelowRows = 2000000;
 
 static int index_reserve_locked(b200_index* ix, int64_t cap, cudaStream_t st) {
   if (cap <= ix->capacity) return B200_OK;
@@ -207,11 +209,13 @@ static int index_reserve_locked(b200_index* ix, int64_t cap, cudaStream_t st) {
 }
 
 // CG = 2 runs CTA pairs (two query tiles per cluster); nqt is then the even number of query tiles.
-template <int BLOCK_N, int KP, int CG>
+// DR = 2: two drain groups per CTA (see sim_topk_kernel); the launch then hands K9 nsplit * DR candidate lists per query,
+// which is what `used->nsplit` reports.
+template <int BLOCK_N, int KP, int CG, int DR = 1>
 static int launch_sim(b200_index* ix, int nq, int nqt, const CUtensorMap& map_q, cudaStream_t st, SimParams* used) {
   const int kc = ix->dpad / SIM_BLOCK_K;
   const size_t a_bytes = (size_t)kc * SIM_A_CHUNK_BYTES;
-  const size_t list_bytes = (size_t)SIM_BLOCK_M * (KP + 1) * 8;
+  const size_t list_bytes = (size_t)DR * SIM_BLOCK_M * (KP + 1) * 8;
   const size_t stage_bytes = (size_t)(BLOCK_N / CG) * SIM_BLOCK_K * 2;
   size_t fixed = 1024 + a_bytes + list_bytes + 256;
   size_t stage_total = stage_bytes;
@@ -234,7 +238,7 @@ static int launch_sim(b200_index* ix, int nq, int nqt, const CUtensorMap& map_q,
   // Split the corpus so that (query tiles x splits) fills whole waves of SMs.  Cost model: every
   // CTA walks tiles_per_split tiles plus a fixed prologue worth ~2 tiles (query-tile load, TMEM
   // allocation, list write-out); waves run back to back.
-  const int max_split = std::max(1, std::min<int>((int)std::min<uint32_t>(total_tiles, 65535u), kMaxCandPerQuery / KP));
+  const int max_split = std::max(1, std::min<int>((int)std::min<uint32_t>(total_tiles, 65535u), kMaxCandPerQuery / (KP * DR)));
   int best = 1;
   double best_cost = 1e300;
   for (int w = 1; w <= 12; ++w) {
@@ -252,7 +256,7 @@ static int launch_sim(b200_index* ix, int nq, int nqt, const CUtensorMap& map_q,
   const uint32_t tps = (total_tiles + nsplit - 1) / nsplit;
   nsplit = (int)((total_tiles + tps - 1) / tps);
 
-  const size_t cand_n = (size_t)nqt * SIM_BLOCK_M * nsplit * KP;
+  const size_t cand_n = (size_t)nqt * SIM_BLOCK_M * nsplit * KP * DR;
   B200_TRY(ix->cand.grow(cand_n * 8, 0, st));
   // [nq_pad][KP] bucket bests followed by [nq_pad] single-CTA bounds; both start at "none"
   const size_t bkt_words = (size_t)nqt * SIM_BLOCK_M * (KP + 1);
@@ -276,7 +280,7 @@ static int launch_sim(b200_index* ix, int nq, int nqt, const CUtensorMap& map_q,
     p.use_bound = (m & 1) && (int)tps >= p.bkt_per_cta;
     p.use_gthr = ((m >> 1) & 1) && ((long)nsplit * units > slots || !p.use_bound);
   }
-  auto kern = sim_topk_kernel<BLOCK_N, KP, CG>;
+  auto kern = sim_topk_kernel<BLOCK_N, KP, CG, DR>;
   B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   {
     // algorithmic work of one pass: every corpus row read once (768 B at dim 384) and 2*dpad flops
@@ -285,7 +289,7 @@ static int launch_sim(b200_index* ix, int nq, int nqt, const CUtensorMap& map_q,
     if (CG == 2) {
       cudaLaunchConfig_t cfg{};
       cfg.gridDim = dim3(nqt, nsplit);          // consecutive blockIdx.x = the two CTAs of a pair
-      cfg.blockDim = dim3(SIM_THREADS);
+      cfg.blockDim = dim3(sim_threads(DR));
       cfg.dynamicSmemBytes = smem;
       cfg.stream = st;
       cudaLaunchAttribute attr[1];
@@ -294,11 +298,12 @@ static int launch_sim(b200_index* ix, int nq, int nqt, const CUtensorMap& map_q,
       cfg.attrs = attr; cfg.numAttrs = 1;
       B200_CUDA(cudaLaunchKernelEx(&cfg, kern, map_q, map_c, p));
     } else {
-      kern<<<dim3(nqt, nsplit), SIM_THREADS, smem, st>>>(map_q, map_c, p);
+      kern<<<dim3(nqt, nsplit), sim_threads(DR), smem, st>>>(map_q, map_c, p);
     }
   }
   B200_CUDA(cudaGetLastError());
   *used = p;
+  used->nsplit = nsplit * DR;      // candidate lists per query, as K9 sees them
   return B200_OK;
 }
 
@@ -388,7 +393,12 @@ static int search_chunk(b200_index* ix, const void* q_dev, int q_dtype, int nq, 
   CUtensorMap map_q;
   B200_TRY(make_tma_2d_bf16(&map_q, ix->q16.p, (uint64_t)nq_pad, (uint64_t)ix->dpad, SIM_BLOCK_M, SIM_BLOCK_K));
   SimParams sp{};
-  if (pair && kp == kKpPair) B200_TRY((launch_sim<256, kKpPair, 2>(ix, nq, nqt, map_q, st, &sp)));
+  // two drain groups per CTA on small shards, where the warm-up of the candidate sets is a large share of the launch
+  // (option sim_drain: 1 / 2 force it; A/B timing)
+  const bool dual = pair && (opt(OPT_SIM_DRAIN) == 2 || (opt(OPT_SIM_DRAIN) == 0 && ix->count < kDualDrainBelowRows));
+  if (dual && kp == kKpPair) B200_TRY((launch_sim<256, kKpPair, 2, 2>(ix, nq, nqt, map_q, st, &sp)));
+  else if (dual) B200_TRY((launch_sim<256, kKpSmall, 2, 2>(ix, nq, nqt, map_q, st, &sp)));
+  else if (pair && kp == kKpPair) B200_TRY((launch_sim<256, kKpPair, 2>(ix, nq, nqt, map_q, st, &sp)));
   else if (pair) B200_TRY((launch_sim<256, kKpSmall, 2>(ix, nq, nqt, map_q, st, &sp)));
   else if (kp == kKpSmall) B200_TRY((launch_sim<256, kKpSmall, 1>(ix, nq, nqt, map_q, st, &sp)));
   else if (kp == 32) B200_TRY((launch_sim<128, 32, 1>(ix, nq, nqt, map_q, st, &sp)));

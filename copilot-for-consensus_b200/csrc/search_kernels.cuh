@@ -28,6 +28,9 @@ namespace b200 {
 constexpr int SIM_BLOCK_M = 128;   // queries per CTA = TMEM lanes
 constexpr int SIM_BLOCK_K = 64;    // 16-bit elements per 128-byte swizzle row
 constexpr int SIM_THREADS = 256;   // warp 0 TMA, 1 MMA, 2 TMEM alloc, 3 idle, 4..7 drain/select
+// DR = 2 adds warps 8..11 as a second drain group: each group scans half of every tile's columns into its own candidate
+// sets, so every SM sub-partition has two drain warps to hide one another's insert latency (see sim_topk_kernel)
+constexpr int sim_threads(int dr) { return 128 + 128 * dr; }
 constexpr int SIM_A_CHUNK_BYTES = SIM_BLOCK_M * SIM_BLOCK_K * 2;
 constexpr uint32_t kNoRow = 0xFFFFFFFFu;
 
@@ -324,10 +327,20 @@ __device__ unsigned long long g_k8_timing[128];
 // drains the scores of its own queries from its own TMEM.  Half the corpus bytes per SM per flop
 // means the same shared-memory ring hides twice the latency and the L2 -> SM path carries half the
 // traffic -- the two things that kept the single-CTA kernel at ~60 % of the tensor roofline.
-template <int BLOCK_N, int KP, int CG>
-__global__ void __launch_bounds__(SIM_THREADS, 1)
+//
+// DR = 2: two drain groups (warps 4..7 and 8..11).  Group g scans columns [g * BLOCK_N / 2, +BLOCK_N / 2) of every tile
+// into its own KP-sets and hands them over as their own candidate list ([query][split][group][KP]: to K9 the launch has
+// nsplit * DR splits).  One drain warp per SM sub-partition cannot hide the latency of its own inserts (~450 clocks
+// each, dependent shared-memory round trips); with independent queries the 32 lanes of a warp pass their thresholds at
+// different columns, so while sets warm up -- the first dozen tiles of every CTA -- the drain, not the tensor pipe, sets
+// the pace.  Costs one more candidate-set area of shared memory (two ring stages of the CTA-pair kernel), so the host
+// uses it on small shards only, where the warm-up is a large share of the launch.
+template <int BLOCK_N, int KP, int CG, int DR = 1>
+__global__ void __launch_bounds__(sim_threads(DR), 1)
 sim_topk_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_c,
                 const SimParams p) {
+  static_assert(DR == 1 || DR == 2, "one or two drain groups");
+  static_assert((BLOCK_N / 32 / DR) % 2 == 0, "every drain group walks an even number of 32-column chunks");
   constexpr uint32_t B_ROWS = BLOCK_N / CG;                     // corpus rows this CTA loads per tile
   constexpr uint32_t B_STAGE_BYTES = B_ROWS * SIM_BLOCK_K * 2;
   constexpr uint32_t IDESC = umma_idesc_f16_f32(SIM_BLOCK_M * CG, BLOCK_N);   // half x half -> fp32
@@ -343,8 +356,8 @@ sim_topk_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant
   const uint32_t stage_stride = a_in_stage + B_STAGE_BYTES;
   uint8_t* sA = smem;
   uint8_t* sB = p.a_stream ? smem : sA + (size_t)p.kc * SIM_A_CHUNK_BYTES;
-  uint64_t* ckeys = reinterpret_cast<uint64_t*>(sB + (size_t)p.nstage * stage_stride);   // [128][KP+1]
-  uint64_t* bars = ckeys + SIM_BLOCK_M * (KP + 1);
+  uint64_t* ckeys = reinterpret_cast<uint64_t*>(sB + (size_t)p.nstage * stage_stride);   // [DR][128][KP+1]
+  uint64_t* bars = ckeys + DR * SIM_BLOCK_M * (KP + 1);
   uint64_t* full = bars;                       // [nstage]  TMA -> MMA
   uint64_t* empty = bars + p.nstage;           // [nstage]  MMA -> TMA
   uint64_t* acc_full = bars + 2 * p.nstage;    // [2]       MMA -> drain
@@ -374,7 +387,7 @@ sim_topk_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&acc_full[i], 1);
-      mbar_init(&acc_empty[i], 4 * CG);  // one arrival per drain warp of the group (leader's copy)
+      mbar_init(&acc_empty[i], 4 * CG * DR);  // one arrival per drain warp of the CTA group (leader's copy)
     }
     mbar_init(a_full, CG);
     fence_mbar_init();
@@ -384,7 +397,7 @@ sim_topk_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant
     else tmem_alloc(tmem_slot, TMEM_COLS);
   }
   // candidate sets start empty
-  for (int i = threadIdx.x; i < SIM_BLOCK_M * (KP + 1); i += SIM_THREADS) ckeys[i] = 0;
+  for (int i = threadIdx.x; i < DR * SIM_BLOCK_M * (KP + 1); i += sim_threads(DR)) ckeys[i] = 0;
   tc_fence_before();
   if (CG == 2) cluster_sync_all();   // the peer's barriers exist before anyone signals them
   else __syncthreads();
@@ -471,10 +484,11 @@ sim_topk_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant
     }
   } else if (warp >= 4) {
     // ===== drain + select: thread owns one query (one TMEM lane) =====
-    const int wq = warp - 4;                   // TMEM lane group this warp may read
+    const int dg = (warp - 4) >> 2;            // drain group: which share of every tile's columns
+    const int wq = (warp - 4) & 3;             // TMEM lane group this warp may read (= warp % 4)
     const int row = wq * 32 + lane;
     const int qg = qtile * SIM_BLOCK_M + row;
-    uint64_t* my_keys = ckeys + row * (KP + 1);      // odd stride in 8-byte words: conflict-free
+    uint64_t* my_keys = ckeys + (dg * SIM_BLOCK_M + row) * (KP + 1);      // odd stride in 8-byte words: conflict-free
     const uint32_t my_keys_s = smem_u32(my_keys);
     int wpos = 0;
     const bool live = qg < p.nq;
@@ -531,16 +545,17 @@ sim_topk_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant
       // Software-pipelined drain: the tcgen05.ld of chunk c+1 is in flight while chunk c is
       // scanned; the accumulator stage goes back to the MMA warp as soon as its last chunk is in
       // registers.
-      constexpr int NCH = BLOCK_N / 32;
+      constexpr int NCH = BLOCK_N / 32 / DR;     // chunks this drain group walks
+      const int cbeg = dg * NCH;
       uint32_t v[2][32];
-      tmem_ld32(taddr, v[0]);
+      tmem_ld32(taddr + cbeg * 32, v[0]);
 #pragma unroll 1
       for (int c2 = 0; c2 < NCH; c2 += 2) {
 #pragma unroll
         for (int u = 0; u < 2; ++u) {
-          const int c = c2 + u;
+          const int c = cbeg + c2 + u;
           tmem_ld_wait_dep(v[u]);
-          if (c + 1 < NCH) {
+          if (c2 + u + 1 < NCH) {
             tmem_ld32(taddr + (c + 1) * 32, v[u ^ 1]);
           } else {
             tc_fence_before();
@@ -601,7 +616,7 @@ sim_topk_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant
     }
     // this split's candidates for this query
     if (qg < p.nq) {
-      const size_t o = ((size_t)qg * p.nsplit + split) * KP;
+      const size_t o = (((size_t)qg * p.nsplit + split) * DR + dg) * KP;
 #pragma unroll 4
       for (int j = 0; j < KP; ++j) p.cand[o + j] = my_keys[j];
     }

@@ -58,7 +58,7 @@ int b200_device_count(void);
 /* Process-wide switches between kernel variants, for A/B timing and for the tests that drive every
  * alternative path against the oracle (no reference counterpart).  Names and defaults:
  *   pdl 0 | gemm_pair 1 | gemm_ast 1 | attention_tc 1 | att_exact_max 0 | att_turns 1 | att_poly 1 (0..4) |
- *   fuse_ln 1 | fuse_ffn 1 | serpentine 1 | sim_pair 1 | sim_bound 3 | sim_refresh_mask 0 | search_certify 1 | sim_pair_kp 0 | sim_nsplit 0 | search_screen 1 | att_norms_fused 1 | defer_ln 1
+ *   fuse_ln 1 | fuse_ffn 1 | serpentine 1 | sim_pair 1 | sim_bound 3 | sim_refresh_mask 0 | search_certify 1 | sim_pair_kp 0 | sim_nsplit 0 | search_screen 1 | att_norms_fused 1 | defer_ln 1 | sim_drain 0
  * Unknown names and out-of-range values are refused with B200_ERR_INVALID. */
 int b200_set_option(const char* name, int value);
 int b200_get_option(const char* name, int* value);

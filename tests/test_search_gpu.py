@@ -259,3 +259,24 @@ def test_million_row_corpus_sampled_oracle_and_properties(vs):
     oi, os_ = so.topk_canonical(qs.float().cpu().numpy()[sample], rows_h, k)
     np.testing.assert_array_equal(ids_h[sample], oi)
     np.testing.assert_array_equal(sc_h[sample].view(np.uint32), os_.view(np.uint32))
+
+
+@pytest.mark.parametrize("opts", [dict(sim_drain=1), dict(sim_drain=2), dict(sim_pair=0), dict(sim_pair_kp=16, sim_drain=2),
+                                  dict(sim_pair_kp=20, sim_drain=2), dict(sim_bound=0), dict(sim_bound=1, sim_drain=2),
+                                  dict(sim_nsplit=3, sim_drain=2), dict(sim_refresh_mask=3)])
+def test_similarity_kernel_variants_match_oracle(vs, opts):
+    """Every switch of the similarity kernel (one / two drain groups, CTA pairs or single CTAs, 16 / 20 kept candidates,
+    cross-CTA bounds on / off, forced slice counts, lazier bound refresh) must leave ids and fp32 score bits untouched:
+    300 independent queries (three query tiles -> the CTA-pair kernel with a padded tile) over 70 000 rows, a tail tile."""
+    nat = pkg("_native")
+    rng = np.random.default_rng(42)
+    rows = rng.standard_normal((70_013, 384)).astype(np.float32)
+    qs = rng.standard_normal((300, 384)).astype(np.float32)
+    ix = vs.B200Index(384, device="cuda:0", master_dtype="float32")
+    ix.add(rows)
+    oi, os_ = so.topk_canonical(qs, rows, 10)
+    with nat.options(**opts):
+        ids, sc = ix.search(qs, 10)
+    np.testing.assert_array_equal(ids, oi)
+    np.testing.assert_array_equal(np.ascontiguousarray(sc).view(np.uint32), np.ascontiguousarray(os_).view(np.uint32))
+    ix.close()
