@@ -159,3 +159,17 @@ print("factory parity ok")
     env = dict(os.environ, PYTHONPATH=os.pathsep.join([ref + "/copilot_config", ref + "/copilot_vectorstore", ROOT]))
     r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300, env=env, cwd="/tmp")
     assert r.returncode == 0 and "factory parity ok" in r.stdout, r.stdout[-2000:] + r.stderr[-3000:]
+
+
+def test_host_out_is_a_fresh_writable_array_without_cuda():
+    """`_native.host_out` hands the host layer its result arrays: page-locked when torch + CUDA can provide them, plain
+    numpy otherwise (this box) -- either way a fresh, writable, C-contiguous array of the requested shape and dtype."""
+    nat = pkg("_native")
+    a = nat.host_out((3, 5), np.float32)
+    b = nat.host_out((3, 5), np.float32)
+    assert a.shape == (3, 5) and a.dtype == np.float32 and a.flags.c_contiguous and a.flags.writeable
+    a[:] = 1.0
+    b[:] = 2.0
+    assert float(a.sum()) == 15.0 and float(b.sum()) == 30.0          # two calls never alias
+    assert nat.host_out((0, 4), np.int64).shape == (0, 4)
+    assert nat.host_out((2,), np.int64).dtype == np.int64
