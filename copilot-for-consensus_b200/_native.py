@@ -135,12 +135,14 @@ def current_stream_ptr(device_ordinal: int) -> int:
 _PINNED_MAX_BYTES = 64 << 20
 
 
-def host_out(shape, dtype):
+def host_out(shape, dtype, device=None):
     """A numpy array for a result the library copies back from the GPU.  Page-locked when torch can provide it (its
     caching host allocator recycles the blocks of arrays that have been dropped, so after the first calls this costs
     microseconds): the device-to-host copy then runs at the DMA rate instead of being staged through the driver's bounce
     buffer, and so does the host-to-device copy when the caller hands the same array back (embeddings -> query).  A
-    fresh array per call, like ``np.empty``; plain pageable memory for results over 64 MB or without torch."""
+    fresh array per call, like ``np.empty``; plain pageable memory for results over 64 MB or without torch.  ``device``:
+    the ordinal the caller works on -- the allocation is made with that device current, so that a process driving
+    ``cuda:3`` does not create a context on ``cuda:0`` for it."""
     import numpy as np
 
     nbytes = int(np.prod(shape)) * np.dtype(dtype).itemsize
@@ -151,7 +153,10 @@ def host_out(shape, dtype):
             if torch.cuda.is_available():
                 tdt = {"float32": torch.float32, "int64": torch.int64, "int32": torch.int32}.get(np.dtype(dtype).name)
                 if tdt is not None:
-                    return torch.empty(tuple(int(x) for x in shape), dtype=tdt, pin_memory=True).numpy()
+                    if device is None:
+                        return torch.empty(tuple(int(x) for x in shape), dtype=tdt, pin_memory=True).numpy()
+                    with torch.cuda.device(int(device)):
+                        return torch.empty(tuple(int(x) for x in shape), dtype=tdt, pin_memory=True).numpy()
         except Exception:
             pass
     return np.empty(shape, dtype=dtype)

@@ -112,7 +112,7 @@ class B200SentenceTransformerProvider(EmbeddingProvider):
                 raise ValueError("Text cannot be empty or whitespace-only")
         n = len(texts)
         if to_host:
-            out = nat.host_out((n, self.dimension), np.float32)
+            out = nat.host_out((n, self.dimension), np.float32, self._dev)
         else:
             import torch
 
@@ -152,7 +152,7 @@ class B200SentenceTransformerProvider(EmbeddingProvider):
 
     def _encode_host(self, ids: np.ndarray, lens: np.ndarray) -> np.ndarray:
         B, S = ids.shape
-        out = nat.host_out((B, self.dimension), np.float32)
+        out = nat.host_out((B, self.dimension), np.float32, self._dev)
         with self._lock:
             nat.check(self._lib.b200_encode(self._h, ctypes.c_void_p(ids.ctypes.data), ctypes.c_void_p(lens.ctypes.data),
                                             B, S, 0, ctypes.c_void_p(out.ctypes.data), 0, self._stream()))

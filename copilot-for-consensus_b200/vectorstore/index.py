@@ -80,8 +80,8 @@ class B200Index:
         q = np.ascontiguousarray(queries, dtype=np.float32)
         if q.ndim != 2 or q.shape[1] != self.dim:
             raise ValueError(f"queries must be [nq, {self.dim}]")
-        ids = nat.host_out((q.shape[0], k), np.int64)
-        sc = nat.host_out((q.shape[0], k), np.float32)
+        ids = nat.host_out((q.shape[0], k), np.int64, self.device)
+        sc = nat.host_out((q.shape[0], k), np.float32, self.device)
         nat.check(self._lib.b200_index_search(self._h, ctypes.c_void_p(q.ctypes.data), 0, 0, q.shape[0], k, id_base,
                                               ctypes.c_void_p(ids.ctypes.data), ctypes.c_void_p(sc.ctypes.data), 0,
                                               self._stream()))
